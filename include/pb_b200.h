@@ -1,0 +1,167 @@
+/*
+ * pb_b200.h -- C ABI of libpb_b200.so: ProteinBERT pretraining forward/backward on B200 (sm_100a).
+ *
+ * The reference (Aedelon/ProteinBERT-PyTorch-Replication) is pure Python over torch.nn and has no
+ * native boundary of its own; every entry point below therefore cites the torch call sites of the
+ * reference that it replaces (file:line relative to the reference root).  A binding needs nothing
+ * but this header: plain device pointers, sizes, a dtype code and a CUDA stream.  No torch types.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; nothing is allocated or freed here:
+ *     outputs and workspaces are caller-owned (ask pb_workspace_bytes for the size).
+ *   - layouts are row-major and channels-last: local track [B, L, C], global track [B, G].
+ *   - dt selects the storage type of tensors marked `act` (activations) and `wt` (weights feeding
+ *     the big local-track contractions): PB_F32 = float, fp32 SIMT arithmetic (parity mode);
+ *     PB_BF16 = __nv_bfloat16 storage, tcgen05 bf16 tensor-core arithmetic with fp32 accumulation.
+ *     Everything else (global track, LayerNorm affine, biases, gradients of parameters) is float;
+ *     LayerNorm statistics and the loss are double.
+ *   - stream is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises.
+ *   - return value: 0 on success, PB_ERR_* otherwise, message via pb_last_error().  There is no
+ *     CPU or library fallback: unsupported shapes are refused.
+ */
+#ifndef PB_B200_H
+#define PB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PB_OK 0
+#define PB_ERR_SHAPE 1
+#define PB_ERR_CUDA 2
+#define PB_ERR_UNSUPPORTED 3
+#define PB_ERR_WORKSPACE 4
+
+#define PB_F32 0
+#define PB_BF16 1
+
+#define PB_ACT_NONE 0
+#define PB_ACT_GELU 1
+#define PB_ACT_SIGMOID 2
+
+/* ---- library ------------------------------------------------------------------------------- */
+int pb_version(void);
+const char* pb_last_error(void);
+/* 0 if `device` is a compute-capability-10.x GPU (the only target); PB_ERR_UNSUPPORTED otherwise. */
+int pb_device_ok(int device);
+/* number of kernel launches issued through this library since load (bench.py's gpu_launches). */
+long long pb_launch_count(void);
+
+/* ---- parameter staging ----------------------------------------------------------------------- */
+/* float -> bf16 copy of a weight tensor (shadow weights of the bf16 mode). */
+int pb_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+/* nn.Conv1d weight [Co, Ci, k] (modules.py:124-147) -> tap-major packs used by the conv kernels:
+ *   fwd_pack [k][Co][Ci]  (forward / wgrad)  and  bwd_pack [k][Ci][Co] (data gradient), dtype dt. */
+int pb_conv_weight_pack(const float* w, void* fwd_pack, void* bwd_pack, int C, int k, int dt, void* stream);
+
+/* ---- a2: token embedding (modules.py:249-253,300; backward = embedding_dense_backward) ------ */
+int pb_embedding_fwd(const int64_t* tok, const float* table, void* out_act, long long n_tok, int C, int V,
+                     int dt, void* stream);
+int pb_embedding_bwd(const int64_t* tok, const void* dout_act, float* dtable, long long n_tok, int C, int V,
+                     int dt, void* stream);
+
+/* ---- a3/a7/a13/a14/a16: dense layers of the global track --------------------------------------
+ * Y = act(X W^T + b), X [M,K], W [N,K] (nn.Linear layout), all float.  Replaces nn.Linear+GELU at
+ * modules.py:255-262 (annotations -> global), :166-173 (global -> local), :175-182, :188-195 and
+ * nn.Linear+Sigmoid at :286-293.  Z (pre-activation) is written when non-NULL (needed by the GELU
+ * backward).  ws: split-K partials, pb_workspace_bytes("linear_fwd", M, N, K).                  */
+int pb_linear_fwd(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
+                  int act, void* ws, size_t ws_bytes, void* stream);
+/* dZ = dY * act'(.) ; dX (+)= dZ W ; dW = dZ^T X ; db = sum_m dZ.  ZY is Z for GELU, Y for sigmoid.
+ * dX may be NULL (annotations carry no gradient, modules.py:301); accumulate_dx adds into dX.
+ * dZ_buf [M,N] is caller scratch.  ws as pb_workspace_bytes("linear_bwd", M, N, K).              */
+int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float* W, float* dZ_buf, float* dX,
+                  float* dW, float* db, int M, int N, int K, int act, int accumulate_dx, void* ws,
+                  size_t ws_bytes, void* stream);
+
+/* y = LayerNorm_G(a + b + coef*c), coef = sum(w_param)/Kdim  (modules.py:183-186,196-199,223-229 and the
+ * head mix of :87-92 under the reference's softmax axis).  b, c may be NULL.  Saves xhat and rstd. */
+int pb_res_ln_rows_fwd(const float* a, const float* b, const float* c, const float* w_param, int Kdim,
+                       const float* gamma, const float* beta, float* xhat, float* rstd, float* y, int B, int G,
+                       void* stream);
+/* dx = d(a) = d(b); d(c) = coef*dx (written to dc when non-NULL); dw_param[k] = (1/Kdim) sum dx*c. */
+int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, const float* rstd, const float* c,
+                       const float* w_param, int Kdim, float* dx, float* dc, float* dgamma, float* dbeta,
+                       float* dw_param, int B, int G, void* stream);
+
+/* ---- a5/a6/a7: narrow + dilated Conv1d, GELU, 4-way add with the global broadcast ---------------
+ * zn = conv(x, Wn, d=1)+bn, zw = conv(x, Ww, d=dil)+bw, u = x + gelu(zn) + gelu(zw) + g2l[b,:]
+ * (modules.py:205-211), and stats[b] += (sum u, sum u^2) over (L,C) for the joint LayerNorm that
+ * follows (:212).  stats must be zero on entry.  wn/ww are fwd packs from pb_conv_weight_pack. */
+int pb_conv_pair_fwd(const void* x_act, const void* wn_pack, const void* ww_pack, const float* bn, const float* bw,
+                     const float* g2l, void* zn_act, void* zw_act, void* u_act, double* stats, int B, int L, int C,
+                     int ksize, int dil, int dt, void* stream);
+/* backward of the above given du: dzn = du*gelu'(zn), dzw = du*gelu'(zw) (scratch, act type),
+ * dx = du + dgrad_n(dzn) + dgrad_w(dzw) (+ dx_extra when non-NULL), dWn/dWw [Co,Ci,k] float, dbn/dbw,
+ * dg2l[b,c] = sum_l du.  wn_bwd/ww_bwd are bwd packs.                                            */
+int pb_conv_pair_bwd(const void* du_act, const void* zn_act, const void* zw_act, const void* x_act,
+                     const void* wn_bwd, const void* ww_bwd, void* dzn_act, void* dzw_act, void* dx_act,
+                     float* dWn, float* dWw, float* dbn, float* dbw, float* dg2l, int B, int L, int C, int ksize,
+                     int dil, int dt, void* stream);
+
+/* ---- a8/a10: LayerNorm over (L,C) jointly, affine [L,C] (modules.py:148-151,161-164,212,217) --- */
+int pb_ln_joint_stats(const void* u_act, double* stats, int B, int L, int C, int dt, void* stream);
+int pb_ln_joint_apply(const void* u_act, const double* stats, const float* gamma, const float* beta, void* h_act,
+                      int B, int L, int C, float eps, int dt, void* stream);
+/* du, dgamma[L,C], dbeta[L,C] from dy; sums [B,2] double is caller scratch. */
+int pb_ln_joint_bwd(const void* dy_act, const void* u_act, const double* stats, const float* gamma, void* du_act,
+                    float* dgamma, float* dbeta, double* sums, int B, int L, int C, float eps, int dt, void* stream);
+
+/* ---- a9: local Linear(C->C)+GELU + residual (modules.py:153-160,214-216) ------------------------
+ * z = h W^T + b, u2 = h + gelu(z), stats2[b] += (sum, sumsq) of u2.  W is [C,C] of type wt.        */
+int pb_local_linear_fwd(const void* h_act, const void* W_wt, const float* bias, void* z_act, void* u2_act,
+                        double* stats2, int B, int L, int C, int dt, void* stream);
+/* dz = du2*gelu'(z) (scratch), dh = du2 + dz W, dW = dz^T h, db = sum dz.                          */
+int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_act, const void* W_wt, void* dz_act,
+                        void* dh_act, float* dW, float* db, int B, int L, int C, int dt, void* stream);
+
+/* ---- a11/a12: global attention (modules.py:21-92) under the reference's softmax axis ------------
+ * pool[b,g] = sum_l gelu(h[b,l,:] . Wv_all[:,g]); the layer output is (sum W_parameter / K) * pool
+ * (Softmax(dim=1) over K identical query rows makes every weight exactly 1/K).
+ * wvT is Wv_all transposed, [G, C], type wt.                                                       */
+int pb_attn_pool_fwd(const void* h_act, const void* wvT_wt, float* pool, int B, int L, int C, int G, int dt,
+                     void* stream);
+/* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip). */
+int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const float* dpool, const void* dh_in_act,
+                     void* dzv_act, void* dh_out_act, float* dWvT, int B, int L, int C, int G, int dt,
+                     void* stream);
+
+/* ---- a15: token head, softmax over the BATCH axis (modules.py:277-284; nn.Softmax() on 3-D) ----- */
+int pb_token_head_fwd(const void* h_act, const float* Wo, const float* bo, float* p_local, int B, int L, int C,
+                      int V, int dt, void* stream);
+int pb_token_head_bwd(const float* dP, const float* p_local, const void* h_act, const float* Wo,
+                      const double* grad_scale, void* dh_act, float* dWo, float* dbo, int B, int L, int C, int V,
+                      int dt, void* stream);
+
+/* ---- a17: the loss of utils.py:293-294 with CrossEntropyLoss/BCELoss(reduction='none') ----------
+ * loss[0] = mean(CE(p_local over V, y_local) * w_local) + mean(BCE(p_global, y_global) * w_global)
+ * (loss[1], loss[2] = the two terms), double.  When dP_local / dP_global are non-NULL they receive
+ * d loss / d p for grad_output = 1.                                                                */
+int pb_pretrain_loss(const float* p_local, const float* p_global, const int64_t* y_local, const float* y_global,
+                     const double* w_local, const double* w_global, double* loss, float* dP_local,
+                     float* dP_global, int B, int L, int V, int A, void* stream);
+/* dZ = grad_scale * dP * p * (1 - p) for the sigmoid head (feeds pb_linear_bwd with PB_ACT_NONE). */
+int pb_sigmoid_bwd(const float* dP, const float* p, const double* grad_scale, float* dZ, long long n, void* stream);
+
+/* ---- a19: input corruption and padding (data_processing.py:30-183), bit-exact given the draws ----
+ * seq_bytes: concatenated residue letters, seq_off [B+1]; draws in the reference's order:
+ * crop_start [B] (ignored unless len+2 > L), tok_mask/tok_rand: concatenated per-token draws with
+ * draw_off [B+1] (n_b = min(len_b+2, L) entries each), coin [B], keep/add [B,A] (0/1), ann [B,A].
+ * Outputs: X_local,Y_local int64 [B,L]; X_global,Y_global float [B,A]; W_local double [B,L];
+ * W_global double [B,A].                                                                           */
+int pb_corrupt_pad(const uint8_t* seq_bytes, const int64_t* seq_off, const int64_t* crop_start,
+                   const uint8_t* tok_mask, const uint8_t* tok_rand, const int64_t* draw_off, const float* coin,
+                   const uint8_t* keep, const uint8_t* add, const uint8_t* ann, int64_t* x_local,
+                   int64_t* y_local, double* w_local, float* x_global, float* y_global, double* w_global, int B,
+                   int L, int A, void* stream);
+
+/* ---- sizing ------------------------------------------------------------------------------------ */
+size_t pb_workspace_bytes(const char* op, int M, int N, int K);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PB_B200_H */

@@ -1,0 +1,101 @@
+// Library plumbing: error string, device check, launch counter, parameter staging kernels.
+#include <stdarg.h>
+#include <string.h>
+#include <atomic>
+#include "common.cuh"
+#include "../../include/pb_b200.h"
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void pb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void pb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int pb_check_launch(const char* what) {
+    cudaError_t e = cudaPeekAtLastError();
+    if (e != cudaSuccess) {
+        pb_set_error("%s: launch failed: %s", what, cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return PB_ERR_CUDA;
+    }
+    return PB_OK;
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long n) {
+    long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 3 < n) {
+        const float4 v = *reinterpret_cast<const float4*>(src + i);
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(dst + i) = o;
+    } else {
+        for (; i < n; ++i) dst[i] = __float2bfloat16_rn(src[i]);
+    }
+}
+
+template <typename T>
+__global__ void conv_pack_kernel(const float* __restrict__ w, T* __restrict__ fwd, T* __restrict__ bwd, int C, int k) {
+    // w [co][ci][t] -> fwd [t][co][ci], bwd [t][ci][co]
+    const long long n = (long long)C * C * k;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const int t = (int)(i % k);
+        const int ci = (int)((i / k) % C);
+        const int co = (int)(i / ((long long)k * C));
+        const float v = w[i];
+        if (fwd) stf(fwd, ((size_t)t * C + co) * C + ci, v);
+        if (bwd) stf(bwd, ((size_t)t * C + ci) * C + co, v);
+    }
+}
+
+extern "C" {
+
+int pb_version(void) { return 100; }
+const char* pb_last_error(void) { return g_err; }
+long long pb_launch_count(void) { return g_launches.load(); }
+
+int pb_device_ok(int device) {
+    cudaDeviceProp p;
+    PB_CUDA(cudaGetDeviceProperties(&p, device));
+    PB_REQUIRE(p.major == 10, PB_ERR_UNSUPPORTED,
+               "device %d is sm_%d%d; libpb_b200 is built for sm_100a (B200) only and has no fallback", device,
+               p.major, p.minor);
+    return PB_OK;
+}
+
+int pb_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
+    if (n <= 0) return PB_OK;
+    PB_REQUIRE(((uintptr_t)src % 16 == 0) && ((uintptr_t)dst % 8 == 0), PB_ERR_SHAPE, "cast: misaligned pointers");
+    const long long nthreads = (n + 3) / 4;
+    cast_f32_bf16_kernel<<<ceil_div(nthreads, 256), 256, 0, (cudaStream_t)stream>>>(src, (bf16*)dst, n);
+    pb_count_launch(1);
+    return pb_check_launch("pb_cast_f32_to_bf16");
+}
+
+int pb_conv_weight_pack(const float* w, void* fwd_pack, void* bwd_pack, int C, int k, int dt, void* stream) {
+    PB_REQUIRE(C > 0 && k > 0, PB_ERR_SHAPE, "conv_weight_pack: bad shape C=%d k=%d", C, k);
+    const long long n = (long long)C * C * k;
+    const int grid = min(ceil_div(n, 256), 1184);
+    if (dt == PB_F32)
+        conv_pack_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(w, (float*)fwd_pack, (float*)bwd_pack, C, k);
+    else
+        conv_pack_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)fwd_pack, (bf16*)bwd_pack, C, k);
+    pb_count_launch(1);
+    return pb_check_launch("pb_conv_weight_pack");
+}
+
+size_t pb_workspace_bytes(const char* op, int M, int N, int K) {
+    // split-K partials of the global-track GEMMs: at most 32 splits of an [M,N] (or [M,K]) float tile
+    if (!strcmp(op, "linear_fwd")) return (size_t)32 * M * N * sizeof(float);
+    if (!strcmp(op, "linear_bwd")) return (size_t)32 * M * K * sizeof(float);
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+// Shared device/host helpers for the ProteinBERT B200 kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <math.h>
+
+#define PB_OK 0
+#define PB_ERR_SHAPE 1
+#define PB_ERR_CUDA 2
+#define PB_ERR_UNSUPPORTED 3
+#define PB_ERR_WORKSPACE 4
+
+#define PB_F32 0
+#define PB_BF16 1
+
+#define PB_ACT_NONE 0
+#define PB_ACT_GELU 1
+#define PB_ACT_SIGMOID 2
+
+typedef __nv_bfloat16 bf16;
+
+// ---- error plumbing ---------------------------------------------------------
+void pb_set_error(const char* fmt, ...);
+int pb_check_launch(const char* what);
+void pb_count_launch(int n);
+
+#define PB_REQUIRE(cond, code, ...)            \
+    do {                                       \
+        if (!(cond)) {                         \
+            pb_set_error(__VA_ARGS__);         \
+            return (code);                     \
+        }                                      \
+    } while (0)
+
+#define PB_CUDA(call)                                                            \
+    do {                                                                         \
+        cudaError_t e__ = (call);                                                \
+        if (e__ != cudaSuccess) {                                                \
+            pb_set_error("%s failed: %s", #call, cudaGetErrorString(e__));       \
+            return PB_ERR_CUDA;                                                  \
+        }                                                                        \
+    } while (0)
+
+// ---- scalar helpers ---------------------------------------------------------
+__device__ __forceinline__ float ldf(const float* p, size_t i) { return p[i]; }
+__device__ __forceinline__ float ldf(const bf16* p, size_t i) { return __bfloat162float(p[i]); }
+__device__ __forceinline__ void stf(float* p, size_t i, float v) { p[i] = v; }
+__device__ __forceinline__ void stf(bf16* p, size_t i, float v) { p[i] = __float2bfloat16_rn(v); }
+// value after a round trip through the storage type (stats are taken of STORED values)
+__device__ __forceinline__ float rnd(const float*, float v) { return v; }
+__device__ __forceinline__ float rnd(const bf16*, float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+// exact-erf GELU, as nn.GELU() (approximate='none')
+__device__ __forceinline__ float gelu_f(float t) { return 0.5f * t * (1.0f + erff(t * 0.70710678118654752440f)); }
+// d gelu / dt = Phi(t) + t*phi(t)
+__device__ __forceinline__ float gelu_grad_f(float t) {
+    const float cdf = 0.5f * (1.0f + erff(t * 0.70710678118654752440f));
+    const float pdf = 0.39894228040143267794f * __expf(-0.5f * t * t);
+    return cdf + t * pdf;
+}
+__device__ __forceinline__ float sigmoid_f(float t) { return 1.0f / (1.0f + expf(-t)); }
+
+__device__ __forceinline__ float act_fwd(int act, float z) {
+    return act == PB_ACT_GELU ? gelu_f(z) : (act == PB_ACT_SIGMOID ? sigmoid_f(z) : z);
+}
+// derivative given pre-activation z (gelu) or OUTPUT y (sigmoid): the caller passes the right one
+__device__ __forceinline__ float act_bwd(int act, float zy) {
+    return act == PB_ACT_GELU ? gelu_grad_f(zy) : (act == PB_ACT_SIGMOID ? zy * (1.0f - zy) : 1.0f);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// block-wide sum for blockDim.x <= 1024; result valid in every thread
+template <typename V>
+__device__ __forceinline__ V block_sum(V v, V* smem /* >= 32 */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) smem[w] = v;
+    __syncthreads();
+    V r = (threadIdx.x < nw) ? smem[threadIdx.x] : V(0);
+    if (w == 0) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+        if (lane == 0) smem[0] = r;
+    }
+    __syncthreads();
+    return smem[0];
+}
+
+// per-sample LayerNorm statistics from the (sum, sumsq) doubles
+struct LnStat { float mean, rstd; };
+__device__ __forceinline__ LnStat ln_stat(const double* stats, int b, double n, float eps) {
+    const double s = stats[2 * b], q = stats[2 * b + 1];
+    const double mean = s / n;
+    double var = q / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    LnStat r;
+    r.mean = (float)mean;
+    r.rstd = (float)(1.0 / sqrt(var + (double)eps));
+    return r;
+}
+
+static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }

@@ -1,0 +1,240 @@
+// Global-track operators (all float, M = batch rows): dense layers with split-K, and the
+// residual + LayerNorm over G.  Reference call sites: modules.py:166-199,208,221-229,255-262,286-293.
+#include "gemm_simt.cuh"
+#include "../../include/pb_b200.h"
+
+namespace {
+
+constexpr int kMaxSplit = 32;
+
+struct EpLinearDirect {
+    const float* bias; float* Z; float* Y; int N; int act;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        const float z = acc + (bias ? bias[n] : 0.f);
+        const size_t i = (size_t)m * N + n;
+        if (Z) Z[i] = z;
+        Y[i] = act_fwd(act, z);
+    }
+};
+struct EpPartial {
+    float* ws; int M; int N;
+    __device__ void operator()(int m, int n, float acc, int split, int) const {
+        ws[((size_t)split * M + m) * N + n] = acc;
+    }
+};
+struct EpStore {
+    float* out; long ld;
+    __device__ void operator()(int m, int n, float acc, int, int) const { out[(size_t)m * ld + n] = acc; }
+};
+struct EpStoreAcc {
+    float* out; long ld; int accumulate;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        const size_t i = (size_t)m * ld + n;
+        out[i] = accumulate ? out[i] + acc : acc;
+    }
+};
+
+__global__ void linear_reduce_kernel(const float* __restrict__ ws, const float* __restrict__ bias, float* Z, float* Y,
+                                     int M, int N, int nsplit, int act) {
+    const long long total = (long long)M * N;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < nsplit; ++k) s += ws[(size_t)k * total + i];
+        const float z = s + (bias ? bias[i % N] : 0.f);
+        if (Z) Z[i] = z;
+        Y[i] = act_fwd(act, z);
+    }
+}
+
+__global__ void partial_reduce_kernel(const float* __restrict__ ws, float* out, long long total, int nsplit, int accumulate) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int k = 0; k < nsplit; ++k) s += ws[(size_t)k * total + i];
+        out[i] = accumulate ? out[i] + s : s;
+    }
+}
+
+// dZ = dY * act'(ZY); db[n] = sum_m dZ[m,n].  One thread per column n.
+__global__ void linear_dz_kernel(const float* __restrict__ dY, const float* __restrict__ ZY, float* __restrict__ dZ,
+                                 float* __restrict__ db, int M, int N, int act) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float s = 0.f;
+    for (int m = 0; m < M; ++m) {
+        const size_t i = (size_t)m * N + n;
+        const float g = dY[i] * (act == PB_ACT_NONE ? 1.f : act_bwd(act, ZY[i]));
+        dZ[i] = g;
+        s += g;
+    }
+    if (db) db[n] = s;
+}
+
+int pick_split(int tiles, int K) {
+    int s = 296 / (tiles > 0 ? tiles : 1);
+    if (s > kMaxSplit) s = kMaxSplit;
+    while (s > 1 && K / s < 64) --s;
+    return s < 1 ? 1 : s;
+}
+
+// y = LN(a + b + coef*c): one CTA per row, dynamic smem of G floats.
+__global__ void res_ln_rows_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ c,
+                                       const float* __restrict__ w_param, int Kdim, const float* __restrict__ gamma,
+                                       const float* __restrict__ beta, float* __restrict__ xhat, float* __restrict__ rstd_out,
+                                       float* __restrict__ y, int G) {
+    extern __shared__ float row[];
+    __shared__ float red[32];
+    const int r = blockIdx.x;
+    float coef = 0.f;
+    if (c) {
+        float t = 0.f;
+        for (int k = threadIdx.x; k < Kdim; k += blockDim.x) t += w_param[k];
+        coef = block_sum(t, red) / (float)Kdim;
+    }
+    float s = 0.f;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        const size_t i = (size_t)r * G + g;
+        float v = a[i];
+        if (b) v += b[i];
+        if (c) v += coef * c[i];
+        row[g] = v;
+        s += v;
+    }
+    const float mean = block_sum(s, red) / (float)G;
+    float q = 0.f;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) { const float d = row[g] - mean; q += d * d; }
+    const float var = block_sum(q, red) / (float)G;
+    const float rstd = rsqrtf(var + 1e-5f);
+    if (threadIdx.x == 0) rstd_out[r] = rstd;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        const size_t i = (size_t)r * G + g;
+        const float xh = (row[g] - mean) * rstd;
+        xhat[i] = xh;
+        y[i] = xh * gamma[g] + beta[g];
+    }
+}
+
+__global__ void res_ln_rows_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ gamma,
+                                       const float* __restrict__ xhat, const float* __restrict__ rstd,
+                                       const float* __restrict__ c, const float* __restrict__ w_param, int Kdim,
+                                       float* __restrict__ dx, float* __restrict__ dc, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta, float* __restrict__ dw_param, int G) {
+    __shared__ float red[32];
+    const int r = blockIdx.x;
+    float s1 = 0.f, s2 = 0.f;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        const size_t i = (size_t)r * G + g;
+        const float d = dy[i] * gamma[g];
+        s1 += d;
+        s2 += d * xhat[i];
+    }
+    const float m1 = block_sum(s1, red) / (float)G;
+    const float m2 = block_sum(s2, red) / (float)G;
+    float coef = 0.f;
+    if (c) {
+        float t = 0.f;
+        for (int k = threadIdx.x; k < Kdim; k += blockDim.x) t += w_param[k];
+        coef = block_sum(t, red) / (float)Kdim;
+    }
+    const float rs = rstd[r];
+    float dcoef = 0.f;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        const size_t i = (size_t)r * G + g;
+        const float xh = xhat[i], dyv = dy[i];
+        const float v = rs * (dyv * gamma[g] - m1 - xh * m2);
+        dx[i] = v;
+        if (c) {
+            if (dc) dc[i] = coef * v;
+            dcoef += v * c[i];
+        }
+        atomicAdd(&dgamma[g], dyv * xh);
+        atomicAdd(&dbeta[g], dyv);
+    }
+    if (c && dw_param) {
+        const float tot = block_sum(dcoef, red) / (float)Kdim;
+        for (int k = threadIdx.x; k < Kdim; k += blockDim.x) atomicAdd(&dw_param[k], tot);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int pb_linear_fwd(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K, int act,
+                  void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, PB_ERR_SHAPE, "linear_fwd: bad shape M=%d N=%d K=%d", M, N, K);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int tiles = ceil_div(N, 64) * ceil_div(M, 64);
+    int nsplit = pick_split(tiles, K);
+    if (nsplit > 1 && (ws == nullptr || ws_bytes < (size_t)nsplit * M * N * sizeof(float))) nsplit = 1;
+    RowMajorA<float> al{X, K};
+    WeightNK<float> bl{W, K};
+    if (nsplit == 1) {
+        launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpLinearDirect{bias, Z, Y, N, act}, M, N, K, 1, 1, st);
+        pb_count_launch(1);
+    } else {
+        launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpPartial{(float*)ws, M, N}, M, N, K, nsplit, 1, st);
+        linear_reduce_kernel<<<min(ceil_div((long)M * N, 256), 1184), 256, 0, st>>>((const float*)ws, bias, Z, Y, M, N, nsplit, act);
+        pb_count_launch(2);
+    }
+    return pb_check_launch("pb_linear_fwd");
+}
+
+int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float* W, float* dZ_buf, float* dX, float* dW,
+                  float* db, int M, int N, int K, int act, int accumulate_dx, void* ws, size_t ws_bytes, void* stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, PB_ERR_SHAPE, "linear_bwd: bad shape M=%d N=%d K=%d", M, N, K);
+    PB_REQUIRE(dZ_buf != nullptr, PB_ERR_WORKSPACE, "linear_bwd: dZ_buf is required");
+    PB_REQUIRE(act == PB_ACT_NONE || ZY != nullptr, PB_ERR_SHAPE, "linear_bwd: ZY required for act=%d", act);
+    cudaStream_t st = (cudaStream_t)stream;
+    linear_dz_kernel<<<ceil_div(N, 128), 128, 0, st>>>(dY, ZY, dZ_buf, db, M, N, act);
+    pb_count_launch(1);
+    if (dX) {
+        // dX[m,k] = sum_n dZ[m,n] W[n,k]
+        const int tiles = ceil_div(K, 64) * ceil_div(M, 64);
+        int nsplit = pick_split(tiles, N);
+        if (nsplit > 1 && (ws == nullptr || ws_bytes < (size_t)nsplit * M * K * sizeof(float))) nsplit = 1;
+        RowMajorA<float> al{dZ_buf, N};
+        MatKN<float> bl{W, K};
+        if (nsplit == 1) {
+            launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpStoreAcc{dX, K, accumulate_dx}, M, K, N, 1, 1, st);
+            pb_count_launch(1);
+        } else {
+            launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpPartial{(float*)ws, M, K}, M, K, N, nsplit, 1, st);
+            partial_reduce_kernel<<<min(ceil_div((long)M * K, 256), 1184), 256, 0, st>>>((const float*)ws, dX, (long long)M * K,
+                                                                                       nsplit, accumulate_dx);
+            pb_count_launch(2);
+        }
+    }
+    if (dW) {
+        // dW[n,k] = sum_m dZ[m,n] X[m,k]
+        ColMajorA<float> al{dZ_buf, N};
+        MatKN<float> bl{X, K};
+        launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpStore{dW, K}, N, K, M, 1, 1, st);
+        pb_count_launch(1);
+    }
+    return pb_check_launch("pb_linear_bwd");
+}
+
+int pb_res_ln_rows_fwd(const float* a, const float* b, const float* c, const float* w_param, int Kdim, const float* gamma,
+                       const float* beta, float* xhat, float* rstd, float* y, int B, int G, void* stream) {
+    PB_REQUIRE(B > 0 && G > 0 && G <= 12288, PB_ERR_SHAPE, "res_ln_rows_fwd: bad shape B=%d G=%d", B, G);
+    PB_REQUIRE(c == nullptr || (w_param != nullptr && Kdim > 0), PB_ERR_SHAPE, "res_ln_rows_fwd: c needs w_param");
+    res_ln_rows_fwd_kernel<<<B, 128, G * sizeof(float), (cudaStream_t)stream>>>(a, b, c, w_param, Kdim, gamma, beta, xhat,
+                                                                               rstd, y, G);
+    pb_count_launch(1);
+    return pb_check_launch("pb_res_ln_rows_fwd");
+}
+
+int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, const float* rstd, const float* c,
+                       const float* w_param, int Kdim, float* dx, float* dc, float* dgamma, float* dbeta, float* dw_param,
+                       int B, int G, void* stream) {
+    PB_REQUIRE(B > 0 && G > 0, PB_ERR_SHAPE, "res_ln_rows_bwd: bad shape B=%d G=%d", B, G);
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(dgamma, 0, G * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dbeta, 0, G * sizeof(float), st));
+    if (c && dw_param) PB_CUDA(cudaMemsetAsync(dw_param, 0, Kdim * sizeof(float), st));
+    res_ln_rows_bwd_kernel<<<B, 128, 0, st>>>(dy, gamma, xhat, rstd, c, w_param, Kdim, dx, dc, dgamma, dbeta, dw_param, G);
+    pb_count_launch(1);
+    return pb_check_launch("pb_res_ln_rows_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,296 @@
+// Embedding, token head (batch-axis softmax), the pretraining loss and the sigmoid backward.
+// Reference call sites: modules.py:249-253,277-293,300,304; utils.py:293-294; dummy_tests.py:132-133.
+#include "common.cuh"
+#include "../../include/pb_b200.h"
+
+namespace {
+
+#define DISPATCH_DT(dt, ...)                                                   \
+    do {                                                                       \
+        if ((dt) == PB_F32) { using T = float; __VA_ARGS__; }                  \
+        else if ((dt) == PB_BF16) { using T = bf16; __VA_ARGS__; }             \
+        else { pb_set_error("unknown dtype code %d", (dt)); return PB_ERR_UNSUPPORTED; } \
+    } while (0)
+
+// ---- embedding --------------------------------------------------------------------------------
+template <typename T>
+__global__ void embedding_fwd_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, T* __restrict__ out,
+                                     long long n_tok, int C, int V) {
+    const long long total = n_tok * C;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / C;
+        const int c = (int)(i - r * C);
+        const int64_t t = tok[r];
+        stf(out, (size_t)i, (t >= 0 && t < V) ? table[(size_t)t * C + c] : 0.f);
+    }
+}
+
+// shared-memory privatised scatter-add: each CTA owns a [V, C] float accumulator for its slice of rows
+template <typename T>
+__global__ void embedding_bwd_kernel(const int64_t* __restrict__ tok, const T* __restrict__ dout, float* __restrict__ dtable,
+                                     long long n_tok, int C, int V) {
+    extern __shared__ float acc[];           // [V*C]
+    for (int i = threadIdx.x; i < V * C; i += blockDim.x) acc[i] = 0.f;
+    __syncthreads();
+    const long long per = (n_tok + gridDim.x - 1) / gridDim.x;
+    const long long r0 = blockIdx.x * per, r1 = min(n_tok, r0 + per);
+    const long long total = (r1 - r0) * C;
+    for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+        const long long r = r0 + i / C;
+        const int c = (int)(i % C);
+        const int64_t t = tok[r];
+        if (t >= 0 && t < V) atomicAdd(&acc[(int)t * C + c], ldf(dout, (size_t)r * C + c));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < V * C; i += blockDim.x) {
+        const float v = acc[i];
+        if (v != 0.f) atomicAdd(&dtable[i], v);
+    }
+}
+
+// ---- token head ---------------------------------------------------------------------------------
+// One CTA per sequence position l (grid-stride).  The softmax runs over the BATCH axis, so the CTA needs
+// all B rows of its position: smem holds h[:, l, :] as float [B][C+1], Wo [V][C+1], logits/probs [B][V].
+template <typename T>
+__global__ void token_head_fwd_kernel(const T* __restrict__ h, const float* __restrict__ Wo, const float* __restrict__ bo,
+                                      float* __restrict__ p_local, int B, int L, int C, int V) {
+    extern __shared__ float sm[];
+    const int ldc = C + 1;
+    float* sh = sm;                          // [B][ldc]
+    float* sw = sh + (size_t)B * ldc;        // [V][ldc]
+    float* sp = sw + (size_t)V * ldc;        // [B][V]
+    for (int i = threadIdx.x; i < V * C; i += blockDim.x) sw[(i / C) * ldc + (i % C)] = Wo[i];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    for (int l = blockIdx.x; l < L; l += gridDim.x) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < B * C; i += blockDim.x) {
+            const int b = i / C, c = i - b * C;
+            sh[b * ldc + c] = ldf(h, ((size_t)b * L + l) * C + c);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < B * V; i += blockDim.x) {
+            const int b = i / V, v = i - b * V;
+            float a = bo[v];
+            const float* hr = sh + b * ldc;
+            const float* wr = sw + v * ldc;
+            for (int c = 0; c < C; ++c) a = fmaf(hr[c], wr[c], a);
+            sp[i] = a;
+        }
+        __syncthreads();
+        // softmax over b for every vocabulary column v: one warp per column
+        for (int v = warp; v < V; v += nwarp) {
+            float mx = -INFINITY;
+            for (int b = lane; b < B; b += 32) mx = fmaxf(mx, sp[b * V + v]);
+            mx = warp_max(mx);
+            float s = 0.f;
+            for (int b = lane; b < B; b += 32) { const float e = expf(sp[b * V + v] - mx); sp[b * V + v] = e; s += e; }
+            s = warp_sum(s);
+            const float inv = 1.0f / s;
+            for (int b = lane; b < B; b += 32) sp[b * V + v] *= inv;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < B * V; i += blockDim.x) {
+            const int b = i / V, v = i - b * V;
+            p_local[((size_t)b * L + l) * V + v] = sp[i];
+        }
+    }
+}
+
+// backward: dlogit[b,v] = s * p[b,v] * (dP[b,v] - sum_b' p[b',v] dP[b',v]);  dh = dlogit Wo;
+// dWo[v,c] += sum_b dlogit[b,v] h[b,l,c];  dbo[v] += sum_b dlogit[b,v].
+template <typename T>
+__global__ void token_head_bwd_kernel(const float* __restrict__ dP, const float* __restrict__ p_local, const T* __restrict__ h,
+                                      const float* __restrict__ Wo, const double* __restrict__ grad_scale, T* __restrict__ dh,
+                                      float* __restrict__ dWo, float* __restrict__ dbo, int B, int L, int C, int V) {
+    extern __shared__ float sm[];
+    const int ldc = C + 1;
+    float* sh = sm;                          // [B][ldc]
+    float* sw = sh + (size_t)B * ldc;        // [V][ldc]
+    float* sd = sw + (size_t)V * ldc;        // [B][V] dlogit
+    float* sacc = sd + (size_t)B * V;        // [V][C] dWo partial
+    float* sb = sacc + (size_t)V * C;        // [V] dbo partial
+    const float gs = grad_scale ? (float)(*grad_scale) : 1.0f;
+    for (int i = threadIdx.x; i < V * C; i += blockDim.x) { sw[(i / C) * ldc + (i % C)] = Wo[i]; sacc[i] = 0.f; }
+    for (int i = threadIdx.x; i < V; i += blockDim.x) sb[i] = 0.f;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    for (int l = blockIdx.x; l < L; l += gridDim.x) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < B * C; i += blockDim.x) {
+            const int b = i / C, c = i - b * C;
+            sh[b * ldc + c] = ldf(h, ((size_t)b * L + l) * C + c);
+        }
+        for (int v = warp; v < V; v += nwarp) {
+            float dot = 0.f;
+            for (int b = lane; b < B; b += 32) {
+                const size_t gi = ((size_t)b * L + l) * V + v;
+                dot += p_local[gi] * dP[gi];
+            }
+            dot = warp_sum(dot);
+            float sbv = 0.f;
+            for (int b = lane; b < B; b += 32) {
+                const size_t gi = ((size_t)b * L + l) * V + v;
+                const float d = gs * p_local[gi] * (dP[gi] - dot);
+                sd[b * V + v] = d;
+                sbv += d;
+            }
+            sbv = warp_sum(sbv);
+            if (lane == 0) sb[v] += sbv;
+        }
+        __syncthreads();
+        // dh[b,l,c] = sum_v dlogit[b,v] Wo[v,c]
+        for (int i = threadIdx.x; i < B * C; i += blockDim.x) {
+            const int b = i / C, c = i - b * C;
+            float a = 0.f;
+            for (int v = 0; v < V; ++v) a = fmaf(sd[b * V + v], sw[v * ldc + c], a);
+            stf(dh, ((size_t)b * L + l) * C + c, a);
+        }
+        // dWo partial: thread owns (v,c) entries
+        for (int i = threadIdx.x; i < V * C; i += blockDim.x) {
+            const int v = i / C, c = i - v * C;
+            float a = 0.f;
+            for (int b = 0; b < B; ++b) a = fmaf(sd[b * V + v], sh[b * ldc + c], a);
+            sacc[i] += a;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < V * C; i += blockDim.x) atomicAdd(&dWo[i], sacc[i]);
+    for (int i = threadIdx.x; i < V; i += blockDim.x) atomicAdd(&dbo[i], sb[i]);
+}
+
+// ---- loss ---------------------------------------------------------------------------------------
+// Token term: CE over the vocabulary axis of the PROBABILITIES (second softmax), times w_local, / (B*L).
+// Annotation term: BCE with logs clamped at -100, times w_global, / (B*A).  fp64 accumulation.
+__global__ void loss_kernel(const float* __restrict__ p_local, const float* __restrict__ p_global,
+                            const int64_t* __restrict__ y_local, const float* __restrict__ y_global,
+                            const double* __restrict__ w_local, const double* __restrict__ w_global, double* __restrict__ loss,
+                            float* __restrict__ dP_local, float* __restrict__ dP_global, long long n_tok, int V, long long n_ann) {
+    __shared__ double red[32];
+    double acc_l = 0.0, acc_g = 0.0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const double inv_tok = 1.0 / (double)n_tok, inv_ann = 1.0 / (double)n_ann;
+    for (long long r = tid; r < n_tok; r += stride) {
+        const float* pr = p_local + (size_t)r * V;
+        float mx = -INFINITY;
+        for (int v = 0; v < V; ++v) mx = fmaxf(mx, pr[v]);
+        float s = 0.f;
+        for (int v = 0; v < V; ++v) s += expf(pr[v] - mx);
+        const float lse = mx + logf(s);
+        const int64_t y = y_local[r];
+        const double w = w_local[r];
+        const bool ok = (y >= 0 && y < V);
+        if (ok) acc_l += (double)(lse - pr[y]) * w;
+        if (dP_local) {
+            const float wf = ok ? (float)(w * inv_tok) : 0.f;
+            float* dr = dP_local + (size_t)r * V;
+            for (int v = 0; v < V; ++v) dr[v] = wf * (expf(pr[v] - lse) - (v == (int)y ? 1.f : 0.f));
+        }
+    }
+    for (long long i = tid; i < n_ann; i += stride) {
+        const float p = p_global[i], y = y_global[i];
+        const double w = w_global[i];
+        const float lp = fmaxf(logf(p), -100.f), l1p = fmaxf(logf(1.f - p), -100.f);   // (1 - input).log() as torch's BCELoss
+        acc_g += (double)(-(y * lp + (1.f - y) * l1p)) * w;
+        if (dP_global) {
+            // torch binary_cross_entropy_backward: (p - y) / max((1 - p) * p, 1e-12)
+            dP_global[i] = (float)(w * inv_ann) * (p - y) / fmaxf((1.f - p) * p, 1e-12f);
+        }
+    }
+    acc_l = block_sum(acc_l, red) * inv_tok;
+    acc_g = block_sum(acc_g, red) * inv_ann;
+    if (threadIdx.x == 0) {
+        atomicAdd(&loss[1], acc_l);
+        atomicAdd(&loss[2], acc_g);
+        atomicAdd(&loss[0], acc_l + acc_g);
+    }
+}
+
+__global__ void sigmoid_bwd_kernel(const float* __restrict__ dP, const float* __restrict__ p, const double* __restrict__ gs,
+                                   float* __restrict__ dZ, long long n) {
+    const float s = gs ? (float)(*gs) : 1.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float pv = p[i];
+        dZ[i] = s * dP[i] * pv * (1.f - pv);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int pb_embedding_fwd(const int64_t* tok, const float* table, void* out, long long n_tok, int C, int V, int dt, void* stream) {
+    PB_REQUIRE(n_tok > 0 && C > 0 && V > 0, PB_ERR_SHAPE, "embedding_fwd: bad shape");
+    const int grid = (int)min((long long)ceil_div(n_tok * C, 256), 148LL * 16);
+    DISPATCH_DT(dt, (embedding_fwd_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(tok, table, (T*)out, n_tok, C, V)));
+    pb_count_launch(1);
+    return pb_check_launch("pb_embedding_fwd");
+}
+
+int pb_embedding_bwd(const int64_t* tok, const void* dout, float* dtable, long long n_tok, int C, int V, int dt, void* stream) {
+    PB_REQUIRE(n_tok > 0 && C > 0 && V > 0, PB_ERR_SHAPE, "embedding_bwd: bad shape");
+    const size_t smem = (size_t)V * C * sizeof(float);
+    PB_REQUIRE(smem <= 200 * 1024, PB_ERR_UNSUPPORTED, "embedding_bwd: table of %d x %d floats does not fit shared memory", V, C);
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(dtable, 0, smem, st));
+    const int grid = (int)min((long long)ceil_div(n_tok, 64), 148LL * 2);
+    DISPATCH_DT(dt, {
+        if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        embedding_bwd_kernel<T><<<grid, 256, smem, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
+    });
+    pb_count_launch(1);
+    return pb_check_launch("pb_embedding_bwd");
+}
+
+int pb_token_head_fwd(const void* h, const float* Wo, const float* bo, float* p_local, int B, int L, int C, int V, int dt,
+                      void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && V > 0, PB_ERR_SHAPE, "token_head_fwd: bad shape");
+    const size_t smem = ((size_t)B * (C + 1) + (size_t)V * (C + 1) + (size_t)B * V) * sizeof(float);
+    PB_REQUIRE(smem <= 220 * 1024, PB_ERR_UNSUPPORTED,
+               "token_head_fwd: the batch-axis softmax keeps all %d rows of a position on chip; B*C too large (%zu B)", B, smem);
+    cudaStream_t st = (cudaStream_t)stream;
+    DISPATCH_DT(dt, {
+        if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(token_head_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        token_head_fwd_kernel<T><<<min(L, 148 * 4), 256, smem, st>>>((const T*)h, Wo, bo, p_local, B, L, C, V);
+    });
+    pb_count_launch(1);
+    return pb_check_launch("pb_token_head_fwd");
+}
+
+int pb_token_head_bwd(const float* dP, const float* p_local, const void* h, const float* Wo, const double* grad_scale, void* dh,
+                      float* dWo, float* dbo, int B, int L, int C, int V, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && V > 0, PB_ERR_SHAPE, "token_head_bwd: bad shape");
+    const size_t smem = ((size_t)B * (C + 1) + (size_t)V * (C + 1) + (size_t)B * V + (size_t)V * C + V) * sizeof(float);
+    PB_REQUIRE(smem <= 220 * 1024, PB_ERR_UNSUPPORTED, "token_head_bwd: B*C too large for the on-chip batch softmax (%zu B)", smem);
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(dWo, 0, (size_t)V * C * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dbo, 0, (size_t)V * sizeof(float), st));
+    DISPATCH_DT(dt, {
+        if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(token_head_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        token_head_bwd_kernel<T><<<min(L, 148 * 2), 256, smem, st>>>(dP, p_local, (const T*)h, Wo, grad_scale, (T*)dh, dWo, dbo, B, L, C, V);
+    });
+    pb_count_launch(1);
+    return pb_check_launch("pb_token_head_bwd");
+}
+
+int pb_pretrain_loss(const float* p_local, const float* p_global, const int64_t* y_local, const float* y_global,
+                     const double* w_local, const double* w_global, double* loss, float* dP_local, float* dP_global, int B,
+                     int L, int V, int A, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && V > 0 && A > 0, PB_ERR_SHAPE, "pretrain_loss: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(loss, 0, 3 * sizeof(double), st));
+    const long long n_tok = (long long)B * L, n_ann = (long long)B * A;
+    const int grid = (int)min((long long)ceil_div(n_ann > n_tok ? n_ann : n_tok, 256), 148LL * 8);
+    loss_kernel<<<grid, 256, 0, st>>>(p_local, p_global, y_local, y_global, w_local, w_global, loss, dP_local, dP_global, n_tok,
+                                      V, n_ann);
+    pb_count_launch(1);
+    return pb_check_launch("pb_pretrain_loss");
+}
+
+int pb_sigmoid_bwd(const float* dP, const float* p, const double* grad_scale, float* dZ, long long n, void* stream) {
+    if (n <= 0) return PB_OK;
+    sigmoid_bwd_kernel<<<(int)min((long long)ceil_div(n, 256), 148LL * 8), 256, 0, (cudaStream_t)stream>>>(dP, p, grad_scale, dZ, n);
+    pb_count_launch(1);
+    return pb_check_launch("pb_sigmoid_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,454 @@
+// Local-track operators, exact-arithmetic (fp32 SIMT) engine, templated on the activation storage
+// type.  In PB_BF16 mode the large contractions are taken over by the tcgen05 kernels in tc_*.cu when
+// the shape qualifies (see pb_tc_*); everything here stays as the parity engine and as the engine for
+// shapes the tensor-core tiling does not cover.
+// Reference call sites: modules.py:124-164 (layers), :205-217 (block forward), :49-60,:87-92 (attention).
+#include "gemm_simt.cuh"
+#include "../../include/pb_b200.h"
+#include "tc_api.cuh"
+
+namespace {
+
+#define DISPATCH_DT(dt, ...)                                                   \
+    do {                                                                       \
+        if ((dt) == PB_F32) { using T = float; __VA_ARGS__; }                  \
+        else if ((dt) == PB_BF16) { using T = bf16; __VA_ARGS__; }             \
+        else { pb_set_error("unknown dtype code %d", (dt)); return PB_ERR_UNSUPPORTED; } \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// loaders / epilogues
+// ---------------------------------------------------------------------------------------------
+// im2col view of a channels-last sequence: A(m=(b,l), k=(t,c)) = x[b, l + sign*(t-half)*dil, c] or 0
+template <typename T>
+struct ConvA {
+    static constexpr bool kContig = true;
+    const T* x; int L, C, dil, half, sign;
+    __device__ float operator()(int m, int k, int) const {
+        const int t = k / C, c = k - t * C;
+        const int b = m / L, l = m - b * L;
+        const int l2 = l + sign * (t - half) * dil;
+        return (l2 >= 0 && l2 < L) ? ldf(x, ((size_t)b * L + l2) * C + c) : 0.f;
+    }
+};
+// tap-major weight pack [t][n][kc]: B(k=(t,kc), n)
+template <typename T>
+struct ConvPackB {
+    static constexpr bool kContig = true;
+    const T* w; int C;
+    __device__ float operator()(int k, int n, int) const {
+        const int t = k / C, kc = k - t * C;
+        return ldf(w, ((size_t)t * C + n) * C + kc);
+    }
+};
+template <typename T>
+struct EpBiasStore {
+    const float* bias; T* out; int N;
+    __device__ void operator()(int m, int n, float acc, int, int) const { stf(out, (size_t)m * N + n, acc + bias[n]); }
+};
+// dx = base (+ extra) + acc   or   dx += acc
+template <typename T>
+struct EpDgrad {
+    const T* base; const T* extra; T* out; int N; int accumulate;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        const size_t i = (size_t)m * N + n;
+        float v = accumulate ? ldf(out, i) : ldf(base, i) + (extra ? ldf(extra, i) : 0.f);
+        stf(out, i, v + acc);
+    }
+};
+// wgrad operands for tap z: A(m=co, k=row) = dz[row, co]; B(k=row, n=ci) = x[row shifted by (z-half)*dil, ci]
+template <typename T>
+struct WgradA {
+    static constexpr bool kContig = false;
+    const T* dz; int C;
+    __device__ float operator()(int m, int k, int) const { return ldf(dz, (size_t)k * C + m); }
+};
+template <typename T>
+struct WgradB {
+    static constexpr bool kContig = false;
+    const T* x; int L, C, dil, half;
+    __device__ float operator()(int k, int n, int z) const {
+        const int b = k / L, l = k - b * L;
+        const int l2 = l + (z - half) * dil;
+        return (l2 >= 0 && l2 < L) ? ldf(x, ((size_t)b * L + l2) * C + n) : 0.f;
+    }
+};
+struct EpWgradAtomic {
+    float* dW; int C, ks;
+    __device__ void operator()(int m, int n, float acc, int, int z) const {
+        atomicAdd(&dW[((size_t)m * C + n) * ks + z], acc);
+    }
+};
+struct EpAtomic {
+    float* out; long ld;
+    __device__ void operator()(int m, int n, float acc, int, int) const { atomicAdd(&out[(size_t)m * ld + n], acc); }
+};
+template <typename T>
+struct EpLocalLinear {
+    const float* bias; const T* h; T* z; T* u2; int N;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        const size_t i = (size_t)m * N + n;
+        const float zz = acc + bias[n];
+        stf(z, i, zz);
+        stf(u2, i, ldf(h, i) + gelu_f(rnd(z, zz)));
+    }
+};
+template <typename T>
+struct EpAddStore {
+    const T* base; T* out; int N;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        const size_t i = (size_t)m * N + n;
+        stf(out, i, ldf(base, i) + acc);
+    }
+};
+struct EpPool {
+    float* pool; int L, G;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        atomicAdd(&pool[(size_t)(m / L) * G + n], gelu_f(acc));
+    }
+};
+template <typename T>
+struct EpPoolBwd {
+    const float* dpool; T* dzv; int L, G;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        stf(dzv, (size_t)m * G + n, dpool[(size_t)(m / L) * G + n] * gelu_grad_f(acc));
+    }
+};
+
+template <class AL, class BL, class EP>
+void gemm_auto(AL al, BL bl, EP ep, int M, int N, int K, int nsplit, int zb, cudaStream_t st) {
+    if (N >= 128 && M >= 128) launch_gemm_simt<128, 128, 8, 8, 8>(al, bl, ep, M, N, K, nsplit, zb, st);
+    else launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, ep, M, N, K, nsplit, zb, st);
+    pb_count_launch(1);
+}
+
+// ---------------------------------------------------------------------------------------------
+// elementwise / reduction kernels.  grid = (chunks, B): a CTA never straddles two samples.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void conv_fuse_kernel(const T* __restrict__ x, const T* __restrict__ zn, const T* __restrict__ zw,
+                                 const float* __restrict__ g2l, T* __restrict__ u, double* __restrict__ stats, int L, int C) {
+    __shared__ double red[32];
+    const int b = blockIdx.y;
+    const long long n = (long long)L * C;
+    const long long per = (n + gridDim.x - 1) / gridDim.x;
+    const long long beg = blockIdx.x * per, end = min(n, beg + per);
+    float s = 0.f, q = 0.f;
+    for (long long i = beg + threadIdx.x; i < end; i += blockDim.x) {
+        const size_t gi = (size_t)b * n + i;
+        const int c = (int)(i % C);
+        float v = ldf(x, gi) + gelu_f(ldf(zn, gi));        // summed left to right as modules.py:211
+        v += gelu_f(ldf(zw, gi));
+        v += g2l[(size_t)b * C + c];
+        v = rnd(u, v);
+        stf(u, gi, v);
+        s += v;
+        q += v * v;
+    }
+    const double ds = block_sum((double)s, red), dq = block_sum((double)q, red);
+    if (threadIdx.x == 0) { atomicAdd(&stats[2 * b], ds); atomicAdd(&stats[2 * b + 1], dq); }
+}
+
+template <typename T>
+__global__ void ln_stats_kernel(const T* __restrict__ u, double* __restrict__ stats, int L, int C) {
+    __shared__ double red[32];
+    const int b = blockIdx.y;
+    const long long n = (long long)L * C;
+    const long long per = (n + gridDim.x - 1) / gridDim.x;
+    const long long beg = blockIdx.x * per, end = min(n, beg + per);
+    float s = 0.f, q = 0.f;
+    for (long long i = beg + threadIdx.x; i < end; i += blockDim.x) {
+        const float v = ldf(u, (size_t)b * n + i);
+        s += v;
+        q += v * v;
+    }
+    const double ds = block_sum((double)s, red), dq = block_sum((double)q, red);
+    if (threadIdx.x == 0) { atomicAdd(&stats[2 * b], ds); atomicAdd(&stats[2 * b + 1], dq); }
+}
+
+template <typename T>
+__global__ void ln_apply_kernel(const T* __restrict__ u, const double* __restrict__ stats, const float* __restrict__ gamma,
+                                const float* __restrict__ beta, T* __restrict__ h, int L, int C, float eps) {
+    const int b = blockIdx.y;
+    const long long n = (long long)L * C;
+    const LnStat st = ln_stat(stats, b, (double)n, eps);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const size_t gi = (size_t)b * n + i;
+        stf(h, gi, (ldf(u, gi) - st.mean) * st.rstd * gamma[i] + beta[i]);
+    }
+}
+
+// pass 1 of the joint-LN backward: each thread owns (l,c) positions and walks the batch, so dgamma/dbeta
+// need no atomics; the per-sample sums s1 = sum dy*gamma, s2 = sum dy*gamma*xhat go through shared memory.
+template <typename T>
+__global__ void ln_bwd_pass1_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
+                                    const float* __restrict__ gamma, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                    double* __restrict__ sums, int B, int L, int C, float eps) {
+    extern __shared__ float sm[];            // [B][2] partial sums + [B][2] mean/rstd
+    float* part = sm;
+    float* mr = sm + 2 * B;
+    const long long n = (long long)L * C;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        const LnStat st = ln_stat(stats, b, (double)n, eps);
+        mr[2 * b] = st.mean; mr[2 * b + 1] = st.rstd;
+        part[2 * b] = 0.f; part[2 * b + 1] = 0.f;
+    }
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < n;
+    const float g = live ? gamma[i] : 0.f;
+    float dg = 0.f, db = 0.f;
+    for (int b = 0; b < B; ++b) {
+        float a1 = 0.f, a2 = 0.f;
+        if (live) {
+            const size_t gi = (size_t)b * n + i;
+            const float d = ldf(dy, gi);
+            const float xh = (ldf(u, gi) - mr[2 * b]) * mr[2 * b + 1];
+            dg += d * xh;
+            db += d;
+            a1 = d * g;
+            a2 = a1 * xh;
+        }
+        a1 = warp_sum(a1);
+        a2 = warp_sum(a2);
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&part[2 * b], a1); atomicAdd(&part[2 * b + 1], a2); }
+    }
+    if (live) { dgamma[i] = dg; dbeta[i] = db; }
+    __syncthreads();
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        atomicAdd(&sums[2 * b], (double)part[2 * b]);
+        atomicAdd(&sums[2 * b + 1], (double)part[2 * b + 1]);
+    }
+}
+
+template <typename T>
+__global__ void ln_bwd_pass2_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
+                                    const float* __restrict__ gamma, const double* __restrict__ sums, T* __restrict__ du,
+                                    int L, int C, float eps) {
+    const int b = blockIdx.y;
+    const long long n = (long long)L * C;
+    const LnStat st = ln_stat(stats, b, (double)n, eps);
+    const float m1 = (float)(sums[2 * b] / (double)n), m2 = (float)(sums[2 * b + 1] / (double)n);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const size_t gi = (size_t)b * n + i;
+        const float xh = (ldf(u, gi) - st.mean) * st.rstd;
+        stf(du, gi, st.rstd * (ldf(dy, gi) * gamma[i] - m1 - xh * m2));
+    }
+}
+
+// dz = dy * gelu'(z) for up to two (z, dz) pairs; column sums of dy per sample (-> dsample[b,c]) and of
+// each dz over all rows (-> dbias[c]).  block = (32, 8): x walks channels, y walks rows; grid = (chunks, B).
+template <typename T>
+__global__ void gelu_bwd_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ z0, const T* __restrict__ z1,
+                                       T* __restrict__ dz0, T* __restrict__ dz1, float* __restrict__ dsample,
+                                       float* __restrict__ db0, float* __restrict__ db1, int L, int C) {
+    extern __shared__ float sm[];            // [3][C]
+    const int b = blockIdx.y;
+    const int rows_per = (L + gridDim.x - 1) / gridDim.x;
+    const int l0 = blockIdx.x * rows_per, l1 = min(L, l0 + rows_per);
+    for (int i = threadIdx.y * 32 + threadIdx.x; i < 3 * C; i += 256) sm[i] = 0.f;
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 32) {
+        float sy = 0.f, s0 = 0.f, s1 = 0.f;
+        for (int l = l0 + threadIdx.y; l < l1; l += 8) {
+            const size_t gi = ((size_t)b * L + l) * C + c;
+            const float d = ldf(dy, gi);
+            sy += d;
+            const float g0 = d * gelu_grad_f(ldf(z0, gi));
+            stf(dz0, gi, g0);
+            s0 += rnd(dz0, g0);
+            if (z1) {
+                const float g1 = d * gelu_grad_f(ldf(z1, gi));
+                stf(dz1, gi, g1);
+                s1 += rnd(dz1, g1);
+            }
+        }
+        atomicAdd(&sm[c], sy);
+        atomicAdd(&sm[C + c], s0);
+        atomicAdd(&sm[2 * C + c], s1);
+    }
+    __syncthreads();
+    for (int c = threadIdx.y * 32 + threadIdx.x; c < C; c += 256) {
+        if (dsample) atomicAdd(&dsample[(size_t)b * C + c], sm[c]);
+        atomicAdd(&db0[c], sm[C + c]);
+        if (z1) atomicAdd(&db1[c], sm[2 * C + c]);
+    }
+}
+
+int split_for(int tiles, long K) {
+    int s = 592 / (tiles > 0 ? tiles : 1);
+    if (s < 1) s = 1;
+    while (s > 1 && K / s < 256) --s;
+    return s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pb_ln_joint_stats(const void* u, double* stats, int B, int L, int C, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "ln_joint_stats: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(stats, 0, (size_t)B * 2 * sizeof(double), st));
+    dim3 grid(max(1, min(ceil_div((long)L * C, 4096), 16)), B);
+    DISPATCH_DT(dt, (ln_stats_kernel<T><<<grid, 256, 0, st>>>((const T*)u, stats, L, C)));
+    pb_count_launch(1);
+    return pb_check_launch("pb_ln_joint_stats");
+}
+
+int pb_ln_joint_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
+                      float eps, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "ln_joint_apply: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dt == PB_BF16 && pb_tc_ln_apply_ok(L, C)) return pb_tc_ln_apply(u, stats, gamma, beta, h, B, L, C, eps, st);
+    dim3 grid(max(1, min(ceil_div((long)L * C, 1024), 32)), B);
+    DISPATCH_DT(dt, (ln_apply_kernel<T><<<grid, 256, 0, st>>>((const T*)u, stats, gamma, beta, (T*)h, L, C, eps)));
+    pb_count_launch(1);
+    return pb_check_launch("pb_ln_joint_apply");
+}
+
+int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const float* gamma, void* du, float* dgamma,
+                    float* dbeta, double* sums, int B, int L, int C, float eps, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "ln_joint_bwd: bad shape");
+    PB_REQUIRE(B <= 4096, PB_ERR_SHAPE, "ln_joint_bwd: batch %d exceeds the 4096 supported per call", B);
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(sums, 0, (size_t)B * 2 * sizeof(double), st));
+    const long long n = (long long)L * C;
+    DISPATCH_DT(dt, (ln_bwd_pass1_kernel<T><<<ceil_div(n, 128), 128, 4 * B * sizeof(float), st>>>(
+                        (const T*)dy, (const T*)u, stats, gamma, dgamma, dbeta, sums, B, L, C, eps)));
+    dim3 grid(max(1, min(ceil_div(n, 1024), 32)), B);
+    DISPATCH_DT(dt, (ln_bwd_pass2_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)u, stats, gamma, sums, (T*)du, L, C, eps)));
+    pb_count_launch(2);
+    return pb_check_launch("pb_ln_joint_bwd");
+}
+
+int pb_conv_pair_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l,
+                     void* zn, void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, int dt,
+                     void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && ksize > 0 && (ksize & 1) && dil > 0, PB_ERR_SHAPE,
+               "conv_pair_fwd: bad shape B=%d L=%d C=%d k=%d dil=%d (odd kernel sizes only: 'same' padding)", B, L, C,
+               ksize, dil);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dt == PB_BF16 && pb_tc_conv_ok(B, L, C, ksize, dil))
+        return pb_tc_conv_pair_fwd(x, wn, ww, bn, bw, g2l, zn, zw, u, stats, B, L, C, ksize, dil, st);
+    const int M = B * L, K = ksize * C, half = ksize / 2;
+    DISPATCH_DT(dt, {
+        gemm_auto(ConvA<T>{(const T*)x, L, C, 1, half, 1}, ConvPackB<T>{(const T*)wn, C}, EpBiasStore<T>{bn, (T*)zn, C}, M, C, K, 1, 1, st);
+        gemm_auto(ConvA<T>{(const T*)x, L, C, dil, half, 1}, ConvPackB<T>{(const T*)ww, C}, EpBiasStore<T>{bw, (T*)zw, C}, M, C, K, 1, 1, st);
+        dim3 grid(max(1, min(ceil_div((long)L * C, 4096), 16)), B);
+        conv_fuse_kernel<T><<<grid, 256, 0, st>>>((const T*)x, (const T*)zn, (const T*)zw, g2l, (T*)u, stats, L, C);
+        pb_count_launch(1);
+    });
+    return pb_check_launch("pb_conv_pair_fwd");
+}
+
+int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void* x, const void* wn_bwd, const void* ww_bwd,
+                     void* dzn, void* dzw, void* dx, float* dWn, float* dWw, float* dbn, float* dbw, float* dg2l, int B,
+                     int L, int C, int ksize, int dil, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && ksize > 0 && (ksize & 1) && dil > 0, PB_ERR_SHAPE, "conv_pair_bwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = B * L, K = ksize * C, half = ksize / 2;
+    PB_CUDA(cudaMemsetAsync(dbn, 0, C * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dbw, 0, C * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dg2l, 0, (size_t)B * C * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dWn, 0, (size_t)C * C * ksize * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
+    const bool tc = dt == PB_BF16 && pb_tc_conv_ok(B, L, C, ksize, dil);
+    DISPATCH_DT(dt, {
+        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
+        gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
+            (const T*)du, (const T*)zn, (const T*)zw, (T*)dzn, (T*)dzw, dg2l, dbn, dbw, L, C);
+        pb_count_launch(1);
+        if (tc) {
+            int rc = pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st);
+            if (rc) return rc;
+            rc = pb_tc_conv_wgrad(dzn, dzw, x, dWn, dWw, B, L, C, ksize, dil, st);
+            if (rc) return rc;
+        } else {
+            // data gradient: same implicit GEMM with the taps mirrored (sign = -1) and the [t][ci][co] pack
+            gemm_auto(ConvA<T>{(const T*)dzn, L, C, 1, half, -1}, ConvPackB<T>{(const T*)wn_bwd, C},
+                      EpDgrad<T>{(const T*)du, nullptr, (T*)dx, C, 0}, M, C, K, 1, 1, st);
+            gemm_auto(ConvA<T>{(const T*)dzw, L, C, dil, half, -1}, ConvPackB<T>{(const T*)ww_bwd, C},
+                      EpDgrad<T>{nullptr, nullptr, (T*)dx, C, 1}, M, C, K, 1, 1, st);
+            // weight gradient: one [C x C] GEMM per tap, contraction over all B*L rows, split-K with atomics
+            const int tiles = ceil_div(C, C >= 128 ? 128 : 64) * ceil_div(C, C >= 128 ? 128 : 64) * ksize;
+            const int ns = split_for(tiles, M);
+            gemm_auto(WgradA<T>{(const T*)dzn, C}, WgradB<T>{(const T*)x, L, C, 1, half}, EpWgradAtomic{dWn, C, ksize}, C, C, M, ns, ksize, st);
+            gemm_auto(WgradA<T>{(const T*)dzw, C}, WgradB<T>{(const T*)x, L, C, dil, half}, EpWgradAtomic{dWw, C, ksize}, C, C, M, ns, ksize, st);
+        }
+    });
+    return pb_check_launch("pb_conv_pair_bwd");
+}
+
+int pb_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L, int C,
+                        int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "local_linear_fwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dt == PB_BF16 && pb_tc_linear_ok(B, L, C))
+        return pb_tc_local_linear_fwd(h, W, bias, z, u2, stats2, B, L, C, st);
+    const int M = B * L;
+    DISPATCH_DT(dt, {
+        gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)W, C}, EpLocalLinear<T>{bias, (const T*)h, (T*)z, (T*)u2, C}, M, C, C, 1, 1, st);
+        dim3 grid(max(1, min(ceil_div((long)L * C, 4096), 16)), B);
+        ln_stats_kernel<T><<<grid, 256, 0, st>>>((const T*)u2, stats2, L, C);
+        pb_count_launch(1);
+    });
+    return pb_check_launch("pb_local_linear_fwd");
+}
+
+int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const void* W, void* dz, void* dh, float* dW, float* db,
+                        int B, int L, int C, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "local_linear_bwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = B * L;
+    PB_CUDA(cudaMemsetAsync(db, 0, C * sizeof(float), st));
+    PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
+    const bool tc = dt == PB_BF16 && pb_tc_linear_ok(B, L, C);
+    DISPATCH_DT(dt, {
+        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
+        gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
+            (const T*)du2, (const T*)z, (const T*)nullptr, (T*)dz, (T*)nullptr, (float*)nullptr, db, (float*)nullptr, L, C);
+        pb_count_launch(1);
+        if (tc) {
+            int rc = pb_tc_local_linear_bwd(du2, dz, h, W, dh, dW, B, L, C, st);
+            if (rc) return rc;
+        } else {
+            // dh = du2 + dz W
+            gemm_auto(RowMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)W, C}, EpAddStore<T>{(const T*)du2, (T*)dh, C}, M, C, C, 1, 1, st);
+            // dW[n,c] = sum_rows dz[row,n] h[row,c]
+            const int tiles = ceil_div(C, C >= 128 ? 128 : 64) * ceil_div(C, C >= 128 ? 128 : 64);
+            gemm_auto(ColMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)h, C}, EpAtomic{dW, C}, C, C, M, split_for(tiles, M), 1, st);
+        }
+    });
+    return pb_check_launch("pb_local_linear_bwd");
+}
+
+int pb_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_fwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    PB_CUDA(cudaMemsetAsync(pool, 0, (size_t)B * G * sizeof(float), st));
+    if (dt == PB_BF16 && pb_tc_attn_ok(B, L, C, G)) return pb_tc_attn_pool_fwd(h, wvT, pool, B, L, C, G, st);
+    DISPATCH_DT(dt, gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPool{pool, L, G}, B * L, G, C, 1, 1, st));
+    return pb_check_launch("pb_attn_pool_fwd");
+}
+
+int pb_attn_pool_bwd(const void* h, const void* wvT, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
+                     float* dWvT, int B, int L, int C, int G, int dt, void* stream) {
+    PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_bwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int M = B * L;
+    if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
+    if (dt == PB_BF16 && pb_tc_attn_ok(B, L, C, G))
+        return pb_tc_attn_pool_bwd(h, wvT, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, st);
+    DISPATCH_DT(dt, {
+        gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
+        gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);
+        if (dWvT) {
+            const int tiles = ceil_div(G, 128) * ceil_div(C, 128);
+            gemm_auto(ColMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)h, C}, EpAtomic{dWvT, C}, G, C, M, split_for(tiles, M), 1, st);
+        }
+    });
+    return pb_check_launch("pb_attn_pool_bwd");
+}
+
+}  // extern "C"

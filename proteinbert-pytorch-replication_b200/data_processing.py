@@ -1,0 +1,153 @@
+"""Host side of the input corruption / padding path (reference: ProteinBERT/data_processing.py:30-183,337-348).
+
+The reference builds every sample in Python on the CPU (tokenise -> <sos>/<eos> -> random crop -> 5 % token
+randomisation -> right-pad; annotation noising; weights).  Here the host only makes the RANDOM DRAWS -- with
+the same torch CPU RNG calls, shapes and order as the reference, so the same seed gives the same draws -- and
+packs the raw bytes; all integer work then runs in one CUDA kernel (``pb_corrupt_pad``) that is bit-exact
+with the reference given those draws.
+
+    ds     = UniRefGO_PretrainingDataset(df, seq_max_length=512)       # same constructor as the reference
+    loader = DataLoader(ds, batch_size=64, collate_fn=ds.collate)      # the collate runs the kernel
+    for X, Y, W in loader: ...                                         # dicts of device tensors
+
+There is no torchtext dependency (the reference's is un-vendored, unpinned and end-of-life).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence
+
+import numpy as np
+import torch
+
+from ._lib import check, lib
+
+ALL_AMINO_ACIDS = "ACDEFGHIKLMNPQRSTUVWXY"          # data_processing.py:338
+SPECIAL_TOKENS = ["<pad>", "<sos>", "<eos>", "<unk>"]  # :339
+
+
+class AminoAcidVocab:
+    """What ``create_amino_acid_vocab()`` returns in the reference, minus torchtext: specials first, then the
+    22 residue letters; unknown tokens map to ``<unk>`` (data_processing.py:337-348)."""
+
+    def __init__(self):
+        self._itos = SPECIAL_TOKENS + list(ALL_AMINO_ACIDS)
+        self._stoi = {s: i for i, s in enumerate(self._itos)}
+        self._default = self._stoi["<unk>"]
+
+    def __getitem__(self, token: str) -> int:
+        return self._stoi.get(token, self._default)
+
+    def __len__(self) -> int:
+        return len(self._itos)
+
+    def get_itos(self) -> List[str]:
+        return list(self._itos)
+
+
+def create_amino_acid_vocab() -> AminoAcidVocab:
+    return AminoAcidVocab()
+
+
+def draw_sample(n_residues: int, num_annotations: int, max_length: int, p: float = .05,
+                positive_p: float = 0.25, negative_p: float = 0.0001) -> Dict[str, object]:
+    """The random draws ``UniRefGO_PretrainingDataset.__getitem__`` makes for one sample, in its order
+    (crop randint -> token multinomial -> replacement randint -> coin rand -> keep/add multinomials;
+    data_processing.py:78-83,100-105,125-142) on the torch CPU generator."""
+    n_ids = n_residues + 2
+    crop = -1
+    if n_ids > max_length:
+        crop = int(torch.randint(0, n_ids - max_length, (1,))[0])
+    n = min(n_ids, max_length)
+    tok_mask = torch.multinomial(torch.tensor([1 - p, p], dtype=torch.float), num_samples=n, replacement=True)
+    tok_rand = torch.randint(3, 4 + len(ALL_AMINO_ACIDS), (n,))
+    coin = float(torch.rand(1)[0])
+    if coin > 0.5:
+        keep = torch.multinomial(torch.tensor([positive_p, 1 - positive_p], dtype=torch.float),
+                                 num_samples=num_annotations, replacement=True)
+        add = torch.multinomial(torch.tensor([1 - negative_p, negative_p], dtype=torch.float),
+                                num_samples=num_annotations, replacement=True)
+    else:
+        keep = add = None
+    return {"crop_start": crop, "tok_mask": tok_mask, "tok_rand": tok_rand, "coin": coin, "keep": keep, "add": add}
+
+
+def pack_batch(seqs: Sequence[str], anns, draws: Sequence[Dict[str, object]], max_length: int, pin: bool = True):
+    """Ragged python samples + their draws -> flat host tensors in the layout ``pb_corrupt_pad`` reads."""
+    B = len(seqs)
+    A = len(anns[0])
+    raw = [s.encode("latin-1", errors="replace") for s in seqs]
+    seq_off = np.zeros(B + 1, dtype=np.int64)
+    seq_off[1:] = np.cumsum([len(r) for r in raw])
+    seq_bytes = np.frombuffer(b"".join(raw) or b"\0", dtype=np.uint8).copy()
+    n_draw = [min(len(r) + 2, max_length) for r in raw]
+    draw_off = np.zeros(B + 1, dtype=np.int64)
+    draw_off[1:] = np.cumsum(n_draw)
+    tok_mask = np.concatenate([np.asarray(d["tok_mask"], dtype=np.int64)[:n] for d, n in zip(draws, n_draw)]).astype(np.uint8)
+    tok_rand = np.concatenate([np.asarray(d["tok_rand"], dtype=np.int64)[:n] for d, n in zip(draws, n_draw)]).astype(np.uint8)
+    crop = np.asarray([max(int(d["crop_start"]), 0) for d in draws], dtype=np.int64)
+    coin = np.asarray([d["coin"] for d in draws], dtype=np.float32)
+    keep = np.zeros((B, A), dtype=np.uint8)
+    add = np.zeros((B, A), dtype=np.uint8)
+    for i, d in enumerate(draws):
+        if d["keep"] is not None:
+            keep[i] = np.asarray(d["keep"], dtype=np.int64)
+            add[i] = np.asarray(d["add"], dtype=np.int64)
+    ann = np.asarray(anns, dtype=np.int64)
+    if ann.min(initial=0) < 0 or ann.max(initial=0) > 255:
+        raise ValueError("annotation values must fit in a byte (the reference uses 0/1 masks)")
+    packed = {"seq_bytes": seq_bytes, "seq_off": seq_off, "crop_start": crop, "tok_mask": tok_mask, "tok_rand": tok_rand,
+              "draw_off": draw_off, "coin": coin, "keep": keep, "add": add, "ann": ann.astype(np.uint8)}
+    out = {}
+    for k, v in packed.items():
+        t = torch.from_numpy(np.ascontiguousarray(v))
+        out[k] = t.pin_memory() if (pin and torch.cuda.is_available()) else t
+    out["B"], out["L"], out["A"] = B, max_length, A
+    return out
+
+
+def corrupt_pad(packed, device="cuda"):
+    """Run the corruption/padding kernel.  Returns (X, Y, W) dicts of device tensors with the reference's
+    shapes and dtypes: local int64 [B,L] / global float32 [B,A]; weights float64."""
+    B, L, A = packed["B"], packed["L"], packed["A"]
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("corrupt_pad runs on a CUDA device only (no CPU fallback)")
+    d = {k: v.to(dev, non_blocking=True) for k, v in packed.items() if isinstance(v, torch.Tensor)}
+    x_local = torch.empty((B, L), dtype=torch.int64, device=dev)
+    y_local = torch.empty((B, L), dtype=torch.int64, device=dev)
+    w_local = torch.empty((B, L), dtype=torch.float64, device=dev)
+    x_global = torch.empty((B, A), dtype=torch.float32, device=dev)
+    y_global = torch.empty((B, A), dtype=torch.float32, device=dev)
+    w_global = torch.empty((B, A), dtype=torch.float64, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    check(lib().pb_corrupt_pad(d["seq_bytes"].data_ptr(), d["seq_off"].data_ptr(), d["crop_start"].data_ptr(),
+                               d["tok_mask"].data_ptr(), d["tok_rand"].data_ptr(), d["draw_off"].data_ptr(),
+                               d["coin"].data_ptr(), d["keep"].data_ptr(), d["add"].data_ptr(), d["ann"].data_ptr(),
+                               x_local.data_ptr(), y_local.data_ptr(), w_local.data_ptr(), x_global.data_ptr(),
+                               y_global.data_ptr(), w_global.data_ptr(), B, L, A, st), "pb_corrupt_pad")
+    return ({"local": x_local, "global": x_global}, {"local": y_local, "global": y_global},
+            {"local": w_local, "global": w_global})
+
+
+class UniRefGO_PretrainingDataset(torch.utils.data.Dataset):
+    """Same constructor and length as the reference dataset (data_processing.py:146-183).  ``__getitem__``
+    returns the raw sample plus its random draws; ``collate`` turns a list of them into the (X, Y, W) batch on
+    the GPU.  Iterating with the same seed visits the RNG exactly as the reference does."""
+
+    def __init__(self, df, seq_max_length=128, device="cuda"):
+        self.df = df
+        self.vocab = create_amino_acid_vocab()
+        self.seq_max_length = seq_max_length
+        self.device = device
+
+    def __getitem__(self, index):
+        seq = self.df.iloc[index, 0]
+        ann = self.df.iloc[index, 1]
+        return seq, ann, draw_sample(len(seq), len(ann), self.seq_max_length)
+
+    def __len__(self):
+        return len(self.df.index)
+
+    def collate(self, samples):
+        seqs, anns, draws = zip(*samples)
+        return corrupt_pad(pack_batch(seqs, anns, draws, self.seq_max_length), self.device)

@@ -1,0 +1,207 @@
+"""Drop-in replacements for the four nn.Modules of the reference ``ProteinBERT/modules.py``.
+
+Same class names, constructor signatures, dict-in/dict-out forwards, attribute names and ``state_dict``
+keys (133 tensors at the default configuration); sub-modules are created in the reference's order, so the
+same ``torch.manual_seed`` yields the same initial weights.  The arithmetic is done by the sm_100a kernels
+of libpb_b200.so (see ops.py); the ``nn.Conv1d`` / ``nn.Linear`` / ``nn.LayerNorm`` objects below are only
+parameter containers -- their own ``forward`` is never called.
+
+Reference behaviours that are reproduced on purpose:
+  * the attention heads live in a plain python list, so their tensors are NOT registered (modules.py:73-81);
+  * ``Softmax(dim=1)`` in the head normalises over the repeated-query axis, which makes the layer
+    ``(sum(W_parameter)/key_dim) * sum_l gelu(x_l Wv)`` (modules.py:34,51-60,92);
+  * the token head's ``nn.Softmax()`` acts on the batch axis (modules.py:283).
+
+One extra, optional constructor keyword: ``precision`` = "fp32" (default; fp32 storage and fp32 arithmetic,
+matches the reference to ~1e-5) or "bf16" (bf16 activations, tcgen05 tensor-core contractions with fp32
+accumulation, fp32/fp64 statistics).
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from ._lib import ACT_GELU, ACT_SIGMOID, BF16, F32
+
+_DEFAULT_DEVICE = ('cuda' if torch.cuda.is_available() else 'cpu')
+_DEFAULT_PRECISION = os.environ.get("PB_B200_PRECISION", "fp32")
+
+
+def _dt(precision: str) -> int:
+    if precision == "fp32":
+        return F32
+    if precision == "bf16":
+        return BF16
+    raise ValueError(f"precision must be 'fp32' or 'bf16', got {precision!r}")
+
+
+class GlobalAttentionHead(nn.Module):
+    """reference: modules.py:21-60."""
+
+    def __init__(self, local_dim: int, global_dim: int, value_dim: int, key_dim: int,
+                 device: torch.device = _DEFAULT_DEVICE):
+        super().__init__()
+        self.key_dim = key_dim
+        self.global_dim = global_dim
+        self.gelu = nn.GELU()
+        self.tanh = nn.Tanh()
+        self.softmax = nn.Softmax(dim=1)
+        self.Wv_parameter = nn.Parameter(data=torch.randn(local_dim, value_dim, device=device), requires_grad=True)
+        self.Wk_parameter = nn.Parameter(data=torch.randn(local_dim, key_dim, device=device), requires_grad=True)
+        self.Wq_parameter = nn.Parameter(data=torch.randn(global_dim, key_dim, device=device), requires_grad=True)
+
+    def forward(self, x):
+        """{"local": [B,L,C], "global": [B,G]} -> [B, key_dim, value_dim].  Every one of the key_dim rows is
+        (1/key_dim) * sum_l gelu(x_l Wv): the K query rows are identical copies of the global vector, and the
+        softmax runs over that axis (modules.py:51-60), so Wq / Wk cancel out of the result exactly."""
+        pool = ops.AttnPoolFn.apply(x["local"], self.Wv_parameter.t())          # [B, Dv]
+        return (pool / self.key_dim).unsqueeze(1).expand(-1, self.key_dim, -1)
+
+
+class GlobalAttention(nn.Module):
+    """reference: modules.py:63-92."""
+
+    def __init__(self, num_heads: int, local_dim: int, global_dim: int, value_dim: int, key_dim: int,
+                 device: torch.device = _DEFAULT_DEVICE):
+        super().__init__()
+        # a plain list, exactly like the reference: the head tensors are not registered parameters
+        self.global_attention_heads = [
+            GlobalAttentionHead(local_dim=local_dim, global_dim=global_dim, value_dim=value_dim, key_dim=key_dim,
+                                device=device) for _ in range(num_heads)
+        ]
+        self.W_parameter = nn.Parameter(data=torch.randn(key_dim, device=device), requires_grad=True)
+
+    def wv_all_t(self) -> torch.Tensor:
+        """cat_heads(Wv)^T, [G, C] (autograd routes the gradient back to each head's Wv_parameter)."""
+        return torch.cat([h.Wv_parameter for h in self.global_attention_heads], dim=1).t()
+
+    def forward(self, x):
+        pool = ops.AttnPoolFn.apply(x["local"], self.wv_all_t())
+        return pool * (self.W_parameter.sum() / self.W_parameter.numel())
+
+
+class ProteinBERTBlock(nn.Module):
+    """reference: modules.py:95-231."""
+
+    def __init__(self, sequences_length, local_dim: int, global_dim: int, num_heads: int, key_dim: int,
+                 conv_kernel_size: int = 9, wide_conv_dilation: int = 5, device: torch.device = _DEFAULT_DEVICE,
+                 precision: str = _DEFAULT_PRECISION):
+        super().__init__()
+        assert global_dim % num_heads == 0, \
+            f"Global_dim must be divisible by num_heads. Global_dim: {global_dim}. Num_heads: {num_heads}"
+        self.sequences_length = sequences_length
+        self.local_dim = local_dim
+        self.conv_kernel_size = conv_kernel_size
+        self.wide_conv_dilation = wide_conv_dilation
+        self.precision = precision
+        self.head_grads = True          # the reference's autograd also fills the (unregistered) heads' .grad
+
+        self.global_attention_layer = GlobalAttention(num_heads=num_heads, local_dim=local_dim, global_dim=global_dim,
+                                                      value_dim=int(global_dim / num_heads), key_dim=key_dim, device=device)
+        self.local_narrow_conv_layer = nn.Sequential(
+            nn.Conv1d(local_dim, local_dim, kernel_size=conv_kernel_size, stride=1, dilation=1, padding="same", device=device),
+            nn.GELU())
+        self.local_wide_conv_layer = nn.Sequential(
+            nn.Conv1d(local_dim, local_dim, kernel_size=conv_kernel_size, stride=1, dilation=wide_conv_dilation,
+                      padding="same", device=device),
+            nn.GELU())
+        self.local_norm_1 = nn.LayerNorm(normalized_shape=(sequences_length, local_dim), device=device)
+        self.local_linear_layer = nn.Sequential(nn.Linear(local_dim, local_dim, device=device), nn.GELU())
+        self.local_norm_2 = nn.LayerNorm(normalized_shape=(sequences_length, local_dim), device=device)
+        self.global_to_local_linear_layer = nn.Sequential(nn.Linear(global_dim, local_dim, device=device), nn.GELU())
+        self.global_linear_layer_1 = nn.Sequential(nn.Linear(global_dim, global_dim, device=device), nn.GELU())
+        self.global_norm_1 = nn.LayerNorm(normalized_shape=global_dim, device=device)
+        self.global_linear_layer_2 = nn.Sequential(nn.Linear(global_dim, global_dim, device=device), nn.GELU())
+        self.global_norm_2 = nn.LayerNorm(normalized_shape=global_dim, device=device)
+
+    def forward_channels_last(self, xl: torch.Tensor, g: torch.Tensor):
+        """xl [B,L,C] in the activation dtype, g [B,G] float -> (h [B,L,C], g_out [B,G])."""
+        if xl.shape[1] != self.sequences_length:
+            raise ValueError(f"sequence length {xl.shape[1]} != sequences_length {self.sequences_length} "
+                             "(the (L,C) LayerNorm fixes it, modules.py:148-151)")
+        nconv, wconv = self.local_narrow_conv_layer[0], self.local_wide_conv_layer[0]
+        lin = self.local_linear_layer[0]
+        att = self.global_attention_layer
+        g2l_lin = self.global_to_local_linear_layer[0]
+        g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                        # modules.py:208
+        h, pool = ops.LocalTrackFn.apply(                                                      # :205-219
+            xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
+            self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
+            self.local_norm_2.weight, self.local_norm_2.bias, att.wv_all_t(),
+            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads)
+        gl1, gl2 = self.global_linear_layer_1[0], self.global_linear_layer_2[0]
+        gh = ops.linear_act(g, gl1.weight, gl1.bias, ACT_GELU)                                  # :221
+        g1 = ops.ResLnRowsFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224
+        gh2 = ops.linear_act(g1, gl2.weight, gl2.bias, ACT_GELU)                                # :226
+        g2 = ops.ResLnRowsFn.apply(g1, gh2, None, None, self.global_norm_2.weight, self.global_norm_2.bias)           # :228-229
+        return h, g2
+
+    def forward(self, x):
+        adt = ops.act_dtype(_dt(self.precision))
+        xl = x["local"].permute(0, 2, 1)              # reference block I/O is channels-first [B,C,L]
+        if xl.dtype != adt:
+            xl = xl.to(adt)
+        h, g = self.forward_channels_last(xl, x["global"].float())
+        return {"local": h.permute(0, 2, 1), "global": g}
+
+
+class ProteinBERT(nn.Module):
+    """reference: modules.py:234-304."""
+
+    def __init__(self, sequences_length: int, num_annotations: int, local_dim: int, global_dim: int, key_dim: int,
+                 num_heads: int, num_blocks: int, conv_kernel_size: int = 9, wide_conv_dilation: int = 5,
+                 vocab_size: int = 26, device: torch.device = _DEFAULT_DEVICE, precision: str = _DEFAULT_PRECISION):
+        super().__init__()
+        _dt(precision)
+        self.precision = precision
+        self.local_embedding = nn.Embedding(num_embeddings=vocab_size, embedding_dim=local_dim, device=device)
+        self.global_linear_layer = nn.Sequential(nn.Linear(num_annotations, global_dim, device=device), nn.GELU())
+        self.proteinBERT_blocks = nn.Sequential(*[
+            ProteinBERTBlock(sequences_length=sequences_length, global_dim=global_dim, local_dim=local_dim,
+                             key_dim=key_dim, num_heads=num_heads, conv_kernel_size=conv_kernel_size,
+                             wide_conv_dilation=wide_conv_dilation, device=device, precision=precision)
+            for _ in range(num_blocks)
+        ])
+        self.pretraining_local_output = nn.Sequential(nn.Linear(local_dim, vocab_size, device=device), nn.Softmax())
+        self.pretraining_global_output = nn.Sequential(nn.Linear(global_dim, num_annotations, device=device), nn.Sigmoid())
+
+    def set_precision(self, precision: str):
+        _dt(precision)
+        self.precision = precision
+        for blk in self.proteinBERT_blocks:
+            blk.precision = precision
+        return self
+
+    def set_head_grads(self, flag: bool):
+        """Whether backward also produces .grad for the unregistered attention-head tensors (the reference
+        does; no optimizer ever reads them).  True by default."""
+        for blk in self.proteinBERT_blocks:
+            blk.head_grads = bool(flag)
+        return self
+
+    def head_tensors(self):
+        """The unregistered Wq/Wk/Wv tensors, keyed like oracle/model_oracle.py."""
+        out = {}
+        for i, blk in enumerate(self.proteinBERT_blocks):
+            for h, head in enumerate(blk.global_attention_layer.global_attention_heads):
+                for n in ("Wq", "Wk", "Wv"):
+                    out[f"proteinBERT_blocks.{i}.global_attention_layer.global_attention_heads.{h}.{n}_parameter"] = \
+                        getattr(head, f"{n}_parameter")
+        return out
+
+    def forward(self, x):
+        """{"local": int64 [B,L], "global": float [B,A]} -> (token probs [B,L,V], annotation probs [B,A])."""
+        dt = _dt(self.precision)
+        x_local, x_global = x["local"], x["global"]
+        h = ops.EmbeddingFn.apply(x_local, self.local_embedding.weight, dt)                     # modules.py:300
+        gin = self.global_linear_layer[0]
+        g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU)                    # :301
+        for blk in self.proteinBERT_blocks:
+            h, g = blk.forward_channels_last(h, g)
+        lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
+        p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284
+        p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID)                           # :286-293
+        return p_local, p_global

@@ -1,0 +1,373 @@
+"""torch.autograd bindings of the C-ABI kernels.
+
+PyTorch is plumbing here: it owns device memory (caching allocator), the current stream and the autograd
+graph; every forward/backward below is one or more calls into libpb_b200.so with raw device pointers.
+There is no eager fallback -- tensors that are not on a CUDA device are refused.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import ACT_GELU, ACT_NONE, ACT_SIGMOID, BF16, F32, check, lib
+
+LN_EPS = 1e-5
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+PROFILE = None      # bench.py: {"pb_<op>": []} -> (start, end) CUDA event pairs around that op's launches
+
+
+def _call(name, *args):
+    """One C-ABI call: raises PBError on a non-zero status; optionally bracketed by CUDA events."""
+    fn = getattr(lib(), name)
+    if PROFILE is not None and name in PROFILE:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = fn(*args)
+        b.record()
+        PROFILE[name].append((a, b))
+    else:
+        rc = fn(*args)
+    check(rc, name)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.PBError("proteinbert_b200 ops run on a CUDA device (sm_100a) only; got a CPU tensor. "
+                               "There is no CPU fallback.")
+
+
+def act_dtype(dt: int):
+    return torch.bfloat16 if dt == BF16 else torch.float32
+
+
+def dt_of(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return BF16
+    if t.dtype == torch.float32:
+        return F32
+    raise _lib.PBError(f"unsupported activation dtype {t.dtype}")
+
+
+_WS = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    """Per-(device, stream) split-K scratch, grown on demand (kernels never allocate)."""
+    key = (device, _st())
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+def to_wt(w: torch.Tensor, dt: int) -> torch.Tensor:
+    """fp32 master weight -> the storage type the big contractions read (`wt` in pb_b200.h)."""
+    w = w.contiguous()
+    if dt == F32:
+        return w
+    out = torch.empty(w.shape, dtype=torch.bfloat16, device=w.device)
+    _call("pb_cast_f32_to_bf16", _p(w), _p(out), w.numel(), _st())
+    return out
+
+
+def conv_pack(w: torch.Tensor, dt: int):
+    """[Co,Ci,k] -> ([k,Co,Ci], [k,Ci,Co]) in the `wt` type."""
+    Co, Ci, k = w.shape
+    w = w.contiguous()
+    fwd = torch.empty((k, Co, Ci), dtype=act_dtype(dt), device=w.device)
+    bwd = torch.empty((k, Ci, Co), dtype=act_dtype(dt), device=w.device)
+    _call("pb_conv_weight_pack", _p(w), _p(fwd), _p(bwd), Co, k, dt, _st())
+    return fwd, bwd
+
+
+# ------------------------------------------------------------------------------------------------
+class EmbeddingFn(torch.autograd.Function):
+    """nn.Embedding forward / embedding_dense_backward (modules.py:249-253,300)."""
+
+    @staticmethod
+    def forward(ctx, tok, table, dt):
+        _need_cuda(tok, table)
+        tok = tok.contiguous()
+        B, L = tok.shape
+        V, C = table.shape
+        out = torch.empty((B, L, C), dtype=act_dtype(dt), device=table.device)
+        _call("pb_embedding_fwd", _p(tok), _p(table.contiguous()), _p(out), B * L, C, V, dt, _st())
+        ctx.save_for_backward(tok)
+        ctx.shape = (V, C, dt)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (tok,) = ctx.saved_tensors
+        V, C, dt = ctx.shape
+        dout = dout.contiguous()
+        dtable = torch.empty((V, C), dtype=torch.float32, device=dout.device)
+        _call("pb_embedding_bwd", _p(tok), _p(dout), _p(dtable), tok.numel(), C, V, dt, _st())
+        return None, dtable, None
+
+
+class LinearActFn(torch.autograd.Function):
+    """act(X W^T + b) on the global track, float32 (modules.py:166-199,255-262,286-293)."""
+
+    @staticmethod
+    def forward(ctx, x, W, b, act):
+        _need_cuda(x, W, b)
+        x = x.contiguous().float()
+        W = W.contiguous()
+        M, K = x.shape
+        N = W.shape[0]
+        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        z = torch.empty_like(y) if act == ACT_GELU else None
+        nbytes = lib().pb_workspace_bytes(b"linear_fwd", M, N, K)
+        ws = _workspace(nbytes, x.device)
+        _call("pb_linear_fwd", _p(x), _p(W), _p(b), _p(z), _p(y), M, N, K, act, _p(ws), ws.numel(), _st())
+        ctx.act = act
+        ctx.needs = (ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        ctx.save_for_backward(x, W, z if act == ACT_GELU else (y if act == ACT_SIGMOID else None))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, W, zy = ctx.saved_tensors
+        M, K = x.shape
+        N = W.shape[0]
+        dy = dy.contiguous()
+        need_dx, need_dw = ctx.needs
+        dz = torch.empty((M, N), dtype=torch.float32, device=dy.device)
+        dx = torch.empty((M, K), dtype=torch.float32, device=dy.device) if need_dx else None
+        dW = torch.empty((N, K), dtype=torch.float32, device=dy.device) if need_dw else None
+        db = torch.empty((N,), dtype=torch.float32, device=dy.device)
+        nbytes = lib().pb_workspace_bytes(b"linear_bwd", M, N, K)
+        ws = _workspace(nbytes, dy.device)
+        _call("pb_linear_bwd", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
+                                  _p(ws), ws.numel(), _st())
+        return dx, dW, db, None
+
+
+class ResLnRowsFn(torch.autograd.Function):
+    """LayerNorm_G(a + b + (sum(w_param)/K) * c)  (modules.py:223-229 and the head mix of :87-92)."""
+
+    @staticmethod
+    def forward(ctx, a, b, c, w_param, gamma, beta):
+        _need_cuda(a, gamma)
+        a = a.contiguous()
+        b = None if b is None else b.contiguous()
+        c = None if c is None else c.contiguous()
+        B, G = a.shape
+        K = 0 if w_param is None else w_param.numel()
+        xhat = torch.empty_like(a)
+        rstd = torch.empty((B,), dtype=torch.float32, device=a.device)
+        y = torch.empty_like(a)
+        _call("pb_res_ln_rows_fwd", _p(a), _p(b), _p(c), _p(w_param), K, _p(gamma), _p(beta), _p(xhat), _p(rstd), _p(y),
+                                       B, G, _st())
+        ctx.save_for_backward(gamma, xhat, rstd, c, w_param)
+        ctx.has = (b is not None, c is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        gamma, xhat, rstd, c, w_param = ctx.saved_tensors
+        has_b, has_c = ctx.has
+        dy = dy.contiguous()
+        B, G = dy.shape
+        K = 0 if w_param is None else w_param.numel()
+        dx = torch.empty_like(dy)
+        dc = torch.empty_like(dy) if has_c else None
+        dgamma = torch.empty_like(gamma)
+        dbeta = torch.empty_like(gamma)
+        dwp = torch.empty_like(w_param) if has_c else None
+        _call("pb_res_ln_rows_bwd", _p(dy), _p(gamma), _p(xhat), _p(rstd), _p(c), _p(w_param), K, _p(dx), _p(dc),
+                                       _p(dgamma), _p(dbeta), _p(dwp), B, G, _st())
+        return dx, (dx if has_b else None), dc, dwp, dgamma, dbeta
+
+
+class LocalTrackFn(torch.autograd.Function):
+    """The local track of one ProteinBERTBlock plus the attention pooling it feeds
+    (modules.py:205-219): conv pair + GELU + 4-way add -> joint LN -> Linear+GELU+residual -> joint LN
+    -> pool[b,g] = sum_l gelu(h . Wv).  Returns (h2 [B,L,C] act, pool [B,G] f32)."""
+
+    @staticmethod
+    def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, wvT, ksize, dil, head_grads):
+        _need_cuda(x, g2l, Wn)
+        x = x.contiguous()
+        dt = dt_of(x)
+        B, L, C = x.shape
+        G = wvT.shape[0]
+        L_ = lib()
+        st = _st()
+        dev = x.device
+        wn_f, wn_b = conv_pack(Wn, dt)
+        ww_f, ww_b = conv_pack(Ww, dt)
+        W2w = to_wt(W2, dt)
+        wvTw = to_wt(wvT, dt)
+        stats1 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
+        stats2 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
+        zn, zw, u1, h1, z2, u2, h2 = (torch.empty_like(x) for _ in range(7))
+        g2l = g2l.contiguous()
+        _call("pb_conv_pair_fwd", _p(x), _p(wn_f), _p(ww_f), _p(bn), _p(bw), _p(g2l), _p(zn), _p(zw), _p(u1), _p(stats1),
+                                  B, L, C, ksize, dil, dt, st)
+        _call("pb_ln_joint_apply", _p(u1), _p(stats1), _p(ln1w), _p(ln1b), _p(h1), B, L, C, LN_EPS, dt, st)
+        _call("pb_local_linear_fwd", _p(h1), _p(W2w), _p(b2), _p(z2), _p(u2), _p(stats2), B, L, C, dt, st)
+        _call("pb_ln_joint_apply", _p(u2), _p(stats2), _p(ln2w), _p(ln2b), _p(h2), B, L, C, LN_EPS, dt, st)
+        pool = torch.empty((B, G), dtype=torch.float32, device=dev)
+        _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
+        ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w)
+        ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads))
+        return h2, pool
+
+    @staticmethod
+    def backward(ctx, dh2, dpool):
+        x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w = ctx.saved_tensors
+        B, L, C, G, ksize, dil, dt, head_grads = ctx.cfg
+        L_ = lib()
+        st = _st()
+        dev = x.device
+        adt = act_dtype(dt)
+        if dh2 is None:
+            dh2 = torch.zeros_like(x)
+        dh2 = dh2.contiguous().to(adt)
+        dpool = torch.zeros((B, G), dtype=torch.float32, device=dev) if dpool is None else dpool.contiguous()
+
+        def f32(*shape):
+            return torch.empty(shape, dtype=torch.float32, device=dev)
+
+        # attention pooling
+        dzv = torch.empty((B * L, G), dtype=adt, device=dev)
+        dh2t = torch.empty_like(x)
+        dWvT = f32(G, C) if head_grads else None
+        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, st)
+        del dzv
+        # LN2
+        sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
+        du2 = torch.empty_like(x)
+        dln2w, dln2b = f32(L, C), f32(L, C)
+        _call("pb_ln_joint_bwd", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(du2), _p(dln2w), _p(dln2b), _p(sums), B, L, C,
+                                 LN_EPS, dt, st)
+        # local linear
+        dz2 = dh2t                      # reuse as scratch
+        dh1 = torch.empty_like(x)
+        dW2, db2 = f32(C, C), f32(C)
+        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, st)
+        # LN1
+        du1 = du2                       # du2 is dead after the linear backward
+        dln1w, dln1b = f32(L, C), f32(L, C)
+        _call("pb_ln_joint_bwd", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(du1), _p(dln1w), _p(dln1b), _p(sums), B, L, C,
+                                 LN_EPS, dt, st)
+        # conv pair
+        dzn, dzw = dz2, dh1             # both dead by now
+        dx = torch.empty_like(x)
+        dWn, dWw = f32(C, C, ksize), f32(C, C, ksize)
+        dbn, dbw = f32(C), f32(C)
+        dg2l = f32(B, C)
+        _call("pb_conv_pair_bwd", _p(du1), _p(zn), _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), _p(dx), _p(dWn),
+                                  _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, st)
+        return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, dWvT, None, None, None)
+
+
+class AttnPoolFn(torch.autograd.Function):
+    """pool[b,g] = sum_l gelu(h[b,l,:] . Wv_all[:,g]) as a standalone op (GlobalAttention(Head).forward)."""
+
+    @staticmethod
+    def forward(ctx, h, wvT):
+        _need_cuda(h, wvT)
+        h = h.contiguous()
+        dt = dt_of(h)
+        B, L, C = h.shape
+        G = wvT.shape[0]
+        wvTw = to_wt(wvT, dt)
+        pool = torch.empty((B, G), dtype=torch.float32, device=h.device)
+        _call("pb_attn_pool_fwd", _p(h), _p(wvTw), _p(pool), B, L, C, G, dt, _st())
+        ctx.save_for_backward(h, wvTw)
+        return pool
+
+    @staticmethod
+    def backward(ctx, dpool):
+        h, wvTw = ctx.saved_tensors
+        dt = dt_of(h)
+        B, L, C = h.shape
+        G = wvTw.shape[0]
+        dev = h.device
+        dzv = torch.empty((B * L, G), dtype=h.dtype, device=dev)
+        zero = torch.zeros_like(h)
+        dh = torch.empty_like(h)
+        dWvT = torch.empty((G, C), dtype=torch.float32, device=dev)
+        _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), B, L, C, G,
+                                     dt, _st())
+        return dh, dWvT
+
+
+class TokenHeadFn(torch.autograd.Function):
+    """softmax over the batch axis of Linear(C->V)(h)  (modules.py:277-284,304)."""
+
+    @staticmethod
+    def forward(ctx, h, Wo, bo):
+        _need_cuda(h, Wo, bo)
+        h = h.contiguous()
+        dt = dt_of(h)
+        B, L, C = h.shape
+        V = Wo.shape[0]
+        p = torch.empty((B, L, V), dtype=torch.float32, device=h.device)
+        _call("pb_token_head_fwd", _p(h), _p(Wo.contiguous()), _p(bo), _p(p), B, L, C, V, dt, _st())
+        ctx.save_for_backward(h, Wo, p)
+        return p
+
+    @staticmethod
+    def backward(ctx, dP):
+        h, Wo, p = ctx.saved_tensors
+        dt = dt_of(h)
+        B, L, C = h.shape
+        V = Wo.shape[0]
+        dP = dP.contiguous().float()
+        dh = torch.empty_like(h)
+        dWo = torch.empty_like(Wo)
+        dbo = torch.empty((V,), dtype=torch.float32, device=h.device)
+        _call("pb_token_head_bwd", _p(dP), _p(p), _p(h), _p(Wo.contiguous()), None, _p(dh), _p(dWo), _p(dbo), B, L, C, V,
+                                      dt, _st())
+        return dh, dWo, dbo
+
+
+class PretrainLossFn(torch.autograd.Function):
+    """utils.py:293-294 with CrossEntropyLoss/BCELoss(reduction='none') (dummy_tests.py:132-133), float64."""
+
+    @staticmethod
+    def forward(ctx, p_local, p_global, y_local, y_global, w_local, w_global):
+        _need_cuda(p_local, p_global, y_local)
+        p_local, p_global = p_local.contiguous(), p_global.contiguous()
+        B, L, V = p_local.shape
+        A = p_global.shape[1]
+        y_local = y_local.contiguous()
+        y_global = y_global.contiguous().float()
+        w_local = w_local.contiguous().double()
+        w_global = w_global.contiguous().double()
+        loss = torch.empty((3,), dtype=torch.float64, device=p_local.device)
+        dPl = torch.empty_like(p_local)
+        dPg = torch.empty_like(p_global)
+        _call("pb_pretrain_loss", _p(p_local), _p(p_global), _p(y_local), _p(y_global), _p(w_local), _p(w_global),
+                                     _p(loss), _p(dPl), _p(dPg), B, L, V, A, _st())
+        ctx.save_for_backward(dPl, dPg)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, dloss):
+        dPl, dPg = ctx.saved_tensors
+        s = dloss.float()
+        return dPl * s, dPg * s, None, None, None, None
+
+
+def linear_act(x, W, b, act):
+    return LinearActFn.apply(x, W, b, act)
+
+
+__all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
+           "LocalTrackFn", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]

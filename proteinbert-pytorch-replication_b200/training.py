@@ -1,0 +1,125 @@
+"""The pretraining step around the model: the loss of the reference loop and data-parallel gradient
+averaging.  Host logic only -- the arithmetic is in ops.py / libpb_b200.so.
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+
+def pretraining_loss(p_local, p_global, Y: Dict[str, torch.Tensor], W: Dict[str, torch.Tensor]) -> torch.Tensor:
+    """``mean(CE(p_local.permute(0,2,1), Y.local) * W.local) + mean(BCE(p_global, Y.global) * W.global)``
+    exactly as utils.py:293-294 evaluates it with the loss modules of dummy_tests.py:132-133
+    (CrossEntropyLoss re-normalises the probabilities over the vocabulary axis; BCELoss clamps logs at -100);
+    float64 scalar.  One fused kernel instead of six torch ops; differentiable w.r.t. both inputs."""
+    return ops.PretrainLossFn.apply(p_local, p_global, Y["local"], Y["global"], W["local"], W["global"])
+
+
+def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None) -> torch.Tensor:
+    """forward + loss + backward (utils.py:291-299 without the optimizer).  Gradients are left in ``.grad``
+    (averaged over ranks when a reducer is given).  Returns the detached loss."""
+    for p in model.parameters():
+        p.grad = None
+    p_local, p_global = model(X)
+    loss = pretraining_loss(p_local, p_global, Y, W)
+    if reducer is not None:
+        reducer.prepare()
+    loss.backward()
+    if reducer is not None:
+        reducer.finish()
+    return loss.detach()
+
+
+class GradAllReducer:
+    """Data-parallel gradient averaging overlapped with backward.
+
+    The reference is single-process; batch sharding is the natural partition of this path, and its one
+    exchange step is the all-reduce of the 133 registered gradients (the attention-head tensors are not
+    registered in the reference, so -- as there -- they are neither broadcast nor reduced).
+
+    Parameters are grouped into buckets in REVERSE registration order (roughly the order backward produces
+    them: the annotation-output layer first, the annotation-input layer last).  A post-accumulate hook on
+    each parameter counts its bucket down; when a bucket is complete its gradients are packed into one flat
+    buffer and all-reduced asynchronously (NCCL runs it on its own stream over NVLink/NVSwitch) while
+    backward continues.  ``finish()`` waits for the outstanding buckets, scales by 1/world and unpacks.
+    Works with any backend (``gloo`` in the CPU tests)."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], bucket_bytes: int = 8 << 20, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
+        self.buckets: List[List[torch.nn.Parameter]] = []
+        cur, size = [], 0
+        for p in reversed(self.params):
+            cur.append(p)
+            size += p.numel() * p.element_size()
+            if size >= bucket_bytes:
+                self.buckets.append(cur)
+                cur, size = [], 0
+        if cur:
+            self.buckets.append(cur)
+        self._bucket_of = {id(p): i for i, b in enumerate(self.buckets) for p in b}
+        self._flat: List[Optional[torch.Tensor]] = [None] * len(self.buckets)
+        self._pending = [0] * len(self.buckets)
+        self._work = []
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+        self._armed = False
+
+    def broadcast_parameters(self, src: int = 0):
+        if self.world > 1:
+            for p in self.params:
+                dist.broadcast(p.data, src, group=self.group)
+
+    def prepare(self):
+        self._pending = [len(b) for b in self.buckets]
+        self._work = []
+        self._armed = True
+
+    def _on_grad(self, p):
+        if not self._armed or self.world == 1:
+            return
+        i = self._bucket_of[id(p)]
+        self._pending[i] -= 1
+        if self._pending[i] == 0:
+            self._launch(i)
+
+    def _launch(self, i):
+        bucket = self.buckets[i]
+        flat = torch.cat([p.grad.reshape(-1) for p in bucket])
+        self._flat[i] = flat
+        self._work.append((i, dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)))
+
+    def finish(self):
+        if not self._armed:
+            return
+        self._armed = False
+        if self.world == 1:
+            return
+        # parameters that received no gradient this step still have to take part in the collective
+        for i, n in enumerate(self._pending):
+            if n > 0:
+                for p in self.buckets[i]:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+                self._pending[i] = 0
+                self._launch(i)
+        for i, work in self._work:
+            work.wait()
+            flat = self._flat[i]
+            flat.mul_(1.0 / self.world)
+            off = 0
+            for p in self.buckets[i]:
+                n = p.numel()
+                p.grad.copy_(flat[off:off + n].view_as(p))
+                off += n
+            self._flat[i] = None
+        self._work = []
+
+    def remove(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
