@@ -49,6 +49,10 @@ const char* pb_last_error(void);
 int pb_device_ok(int device);
 /* number of kernel launches issued through this library since load (bench.py's gpu_launches). */
 long long pb_launch_count(void);
+/* 1 (default): PB_BF16 contractions run on the tcgen05 tensor-core engine where the tiling covers the shape
+ * (C = 128 for the convolutions, C, G multiples of 128, L a multiple of 128); 0: force the fp32-accumulating
+ * SIMT engine (same bf16 operands; used by the tests to cross-check the two engines).  Returns the old value. */
+int pb_set_tensor_cores(int enabled);
 
 /* ---- parameter staging ----------------------------------------------------------------------- */
 /* float -> bf16 copy of a weight tensor (shadow weights of the bf16 mode). */
@@ -114,8 +118,10 @@ int pb_ln_joint_bwd(const void* dy_act, const void* u_act, const double* stats, 
  * z = h W^T + b, u2 = h + gelu(z), stats2[b] += (sum, sumsq) of u2.  W is [C,C] of type wt.        */
 int pb_local_linear_fwd(const void* h_act, const void* W_wt, const float* bias, void* z_act, void* u2_act,
                         double* stats2, int B, int L, int C, int dt, void* stream);
-/* dz = du2*gelu'(z) (scratch), dh = du2 + dz W, dW = dz^T h, db = sum dz.                          */
-int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_act, const void* W_wt, void* dz_act,
+/* dz = du2*gelu'(z) (scratch), dh = du2 + dz W, dW = dz^T h, db = sum dz.  Wt_wt = W transposed ([C_in, C_out],
+ * the K-major operand of the tensor-core data-gradient GEMM); may be NULL, which selects the SIMT engine.   */
+int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_act, const void* W_wt, const void* Wt_wt,
+                        void* dz_act,
                         void* dh_act, float* dW, float* db, int B, int L, int C, int dt, void* stream);
 
 /* ---- a11/a12: global attention (modules.py:21-92) under the reference's softmax axis ------------
@@ -124,8 +130,9 @@ int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_ac
  * wvT is Wv_all transposed, [G, C], type wt.                                                       */
 int pb_attn_pool_fwd(const void* h_act, const void* wvT_wt, float* pool, int B, int L, int C, int G, int dt,
                      void* stream);
-/* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip). */
-int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const float* dpool, const void* dh_in_act,
+/* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip).
+ * wv_wt = Wv_all [C, G] (K-major operand of the tensor-core dh GEMM); NULL selects the SIMT engine.          */
+int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const void* wv_wt, const float* dpool, const void* dh_in_act,
                      void* dzv_act, void* dh_out_act, float* dWvT, int B, int L, int C, int G, int dt,
                      void* stream);
 

@@ -22,6 +22,7 @@ PROTOTYPES = {
     "pb_last_error": [],
     "pb_device_ok": [_i],
     "pb_launch_count": [],
+    "pb_set_tensor_cores": [_i],
     "pb_cast_f32_to_bf16": [_p, _p, _ll, _p],
     "pb_conv_weight_pack": [_p, _p, _p, _i, _i, _i, _p],
     "pb_embedding_fwd": [_p, _p, _p, _ll, _i, _i, _i, _p],
@@ -36,9 +37,9 @@ PROTOTYPES = {
     "pb_ln_joint_apply": [_p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
     "pb_ln_joint_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
     "pb_local_linear_fwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
-    "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_attn_pool_fwd": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
-    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_pretrain_loss": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],

@@ -396,21 +396,21 @@ int pb_local_linear_fwd(const void* h, const void* W, const float* bias, void* z
     return pb_check_launch("pb_local_linear_fwd");
 }
 
-int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const void* W, void* dz, void* dh, float* dW, float* db,
+int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const void* W, const void* Wt, void* dz, void* dh, float* dW, float* db,
                         int B, int L, int C, int dt, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "local_linear_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
     PB_CUDA(cudaMemsetAsync(db, 0, C * sizeof(float), st));
     PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
-    const bool tc = dt == PB_BF16 && pb_tc_linear_ok(B, L, C);
+    const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
     DISPATCH_DT(dt, {
         dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
         gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
             (const T*)du2, (const T*)z, (const T*)nullptr, (T*)dz, (T*)nullptr, (float*)nullptr, db, (float*)nullptr, L, C);
         pb_count_launch(1);
         if (tc) {
-            int rc = pb_tc_local_linear_bwd(du2, dz, h, W, dh, dW, B, L, C, st);
+            int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, st);
             if (rc) return rc;
         } else {
             // dh = du2 + dz W
@@ -432,14 +432,14 @@ int pb_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, 
     return pb_check_launch("pb_attn_pool_fwd");
 }
 
-int pb_attn_pool_bwd(const void* h, const void* wvT, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
+int pb_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
                      float* dWvT, int B, int L, int C, int G, int dt, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
     if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
-    if (dt == PB_BF16 && pb_tc_attn_ok(B, L, C, G))
-        return pb_tc_attn_pool_bwd(h, wvT, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, st);
+    if (dt == PB_BF16 && wv != nullptr && pb_tc_attn_ok(B, L, C, G))
+        return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, st);
     DISPATCH_DT(dt, {
         gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
         gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);

@@ -4,6 +4,7 @@
 #pragma once
 #include "common.cuh"
 
+bool pb_tc_enabled();
 bool pb_tc_conv_ok(int B, int L, int C, int ksize, int dil);
 bool pb_tc_linear_ok(int B, int L, int C);
 bool pb_tc_attn_ok(int B, int L, int C, int G);
@@ -17,10 +18,10 @@ int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn
                      int dil, cudaStream_t st);
 int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L,
                            int C, cudaStream_t st);
-int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* W, void* dh, float* dW, int B, int L,
+int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* Wt, void* dh, float* dW, int B, int L,
                            int C, cudaStream_t st);
 int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st);
-int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
+int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
                         float* dWvT, int B, int L, int C, int G, cudaStream_t st);
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st);

@@ -1,0 +1,392 @@
+// bf16 tcgen05 GEMMs of the local track that are not convolutions.
+//
+//   tc_gemm_kernel  : D[128 x 128 tile] = A[M,K] * B[N,K]^T, both operands K-major, fused epilogues:
+//       LINEAR_FWD  z = D + b ; u2 = h + gelu(z) ; LayerNorm sums           (modules.py:214-216)
+//       POOL_FWD    pool[b, n] += sum over the tile's rows of gelu(D)        (modules.py:55-60,92)
+//       POOL_DZ     dzv = dpool[b, n] * gelu'(D)
+//       ADD_STORE   out = base + D                                           (data gradients)
+//   tc_wgrad_kernel : D[m, n] += sum_rows P[row, m] * Q[row + shift, n]  -- the contraction runs over sequence
+//       positions, so both operands are MN-major in shared memory (rows of the activation tensors are K);
+//       used for the conv weight gradients (one launch covers all taps), dW of the local linear and dWv.
+//
+// Same skeleton as tc_conv.cu: warp 0 TMA producer, warp 1 TMEM alloc + MMA issue, warps 2..5 epilogue.
+#include "tc_common.cuh"
+#include "tc_api.cuh"
+
+namespace {
+
+constexpr int kBM = 128, kBN = 128;
+constexpr int kStages = 3;
+constexpr int kStageBytes = (kBM + kBN) * 64 * 2;          // 32 KB
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 4 * kBN * 4;
+constexpr int kThreads = 192;
+
+enum { EPI_LINEAR_FWD = 0, EPI_POOL_FWD = 1, EPI_POOL_DZ = 2, EPI_ADD_STORE = 3 };
+
+struct GemmEpi {
+    int ldn;                       // row pitch (elements) of the [M, ldn] tensors touched by the epilogue
+    int L;                         // rows per sample (sample index = row / L)
+    const float* bias;             // [N]
+    const bf16* base;              // residual / addend [M, ldn]
+    bf16* out0;                    // z / dzv / out
+    bf16* out1;                    // u2
+    double* stats;                 // [B, 2]
+    float* pool;                   // [B, ldn]
+    const float* dpool;            // [B, ldn]
+};
+
+// transpose-reduce: on return lane i holds the sum over the warp's 32 lanes of v[i]
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j < n / 2) {
+                const float send = up ? v[j] : v[j + n / 2];
+                const float keep = up ? v[j + n / 2] : v[j];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+    }
+    return v[0];
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 2)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmEpi ep, int K) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+    float* colsum = (float*)(smem + kStages * kStageBytes + 256);      // [4][kBN]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+    const int n_iter = K / 64;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapA); tma_prefetch_desc(&mapB);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<kBN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int i = 0; i < n_iter; ++i) {
+                const int s = i % kStages;
+                mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
+                uint8_t* a_dst = smem + s * kStageBytes;
+                uint8_t* b_dst = a_dst + kBM * 64 * 2;
+                mbar_expect_tx(&full_bar[s], kStageBytes);
+                tma_load_2d(a_dst, &mapA, &full_bar[s], i * 64, m0);
+                tma_load_2d(b_dst, &mapB, &full_bar[s], i * 64, n0);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(kBM, kBN, 0, 0);
+            for (int i = 0; i < n_iter; ++i) {
+                const int s = i % kStages;
+                mbar_wait(&full_bar[s], (i / kStages) & 1);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+                const uint32_t b_addr = a_addr + kBM * 64 * 2;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
+                              make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i == 0 && k == 0) ? 0u : 1u);
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else {
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        const int q = warp & 3;
+        const int row = m0 + q * 32 + lane;
+        const int b = m0 / ep.L;                         // tiles never straddle samples (L % 128 == 0)
+        const size_t grow = (size_t)row * ep.ldn + n0;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        float s_sum = 0.f, s_sq = 0.f;
+#pragma unroll 1
+        for (int ch = 0; ch < kBN / 32; ++ch) {
+            float acc[32];
+            tmem_ld32(taddr + ch * 32, acc);
+            const int c0 = ch * 32;
+            if (EPI == EPI_LINEAR_FWD) {
+                uint4 hv[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) hv[v] = *reinterpret_cast<const uint4*>(ep.base + grow + c0 + v * 8);
+                const bf16* hb = reinterpret_cast<const bf16*>(hv);
+                __align__(16) bf16 oz[32], ou[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const bf16 z = __float2bfloat16_rn(acc[j] + __ldg(ep.bias + n0 + c0 + j));
+                    oz[j] = z;
+                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_f(__bfloat162float(z)));
+                    ou[j] = ub;
+                    const float ur = __bfloat162float(ub);
+                    s_sum += ur; s_sq += ur * ur;
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oz)[v];
+                    *reinterpret_cast<uint4*>(ep.out1 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(ou)[v];
+                }
+            } else if (EPI == EPI_POOL_FWD) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[j] = gelu_f(acc[j]);
+                const float cs = warp_transpose_sum(acc, lane);
+                colsum[q * kBN + c0 + lane] = cs;
+            } else if (EPI == EPI_POOL_DZ) {
+                __align__(16) bf16 od[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    od[j] = __float2bfloat16_rn(__ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + j) * gelu_grad_f(acc[j]));
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(od)[v];
+            } else {
+                uint4 bv[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) bv[v] = *reinterpret_cast<const uint4*>(ep.base + grow + c0 + v * 8);
+                const bf16* bb = reinterpret_cast<const bf16*>(bv);
+                __align__(16) bf16 oo[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) oo[j] = __float2bfloat16_rn(__bfloat162float(bb[j]) + acc[j]);
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oo)[v];
+            }
+        }
+        if (EPI == EPI_LINEAR_FWD) {
+            const double ds = warp_sum_d((double)s_sum), dq = warp_sum_d((double)s_sq);
+            if (lane == 0) { atomicAdd(&ep.stats[2 * b], ds); atomicAdd(&ep.stats[2 * b + 1], dq); }
+        }
+        if (EPI == EPI_POOL_FWD) {
+            asm volatile("bar.sync 1, 128;" ::: "memory");           // the four epilogue warps only
+            const int t = threadIdx.x - 64;                          // 0..127
+            const float tot = colsum[t] + colsum[kBN + t] + colsum[2 * kBN + t] + colsum[3 * kBN + t];
+            atomicAdd(&ep.pool[(size_t)b * ep.ldn + n0 + t], tot);
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kBN>(tmem_base);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// weight-gradient GEMM: contraction over sequence positions, MN-major operands
+// ---------------------------------------------------------------------------------------------------------
+struct WgradParams {
+    float* out; long stride_m, stride_n, stride_t;     // out[m*stride_m + n*stride_n + t*stride_t] += D[m, n]
+    int L, dil, half;                                   // shift(t) = (t - half) * dil
+    int chunks_total, chunks_per_split;                 // 64-row chunks over all samples
+};
+
+__global__ void __launch_bounds__(kThreads, 2)
+tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant__ CUtensorMap mapQ, WgradParams wp, int tiles_n) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tmem_full_bar = empty_bar + kStages;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = (blockIdx.x / tiles_n) * kBM, n0 = (blockIdx.x % tiles_n) * kBN;
+    const int t = blockIdx.y;
+    const int shift = (t - wp.half) * wp.dil;
+    const int c_beg = blockIdx.z * wp.chunks_per_split;
+    const int c_end = min(wp.chunks_total, c_beg + wp.chunks_per_split);
+    const int n_iter = c_end - c_beg;
+    const int chunks_per_sample = wp.L / 64;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapP); tma_prefetch_desc(&mapQ);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<kBN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (n_iter > 0) {
+        if (warp == 0) {
+            if (lane == 0) {
+                for (int i = 0; i < n_iter; ++i) {
+                    const int s = i % kStages;
+                    mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
+                    const int chunk = c_beg + i;
+                    const int b = chunk / chunks_per_sample;
+                    const int l0 = (chunk % chunks_per_sample) * 64;
+                    uint8_t* a_dst = smem + s * kStageBytes;
+                    uint8_t* b_dst = a_dst + kBM * 64 * 2;
+                    mbar_expect_tx(&full_bar[s], kStageBytes);
+                    tma_load_3d(a_dst, &mapP, &full_bar[s], m0, l0, b);
+                    tma_load_3d(a_dst + 8192, &mapP, &full_bar[s], m0 + 64, l0, b);
+                    tma_load_3d(b_dst, &mapQ, &full_bar[s], n0, l0 + shift, b);
+                    tma_load_3d(b_dst + 8192, &mapQ, &full_bar[s], n0 + 64, l0 + shift, b);
+                }
+            }
+        } else if (warp == 1) {
+            if (lane == 0) {
+                constexpr uint32_t idesc = make_idesc_bf16(kBM, kBN, 1, 1);
+                for (int i = 0; i < n_iter; ++i) {
+                    const int s = i % kStages;
+                    mbar_wait(&full_bar[s], (i / kStages) & 1);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+                    const uint32_t b_addr = a_addr + kBM * 64 * 2;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)      // 16 contraction rows per MMA = 2048 B down the tile
+                        umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 2048, 8192, 1024),
+                                  make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024), idesc, (i == 0 && k == 0) ? 0u : 1u);
+                    umma_commit(&empty_bar[s]);
+                }
+                umma_commit(tmem_full_bar);
+            }
+        } else {
+            mbar_wait(tmem_full_bar, 0);
+            tc_fence_after();
+            const int q = warp & 3;
+            const int m = m0 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+            for (int ch = 0; ch < kBN / 32; ++ch) {
+                float acc[32];
+                tmem_ld32(taddr + ch * 32, acc);
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                    atomicAdd(wp.out + (size_t)m * wp.stride_m + (size_t)(n0 + ch * 32 + j) * wp.stride_n + (size_t)t * wp.stride_t,
+                              acc[j]);
+            }
+            tc_fence_before();
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kBN>(tmem_base);
+    }
+}
+
+int make_mat_map(CUtensorMap* m, const void* base, long rows, int cols, int box_rows) {
+    const uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
+    const uint64_t strides[1] = {(uint64_t)cols * 2};
+    const uint32_t box[2] = {64, (uint32_t)box_rows};
+    return pb_make_tmap_bf16(m, base, 2, dims, strides, box);
+}
+int make_act_map(CUtensorMap* m, const void* base, int B, int L, int C, int box_rows) {
+    const uint64_t dims[3] = {(uint64_t)C, (uint64_t)L, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)C * 2, (uint64_t)L * C * 2};
+    const uint32_t box[3] = {64, (uint32_t)box_rows, 1};
+    return pb_make_tmap_bf16(m, base, 3, dims, strides, box);
+}
+
+template <int EPI>
+int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, int K, cudaStream_t st, const char* what) {
+    CUtensorMap mA, mB;
+    int rc;
+    if ((rc = make_mat_map(&mA, A, M, K, kBM))) return rc;
+    if ((rc = make_mat_map(&mB, Bm, N, K, kBN))) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PB_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_set = true;
+    }
+    tc_gemm_kernel<EPI><<<dim3(M / kBM, N / kBN), kThreads, kSmemBytes, st>>>(mA, mB, ep, K);
+    pb_count_launch(1);
+    return pb_check_launch(what);
+}
+
+// P [B, L, Mtot], Q [B, L, Ntot]  ->  out[m, n, t] += sum_{b,l} P[b,l,m] Q[b,l+shift(t),n]
+int launch_wgrad(const void* P, const void* Q, float* out, long stride_m, long stride_n, long stride_t, int B, int L, int Mtot,
+                 int Ntot, int ntaps, int dil, cudaStream_t st, const char* what) {
+    CUtensorMap mP, mQ;
+    int rc;
+    if ((rc = make_act_map(&mP, P, B, L, Mtot, 64))) return rc;
+    if ((rc = make_act_map(&mQ, Q, B, L, Ntot, 64))) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PB_CUDA(cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_set = true;
+    }
+    WgradParams wp;
+    wp.out = out; wp.stride_m = stride_m; wp.stride_n = stride_n; wp.stride_t = stride_t;
+    wp.L = L; wp.dil = dil; wp.half = ntaps / 2;
+    wp.chunks_total = B * (L / 64);
+    const int tiles = (Mtot / kBM) * (Ntot / kBN) * ntaps;
+    int splits = (2 * 148 + tiles - 1) / tiles;
+    if (splits > wp.chunks_total) splits = wp.chunks_total;
+    if (splits < 1) splits = 1;
+    wp.chunks_per_split = (wp.chunks_total + splits - 1) / splits;
+    splits = (wp.chunks_total + wp.chunks_per_split - 1) / wp.chunks_per_split;
+    tc_wgrad_kernel<<<dim3((Mtot / kBM) * (Ntot / kBN), ntaps, splits), kThreads, kSmemBytes, st>>>(mP, mQ, wp, Ntot / kBN);
+    pb_count_launch(1);
+    return pb_check_launch(what);
+}
+
+}  // namespace
+
+bool pb_tc_linear_ok(int B, int L, int C) { return pb_tc_enabled() && C % 128 == 0 && L % 128 == 0 && B >= 1; }
+bool pb_tc_attn_ok(int B, int L, int C, int G) { return pb_tc_enabled() && C % 128 == 0 && G % 128 == 0 && L % 128 == 0 && B >= 1; }
+
+int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int C, int ksize,
+                     int dil, cudaStream_t st) {
+    // dW[co, ci, t] = sum_{b,l} dz[b,l,co] x[b,l+(t-half)*d,ci]   (dW zeroed by the caller)
+    int rc = launch_wgrad(dzn, x, dWn, (long)C * ksize, ksize, 1, B, L, C, C, ksize, 1, st, "tc_conv_wgrad(narrow)");
+    if (rc) return rc;
+    return launch_wgrad(dzw, x, dWw, (long)C * ksize, ksize, 1, B, L, C, C, ksize, dil, st, "tc_conv_wgrad(wide)");
+}
+
+int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L,
+                           int C, cudaStream_t st) {
+    GemmEpi ep{};
+    ep.ldn = C; ep.L = L; ep.bias = bias; ep.base = (const bf16*)h; ep.out0 = (bf16*)z; ep.out1 = (bf16*)u2; ep.stats = stats2;
+    return launch_gemm<EPI_LINEAR_FWD>(h, W, ep, B * L, C, C, st, "tc_local_linear_fwd");
+}
+
+int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* Wt, void* dh, float* dW, int B, int L,
+                           int C, cudaStream_t st) {
+    // dh = du2 + dz W   (B operand = W^T [C_in, C_out], K-major)   ;   dW[n, c] = sum_rows dz[row, n] h[row, c]
+    GemmEpi ep{};
+    ep.ldn = C; ep.L = L; ep.base = (const bf16*)du2; ep.out0 = (bf16*)dh;
+    int rc = launch_gemm<EPI_ADD_STORE>(dz, Wt, ep, B * L, C, C, st, "tc_local_linear_bwd(dh)");
+    if (rc) return rc;
+    return launch_wgrad(dz, h, dW, C, 1, 0, B, L, C, C, 1, 1, st, "tc_local_linear_bwd(dW)");
+}
+
+int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st) {
+    GemmEpi ep{};
+    ep.ldn = G; ep.L = L; ep.pool = pool;
+    return launch_gemm<EPI_POOL_FWD>(h, wvT, ep, B * L, G, C, st, "tc_attn_pool_fwd");
+}
+
+int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv,
+                        void* dh_out, float* dWvT, int B, int L, int C, int G, cudaStream_t st) {
+    GemmEpi e1{};
+    e1.ldn = G; e1.L = L; e1.dpool = dpool; e1.out0 = (bf16*)dzv;
+    int rc = launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
+    if (rc) return rc;
+    GemmEpi e2{};
+    e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
+    rc = launch_gemm<EPI_ADD_STORE>(dzv, wv, e2, B * L, C, G, st, "tc_attn_pool_bwd(dh)");
+    if (rc) return rc;
+    if (dWvT) rc = launch_wgrad(dzv, h, dWvT, C, 1, 0, B, L, G, C, 1, 1, st, "tc_attn_pool_bwd(dWv)");
+    return rc;
+}

@@ -1,0 +1,75 @@
+// Host side of the tensor-core engine: CUtensorMap construction through the driver entry point, the
+// engine switch, and the vectorised bf16 LayerNorm-apply.
+#include <atomic>
+#include <cudaTypedefs.h>
+#include "tc_common.cuh"
+#include "tc_api.cuh"
+#include "../../include/pb_b200.h"
+
+static std::atomic<int> g_tc_enabled{1};
+
+bool pb_tc_enabled() { return g_tc_enabled.load(std::memory_order_relaxed) != 0; }
+
+extern "C" int pb_set_tensor_cores(int enabled) { return g_tc_enabled.exchange(enabled ? 1 : 0); }
+
+int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box) {
+    static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        PB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        PB_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, PB_ERR_CUDA, "cuTensorMapEncodeTiled not available");
+        encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+    }
+    PB_REQUIRE(((uintptr_t)base % 16) == 0, PB_ERR_SHAPE, "tensor map base address must be 16-byte aligned");
+    cuuint64_t gdim[5];
+    cuuint64_t gstr[4];
+    cuuint32_t bdim[5], estr[5];
+    for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bdim[i] = box[i]; estr[i] = 1; }
+    for (int i = 0; i + 1 < rank; ++i) {
+        PB_REQUIRE(strides_bytes[i] % 16 == 0, PB_ERR_SHAPE, "tensor map stride %d (%llu B) is not a multiple of 16", i,
+                   (unsigned long long)strides_bytes[i]);
+        gstr[i] = strides_bytes[i];
+    }
+    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    PB_REQUIRE(r == CUDA_SUCCESS, PB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return PB_OK;
+}
+
+namespace {
+
+// h = (u - mean) * rstd * gamma + beta, 8 bf16 per thread; grid = (chunks, B)
+__global__ void ln_apply_bf16_kernel(const bf16* __restrict__ u, const double* __restrict__ stats, const float* __restrict__ gamma,
+                                     const float* __restrict__ beta, bf16* __restrict__ h, long long n, float eps) {
+    const int b = blockIdx.y;
+    const LnStat st = ln_stat(stats, b, (double)n, eps);
+    const long long nv = n / 8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+        const uint4 uv = *reinterpret_cast<const uint4*>(u + (size_t)b * n + i * 8);
+        const float4 g0 = *reinterpret_cast<const float4*>(gamma + i * 8), g1 = *reinterpret_cast<const float4*>(gamma + i * 8 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(beta + i * 8), b1 = *reinterpret_cast<const float4*>(beta + i * 8 + 4);
+        const bf16* ub = reinterpret_cast<const bf16*>(&uv);
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        __align__(16) bf16 o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16_rn((__bfloat162float(ub[j]) - st.mean) * st.rstd * gg[j] + bb[j]);
+        *reinterpret_cast<uint4*>(h + (size_t)b * n + i * 8) = *reinterpret_cast<const uint4*>(o);
+    }
+}
+
+}  // namespace
+
+bool pb_tc_ln_apply_ok(int L, int C) { return ((long long)L * C) % 8 == 0; }
+
+int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
+                   float eps, cudaStream_t st) {
+    const long long n = (long long)L * C;
+    dim3 grid((unsigned)max(1, min(ceil_div(n / 8, 256), 16)), B);
+    ln_apply_bf16_kernel<<<grid, 256, 0, st>>>((const bf16*)u, stats, gamma, beta, (bf16*)h, n, eps);
+    pb_count_launch(1);
+    return pb_check_launch("pb_ln_joint_apply(bf16)");
+}

@@ -211,6 +211,9 @@ class LocalTrackFn(torch.autograd.Function):
         ww_f, ww_b = conv_pack(Ww, dt)
         W2w = to_wt(W2, dt)
         wvTw = to_wt(wvT, dt)
+        # transposed copies: the K-major operands of the tensor-core data-gradient GEMMs (bf16 mode only)
+        W2Tw = to_wt(W2.t(), dt) if dt == BF16 else None
+        wvw = to_wt(wvT.t(), dt) if dt == BF16 else None
         stats1 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
         stats2 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
         zn, zw, u1, h1, z2, u2, h2 = (torch.empty_like(x) for _ in range(7))
@@ -222,13 +225,13 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_ln_joint_apply", _p(u2), _p(stats2), _p(ln2w), _p(ln2b), _p(h2), B, L, C, LN_EPS, dt, st)
         pool = torch.empty((B, G), dtype=torch.float32, device=dev)
         _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
-        ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w)
+        ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w, W2Tw, wvw)
         ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads))
         return h2, pool
 
     @staticmethod
     def backward(ctx, dh2, dpool):
-        x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w = ctx.saved_tensors
+        x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w, W2Tw, wvw = ctx.saved_tensors
         B, L, C, G, ksize, dil, dt, head_grads = ctx.cfg
         L_ = lib()
         st = _st()
@@ -246,7 +249,7 @@ class LocalTrackFn(torch.autograd.Function):
         dzv = torch.empty((B * L, G), dtype=adt, device=dev)
         dh2t = torch.empty_like(x)
         dWvT = f32(G, C) if head_grads else None
-        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, st)
+        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, st)
         del dzv
         # LN2
         sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
@@ -258,7 +261,7 @@ class LocalTrackFn(torch.autograd.Function):
         dz2 = dh2t                      # reuse as scratch
         dh1 = torch.empty_like(x)
         dW2, db2 = f32(C, C), f32(C)
-        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, st)
+        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, st)
         # LN1
         du1 = du2                       # du2 is dead after the linear backward
         dln1w, dln1b = f32(L, C), f32(L, C)
@@ -286,14 +289,15 @@ class AttnPoolFn(torch.autograd.Function):
         B, L, C = h.shape
         G = wvT.shape[0]
         wvTw = to_wt(wvT, dt)
+        wvw = to_wt(wvT.t(), dt) if dt == BF16 else None
         pool = torch.empty((B, G), dtype=torch.float32, device=h.device)
         _call("pb_attn_pool_fwd", _p(h), _p(wvTw), _p(pool), B, L, C, G, dt, _st())
-        ctx.save_for_backward(h, wvTw)
+        ctx.save_for_backward(h, wvTw, wvw)
         return pool
 
     @staticmethod
     def backward(ctx, dpool):
-        h, wvTw = ctx.saved_tensors
+        h, wvTw, wvw = ctx.saved_tensors
         dt = dt_of(h)
         B, L, C = h.shape
         G = wvTw.shape[0]
@@ -302,7 +306,7 @@ class AttnPoolFn(torch.autograd.Function):
         zero = torch.zeros_like(h)
         dh = torch.empty_like(h)
         dWvT = torch.empty((G, C), dtype=torch.float32, device=dev)
-        _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), B, L, C, G,
+        _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(wvw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), B, L, C, G,
                                      dt, _st())
         return dh, dWvT
 

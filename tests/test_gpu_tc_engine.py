@@ -1,0 +1,152 @@
+"""GPU: the tcgen05 tensor-core engine against the fp32-accumulating SIMT engine on identical bf16 operands,
+op by op through the C ABI (pb_set_tensor_cores toggles the engine).  Both engines round the same inputs to
+bf16 and accumulate in fp32, so they may differ only by summation order and by one-ulp flips of bf16 outputs:
+rel-Frobenius <= 3e-3 for bf16 outputs, <= 1e-3 for fp32 outputs."""
+import pytest
+import torch
+
+from helpers import rel_fro
+
+pytestmark = pytest.mark.gpu
+
+B, L, C, G, KS, DIL = 3, 256, 128, 512, 9, 5
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import proteinbert_b200
+    return proteinbert_b200
+
+
+def both_engines(pb, fn):
+    lib = pb._lib.lib()
+    outs = []
+    for enabled in (0, 1):
+        lib.pb_set_tensor_cores(enabled)
+        try:
+            outs.append([o.float().clone() for o in fn()])
+            torch.cuda.synchronize()
+        finally:
+            lib.pb_set_tensor_cores(1)
+    return outs
+
+
+def compare(names, simt, tc, tol_bf16=3e-3):
+    bad = []
+    for n, a, b in zip(names, simt, tc):
+        e = rel_fro(b, a)
+        print(f"  {n}: rel_fro {e:.3e} |ref| {float(a.norm()):.3e}")
+        if not e <= tol_bf16:
+            bad.append((n, e))
+    assert not bad, bad
+
+
+def rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale)
+
+
+def test_conv_pair_forward(pb):
+    from proteinbert_b200 import ops
+    x = rnd(B, L, C, seed=1).cuda().bfloat16()
+    wn, ww = rnd(C, C, KS, scale=0.05, seed=2).cuda(), rnd(C, C, KS, scale=0.05, seed=3).cuda()
+    bn, bw, g2l = rnd(C, seed=4).cuda(), rnd(C, seed=5).cuda(), rnd(B, C, seed=6).cuda()
+    wn_f, _ = ops.conv_pack(wn, 1)
+    ww_f, _ = ops.conv_pack(ww, 1)
+
+    def run():
+        zn, zw, u = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+        stats = torch.zeros(B, 2, dtype=torch.float64, device="cuda")
+        ops._call("pb_conv_pair_fwd", x.data_ptr(), wn_f.data_ptr(), ww_f.data_ptr(), bn.data_ptr(), bw.data_ptr(), g2l.data_ptr(),
+                  zn.data_ptr(), zw.data_ptr(), u.data_ptr(), stats.data_ptr(), B, L, C, KS, DIL, 1, torch.cuda.current_stream().cuda_stream)
+        return zn, zw, u, stats
+
+    simt, tc = both_engines(pb, run)
+    compare(["zn", "zw", "u", "stats"], simt, tc)
+    # and against torch conv1d in fp64 on the bf16-rounded operands (edge rows exercise the zero padding)
+    xr = x.double().cpu().permute(0, 2, 1)
+    ref = torch.nn.functional.conv1d(xr, ww.bfloat16().double().cpu(), bw.double().cpu(), padding="same", dilation=DIL).permute(0, 2, 1)
+    assert rel_fro(tc[1], ref) < 4e-3
+    assert rel_fro(tc[1][:, :24], ref[:, :24]) < 4e-3 and rel_fro(tc[1][:, -24:], ref[:, -24:]) < 4e-3
+
+
+def test_conv_pair_backward(pb):
+    from proteinbert_b200 import ops
+    x = rnd(B, L, C, seed=1).cuda().bfloat16()
+    zn, zw = rnd(B, L, C, seed=7).cuda().bfloat16(), rnd(B, L, C, seed=8).cuda().bfloat16()
+    du = rnd(B, L, C, scale=0.1, seed=9).cuda().bfloat16()
+    wn, ww = rnd(C, C, KS, scale=0.05, seed=2).cuda(), rnd(C, C, KS, scale=0.05, seed=3).cuda()
+    _, wn_b = ops.conv_pack(wn, 1)
+    _, ww_b = ops.conv_pack(ww, 1)
+
+    def run():
+        dzn, dzw, dx = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+        dWn, dWw = torch.empty(C, C, KS, device="cuda"), torch.empty(C, C, KS, device="cuda")
+        dbn, dbw, dg2l = torch.empty(C, device="cuda"), torch.empty(C, device="cuda"), torch.empty(B, C, device="cuda")
+        ops._call("pb_conv_pair_bwd", du.data_ptr(), zn.data_ptr(), zw.data_ptr(), x.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(),
+                  dzn.data_ptr(), dzw.data_ptr(), dx.data_ptr(), dWn.data_ptr(), dWw.data_ptr(), dbn.data_ptr(), dbw.data_ptr(),
+                  dg2l.data_ptr(), B, L, C, KS, DIL, 1, torch.cuda.current_stream().cuda_stream)
+        return dx, dWn, dWw, dbn, dbw, dg2l
+
+    simt, tc = both_engines(pb, run)
+    compare(["dx", "dWn", "dWw", "dbn", "dbw", "dg2l"], simt, tc)
+
+
+def test_local_linear(pb):
+    from proteinbert_b200 import ops
+    h = rnd(B, L, C, seed=1).cuda().bfloat16()
+    W = rnd(C, C, scale=0.1, seed=2).cuda()
+    bias = rnd(C, seed=3).cuda()
+    Ww, WTw = ops.to_wt(W, 1), ops.to_wt(W.t(), 1)
+    du2 = rnd(B, L, C, scale=0.1, seed=4).cuda().bfloat16()
+
+    def run():
+        z, u2 = torch.empty_like(h), torch.empty_like(h)
+        stats = torch.zeros(B, 2, dtype=torch.float64, device="cuda")
+        st = torch.cuda.current_stream().cuda_stream
+        ops._call("pb_local_linear_fwd", h.data_ptr(), Ww.data_ptr(), bias.data_ptr(), z.data_ptr(), u2.data_ptr(), stats.data_ptr(), B, L, C, 1, st)
+        dz, dh = torch.empty_like(h), torch.empty_like(h)
+        dW, db = torch.empty(C, C, device="cuda"), torch.empty(C, device="cuda")
+        ops._call("pb_local_linear_bwd", du2.data_ptr(), z.data_ptr(), h.data_ptr(), Ww.data_ptr(), WTw.data_ptr(), dz.data_ptr(),
+                  dh.data_ptr(), dW.data_ptr(), db.data_ptr(), B, L, C, 1, st)
+        return z, u2, stats, dh, dW, db
+
+    simt, tc = both_engines(pb, run)
+    compare(["z", "u2", "stats", "dh", "dW", "db"], simt, tc)
+
+
+def test_attention_pool(pb):
+    from proteinbert_b200 import ops
+    h = rnd(B, L, C, seed=1).cuda().bfloat16()
+    wv = rnd(C, G, scale=0.3, seed=2).cuda()
+    wvTw, wvw = ops.to_wt(wv.t(), 1), ops.to_wt(wv, 1)
+    dpool = rnd(B, G, scale=0.1, seed=3).cuda()
+    dh_in = rnd(B, L, C, scale=0.1, seed=4).cuda().bfloat16()
+
+    def run():
+        st = torch.cuda.current_stream().cuda_stream
+        pool = torch.empty(B, G, device="cuda")
+        ops._call("pb_attn_pool_fwd", h.data_ptr(), wvTw.data_ptr(), pool.data_ptr(), B, L, C, G, 1, st)
+        dzv = torch.empty(B * L, G, device="cuda", dtype=torch.bfloat16)
+        dh = torch.empty_like(h)
+        dWvT = torch.empty(G, C, device="cuda")
+        ops._call("pb_attn_pool_bwd", h.data_ptr(), wvTw.data_ptr(), wvw.data_ptr(), dpool.data_ptr(), dh_in.data_ptr(), dzv.data_ptr(),
+                  dh.data_ptr(), dWvT.data_ptr(), B, L, C, G, 1, st)
+        return pool, dzv, dh, dWvT
+
+    simt, tc = both_engines(pb, run)
+    compare(["pool", "dzv", "dh", "dWvT"], simt, tc)
+    ref = (torch.nn.functional.gelu(h.double().cpu() @ wvw.double().cpu())).sum(1)
+    assert rel_fro(tc[0], ref) < 2e-3
+
+
+def test_ln_apply_fast_path(pb):
+    from proteinbert_b200 import ops
+    u = rnd(B, L, C, seed=1).cuda().bfloat16()
+    gamma, beta = (1 + 0.2 * rnd(L, C, seed=2)).cuda(), (0.1 * rnd(L, C, seed=3)).cuda()
+    stats = torch.stack([u.double().sum((1, 2)), (u.double() ** 2).sum((1, 2))], 1).contiguous()
+    h = torch.empty_like(u)
+    ops._call("pb_ln_joint_apply", u.data_ptr(), stats.data_ptr(), gamma.data_ptr(), beta.data_ptr(), h.data_ptr(), B, L, C, 1e-5, 1,
+              torch.cuda.current_stream().cuda_stream)
+    ref = torch.nn.functional.layer_norm(u.double(), (L, C), gamma.double(), beta.double(), 1e-5)
+    assert rel_fro(h, ref) < 3e-3
