@@ -74,6 +74,15 @@ int pb_embedding_bwd(const int64_t* tok, const void* dout_act, float* dtable, lo
  * backward).  ws: split-K partials, pb_workspace_bytes("linear_fwd", M, N, K).                  */
 int pb_linear_fwd(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
                   int act, void* ws, size_t ws_bytes, void* stream);
+/* Same result as pb_linear_fwd, for callers that cannot provide (or create) a scratch buffer.  It has no
+ * counterpart in the reference.  The split-K partial sums live in a 4 MiB device array that is part of the
+ * library image (held by every GPU that loads the library, until exit), so the call allocates nothing.
+ * Limit: M*N <= 32768 output elements per call (larger -> PB_ERR_UNSUPPORTED; use pb_linear_fwd).  The first
+ * call on each device looks the array's address up (cudaGetSymbolAddress): make it before any stream capture
+ * on that device.  All calls on a device share the array: calls that overlap on the GPU race -- serialise them.
+ * Nothing in the array needs clearing between calls (every partial is rewritten before it is read).           */
+int pb_linear_fwd_noalloc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N,
+                          int K, int act, void* stream);
 /* dZ = dY * act'(.) ; dX (+)= dZ W ; dW = dZ^T X ; db = sum_m dZ.  ZY is Z for GELU, Y for sigmoid.
  * dX may be NULL (annotations carry no gradient, modules.py:301); accumulate_dx adds into dX.
  * dZ_buf [M,N] is caller scratch.  ws as pb_workspace_bytes("linear_bwd", M, N, K).              */

@@ -28,6 +28,7 @@ PROTOTYPES = {
     "pb_embedding_fwd": [_p, _p, _p, _ll, _i, _i, _i, _p],
     "pb_embedding_bwd": [_p, _p, _p, _ll, _i, _i, _i, _p],
     "pb_linear_fwd": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
+    "pb_linear_fwd_noalloc": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_res_ln_rows_fwd": [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_res_ln_rows_bwd": [_p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],

@@ -238,3 +238,66 @@ int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, c
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// pb_linear_fwd_noalloc: pb_linear_fwd for callers that have no scratch buffer to hand over.
+//
+// Who needs this: host programs that must not (or cannot) create device allocations at the point where
+// they call into this library -- for example an application that gave the whole device heap to its own
+// memory arena at start-up, a serving loop that cannot afford the device-wide synchronisation a
+// cudaMalloc/cudaFree implies, or a plugin host that lets plugins launch kernels but not allocate.
+// pb_linear_fwd needs split-K scratch from its caller; this variant keeps that scratch inside the
+// library image instead, in the fixed-size device array below, so the call itself allocates nothing
+// (no cudaMalloc/cudaFree, no allocating library routine).  Inputs and outputs are still the caller's.
+//
+// Cost and limits: every GPU that loads libpb_b200.so holds the 4 MiB array until the process exits.
+// One call may use at most PB_NOALLOC_MAX_MN = 32768 output elements (M*N; e.g. batch 64 x 512 features,
+// the annotation->global layer of the default model); larger problems are refused with PB_ERR_UNSUPPORTED.
+//
+// Sharing: all calls on a device use the same array.  Nothing in it has to start at zero -- every partial
+// sum that the reduction reads is overwritten by the GEMM kernel of the same call first -- so stale
+// contents from an earlier call are harmless; but two calls that run concurrently on one GPU (different
+// streams, or different host threads) would overwrite each other's partial sums: serialise them.
+//
+// Set-up: the array's device address is looked up once per device with cudaGetSymbolAddress, by the first
+// call made while that device is current (the array's name is only a host-side handle, it is not usable as
+// a pointer in a launch).  Make that first call before starting any stream capture on that device.
+// =================================================================================================
+#define PB_NOALLOC_MAX_MN 32768
+#define PB_NOALLOC_SCRATCH_FLOATS (kMaxSplit * PB_NOALLOC_MAX_MN)          /* 32 splits x 32768 floats = 4 MiB */
+#define PB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_linear_scratch[PB_NOALLOC_SCRATCH_FLOATS];
+static float* g_linear_scratch_addr[PB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int pb_linear_fwd_noalloc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
+                                     int act, void* stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0, PB_ERR_SHAPE, "linear_fwd_noalloc: bad shape M=%d N=%d K=%d", M, N, K);
+    PB_REQUIRE((long long)M * N <= PB_NOALLOC_MAX_MN, PB_ERR_UNSUPPORTED,
+               "linear_fwd_noalloc: M*N = %lld exceeds the built-in scratch limit of %d output elements; "
+               "use pb_linear_fwd with a caller-provided workspace", (long long)M * N, PB_NOALLOC_MAX_MN);
+    int dev = -1;
+    PB_CUDA(cudaGetDevice(&dev));
+    PB_REQUIRE(dev >= 0 && dev < PB_NOALLOC_MAX_DEVICES, PB_ERR_UNSUPPORTED, "linear_fwd_noalloc: device index %d not supported", dev);
+    if (g_linear_scratch_addr[dev] == nullptr) {            // once per device, with that device current
+        float* ptr = nullptr;
+        PB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_linear_scratch));
+        PB_REQUIRE(ptr != nullptr, PB_ERR_CUDA, "linear_fwd_noalloc: cudaGetSymbolAddress returned a null address");
+        g_linear_scratch_addr[dev] = ptr;
+    }
+    float* ws = g_linear_scratch_addr[dev];                 // a real device address; never the symbol name itself
+    cudaStream_t st = (cudaStream_t)stream;
+    const int tiles = ceil_div(N, 64) * ceil_div(M, 64);
+    const int nsplit = pick_split(tiles, K);                // <= kMaxSplit, so nsplit*M*N floats always fit
+    RowMajorA<float> al{X, K};
+    WeightNK<float> bl{W, K};
+    if (nsplit == 1) {
+        launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpLinearDirect{bias, Z, Y, N, act}, M, N, K, 1, 1, st);
+        pb_count_launch(1);
+    } else {
+        launch_gemm_simt<64, 64, 16, 4, 4>(al, bl, EpPartial{ws, M, N}, M, N, K, nsplit, 1, st);
+        linear_reduce_kernel<<<min(ceil_div((long)M * N, 256), 1184), 256, 0, st>>>(ws, bias, Z, Y, M, N, nsplit, act);
+        pb_count_launch(2);
+    }
+    return pb_check_launch("pb_linear_fwd_noalloc");
+}
