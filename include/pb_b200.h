@@ -109,11 +109,12 @@ int pb_conv_pair_fwd(const void* x_act, const void* wn_pack, const void* ww_pack
                      int ksize, int dil, int dt, void* stream);
 /* backward of the above given du: dzn = du*gelu'(zn), dzw = du*gelu'(zw) (scratch, act type),
  * dx = du + dgrad_n(dzn) + dgrad_w(dzw) (+ dx_extra when non-NULL), dWn/dWw [Co,Ci,k] float, dbn/dbw,
- * dg2l[b,c] = sum_l du.  wn_bwd/ww_bwd are bwd packs.                                            */
+ * dg2l[b,c] = sum_l du.  wn_bwd/ww_bwd are bwd packs.  ws: split-K partial tiles of the weight-gradient
+ * GEMMs, pb_workspace_bytes("wgrad", 0, 0, 0) bytes (NULL or too small: atomics are used instead).   */
 int pb_conv_pair_bwd(const void* du_act, const void* zn_act, const void* zw_act, const void* x_act,
                      const void* wn_bwd, const void* ww_bwd, void* dzn_act, void* dzw_act, void* dx_act,
                      float* dWn, float* dWw, float* dbn, float* dbw, float* dg2l, int B, int L, int C, int ksize,
-                     int dil, int dt, void* stream);
+                     int dil, int dt, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- a8/a10: LayerNorm over (L,C) jointly, affine [L,C] (modules.py:148-151,161-164,212,217) --- */
 int pb_ln_joint_stats(const void* u_act, double* stats, int B, int L, int C, int dt, void* stream);
@@ -131,7 +132,8 @@ int pb_local_linear_fwd(const void* h_act, const void* W_wt, const float* bias, 
  * the K-major operand of the tensor-core data-gradient GEMM); may be NULL, which selects the SIMT engine.   */
 int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_act, const void* W_wt, const void* Wt_wt,
                         void* dz_act,
-                        void* dh_act, float* dW, float* db, int B, int L, int C, int dt, void* stream);
+                        void* dh_act, float* dW, float* db, int B, int L, int C, int dt, void* ws, size_t ws_bytes,
+                        void* stream);
 
 /* ---- a11/a12: global attention (modules.py:21-92) under the reference's softmax axis ------------
  * pool[b,g] = sum_l gelu(h[b,l,:] . Wv_all[:,g]); the layer output is (sum W_parameter / K) * pool
@@ -142,8 +144,8 @@ int pb_attn_pool_fwd(const void* h_act, const void* wvT_wt, float* pool, int B, 
 /* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip).
  * wv_wt = Wv_all [C, G] (K-major operand of the tensor-core dh GEMM); NULL selects the SIMT engine.          */
 int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const void* wv_wt, const float* dpool, const void* dh_in_act,
-                     void* dzv_act, void* dh_out_act, float* dWvT, int B, int L, int C, int G, int dt,
-                     void* stream);
+                     void* dzv_act, void* dh_out_act, float* dWvT, int B, int L, int C, int G, int dt, void* ws,
+                     size_t ws_bytes, void* stream);
 
 /* ---- a15: token head, softmax over the BATCH axis (modules.py:277-284; nn.Softmax() on 3-D) ----- */
 int pb_token_head_fwd(const void* h_act, const float* Wo, const float* bo, float* p_local, int B, int L, int C,

@@ -33,14 +33,14 @@ PROTOTYPES = {
     "pb_res_ln_rows_fwd": [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_res_ln_rows_bwd": [_p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_conv_pair_fwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
-    "pb_conv_pair_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
+    "pb_conv_pair_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_ln_joint_stats": [_p, _p, _i, _i, _i, _i, _p],
     "pb_ln_joint_apply": [_p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
     "pb_ln_joint_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
     "pb_local_linear_fwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
-    "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_attn_pool_fwd": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
-    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_token_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_pretrain_loss": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],

@@ -344,16 +344,18 @@ int pb_conv_pair_fwd(const void* x, const void* wn, const void* ww, const float*
 
 int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void* x, const void* wn_bwd, const void* ww_bwd,
                      void* dzn, void* dzw, void* dx, float* dWn, float* dWw, float* dbn, float* dbw, float* dg2l, int B,
-                     int L, int C, int ksize, int dil, int dt, void* stream) {
+                     int L, int C, int ksize, int dil, int dt, void* ws, size_t ws_bytes, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && ksize > 0 && (ksize & 1) && dil > 0, PB_ERR_SHAPE, "conv_pair_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L, K = ksize * C, half = ksize / 2;
     PB_CUDA(cudaMemsetAsync(dbn, 0, C * sizeof(float), st));
     PB_CUDA(cudaMemsetAsync(dbw, 0, C * sizeof(float), st));
     PB_CUDA(cudaMemsetAsync(dg2l, 0, (size_t)B * C * sizeof(float), st));
-    PB_CUDA(cudaMemsetAsync(dWn, 0, (size_t)C * C * ksize * sizeof(float), st));
-    PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
     const bool tc = dt == PB_BF16 && pb_tc_conv_ok(B, L, C, ksize, dil);
+    if (!tc) {
+        PB_CUDA(cudaMemsetAsync(dWn, 0, (size_t)C * C * ksize * sizeof(float), st));
+        PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
+    }
     DISPATCH_DT(dt, {
         dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
         gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
@@ -362,7 +364,7 @@ int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void*
         if (tc) {
             int rc = pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st);
             if (rc) return rc;
-            rc = pb_tc_conv_wgrad(dzn, dzw, x, dWn, dWw, B, L, C, ksize, dil, st);
+            rc = pb_tc_conv_wgrad(dzn, dzw, x, dWn, dWw, B, L, C, ksize, dil, ws, ws_bytes, st);
             if (rc) return rc;
         } else {
             // data gradient: same implicit GEMM with the taps mirrored (sign = -1) and the [t][ci][co] pack
@@ -397,20 +399,20 @@ int pb_local_linear_fwd(const void* h, const void* W, const float* bias, void* z
 }
 
 int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const void* W, const void* Wt, void* dz, void* dh, float* dW, float* db,
-                        int B, int L, int C, int dt, void* stream) {
+                        int B, int L, int C, int dt, void* ws, size_t ws_bytes, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "local_linear_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
     PB_CUDA(cudaMemsetAsync(db, 0, C * sizeof(float), st));
-    PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
+    if (!tc) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     DISPATCH_DT(dt, {
         dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
         gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
             (const T*)du2, (const T*)z, (const T*)nullptr, (T*)dz, (T*)nullptr, (float*)nullptr, db, (float*)nullptr, L, C);
         pb_count_launch(1);
         if (tc) {
-            int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, st);
+            int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, ws, ws_bytes, st);
             if (rc) return rc;
         } else {
             // dh = du2 + dz W
@@ -433,13 +435,13 @@ int pb_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, 
 }
 
 int pb_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
-                     float* dWvT, int B, int L, int C, int G, int dt, void* stream) {
+                     float* dWvT, int B, int L, int C, int G, int dt, void* ws, size_t ws_bytes, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
-    if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
     if (dt == PB_BF16 && wv != nullptr && pb_tc_attn_ok(B, L, C, G))
-        return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, st);
+        return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, ws, ws_bytes, st);
+    if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
     DISPATCH_DT(dt, {
         gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
         gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);

@@ -15,13 +15,13 @@ int pb_tc_conv_pair_fwd(const void* x, const void* wn, const void* ww, const flo
 int pb_tc_conv_pair_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx,
                           int B, int L, int C, int ksize, int dil, cudaStream_t st);
 int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int C, int ksize,
-                     int dil, cudaStream_t st);
+                     int dil, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L,
                            int C, cudaStream_t st);
 int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* Wt, void* dh, float* dW, int B, int L,
-                           int C, cudaStream_t st);
+                           int C, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st);
 int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
-                        float* dWvT, int B, int L, int C, int G, cudaStream_t st);
+                        float* dWvT, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st);

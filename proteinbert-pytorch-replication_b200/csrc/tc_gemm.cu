@@ -191,13 +191,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 // weight-gradient GEMM: contraction over sequence positions, MN-major operands
 // ---------------------------------------------------------------------------------------------------------
 struct WgradParams {
-    float* out; long stride_m, stride_n, stride_t;     // out[m*stride_m + n*stride_n + t*stride_t] += D[m, n]
-    int L, dil, half;                                   // shift(t) = (t - half) * dil
+    float* out[2]; long stride_m, stride_n, stride_t;  // out[src][m*stride_m + n*stride_n + t*stride_t] += D[m, n]
+    int L, dil[2], half, ntaps;                         // blockIdx.y = src * ntaps + t ; shift = (t - half) * dil[src]
     int chunks_total, chunks_per_split;                 // 64-row chunks over all samples
+    float* ws;                                          // split-K partial tiles [split][y][tile][128][128], or NULL = atomics
 };
 
 __global__ void __launch_bounds__(kThreads, 2)
-tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant__ CUtensorMap mapQ, WgradParams wp, int tiles_n) {
+tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant__ CUtensorMap mapP1,
+                const __grid_constant__ CUtensorMap mapQ, WgradParams wp, int tiles_n) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
@@ -207,15 +209,17 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = (blockIdx.x / tiles_n) * kBM, n0 = (blockIdx.x % tiles_n) * kBN;
-    const int t = blockIdx.y;
-    const int shift = (t - wp.half) * wp.dil;
+    const int src = blockIdx.y / wp.ntaps;
+    const int t = blockIdx.y % wp.ntaps;
+    const int shift = (t - wp.half) * wp.dil[src];
+    const CUtensorMap* mapP = src == 0 ? &mapP0 : &mapP1;
     const int c_beg = blockIdx.z * wp.chunks_per_split;
     const int c_end = min(wp.chunks_total, c_beg + wp.chunks_per_split);
     const int n_iter = c_end - c_beg;
     const int chunks_per_sample = wp.L / 64;
 
     if (warp == 0 && lane == 0) {
-        tma_prefetch_desc(&mapP); tma_prefetch_desc(&mapQ);
+        tma_prefetch_desc(mapP); tma_prefetch_desc(&mapQ);
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         mbar_init(tmem_full_bar, 1);
         fence_barrier_init();
@@ -225,6 +229,11 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (n_iter <= 0 && wp.ws != nullptr && warp >= 2) {
+        // an empty split still owns a partial tile: write zeros so the reduction can read every slot
+        float* dst = wp.ws + ((((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * kBM) * kBN;
+        for (int i = threadIdx.x - 64; i < kBM * kBN / 4; i += 128) reinterpret_cast<float4*>(dst)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     if (n_iter > 0) {
         if (warp == 0) {
             if (lane == 0) {
@@ -237,8 +246,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant_
                     uint8_t* a_dst = smem + s * kStageBytes;
                     uint8_t* b_dst = a_dst + kBM * 64 * 2;
                     mbar_expect_tx(&full_bar[s], kStageBytes);
-                    tma_load_3d(a_dst, &mapP, &full_bar[s], m0, l0, b);
-                    tma_load_3d(a_dst + 8192, &mapP, &full_bar[s], m0 + 64, l0, b);
+                    tma_load_3d(a_dst, mapP, &full_bar[s], m0, l0, b);
+                    tma_load_3d(a_dst + 8192, mapP, &full_bar[s], m0 + 64, l0, b);
                     tma_load_3d(b_dst, &mapQ, &full_bar[s], n0, l0 + shift, b);
                     tma_load_3d(b_dst + 8192, &mapQ, &full_bar[s], n0 + 64, l0 + shift, b);
                 }
@@ -266,14 +275,22 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant_
             const int q = warp & 3;
             const int m = m0 + q * 32 + lane;
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+            float* wrow = wp.ws == nullptr ? nullptr
+                : wp.ws + ((((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * kBM + (q * 32 + lane)) * kBN;
+            float* outp = wp.out[src];
 #pragma unroll 1
             for (int ch = 0; ch < kBN / 32; ++ch) {
                 float acc[32];
                 tmem_ld32(taddr + ch * 32, acc);
+                if (wrow != nullptr) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    atomicAdd(wp.out + (size_t)m * wp.stride_m + (size_t)(n0 + ch * 32 + j) * wp.stride_n + (size_t)t * wp.stride_t,
-                              acc[j]);
+                    for (int v = 0; v < 8; ++v)
+                        reinterpret_cast<float4*>(wrow + ch * 32)[v] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        atomicAdd(outp + (size_t)m * wp.stride_m + (size_t)(n0 + ch * 32 + j) * wp.stride_n + (size_t)t * wp.stride_t, acc[j]);
+                }
             }
             tc_fence_before();
         }
@@ -282,6 +299,22 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP, const __grid_constant_
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc<kBN>(tmem_base);
+    }
+}
+
+// out[src][m, n, t] = sum over splits of the partial tiles (plain stores: every output element is written once)
+__global__ void wgrad_reduce_kernel(WgradParams wp, int tiles_m, int tiles_n, int ny, int splits) {
+    const long long total = (long long)ny * tiles_m * tiles_n * kBM * kBN;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int n = (int)(i % kBN);
+        const int m = (int)((i / kBN) % kBM);
+        const int tile = (int)((i / (kBM * kBN)) % (tiles_m * tiles_n));
+        const int y = (int)(i / ((long long)kBM * kBN * tiles_m * tiles_n));
+        float s = 0.f;
+        for (int k = 0; k < splits; ++k) s += wp.ws[(size_t)k * total + i];
+        const int src = y / wp.ntaps, t = y % wp.ntaps;
+        const int gm = (tile / tiles_n) * kBM + m, gn = (tile % tiles_n) * kBN + n;
+        wp.out[src][(size_t)gm * wp.stride_m + (size_t)gn * wp.stride_n + (size_t)t * wp.stride_t] = s;
     }
 }
 
@@ -314,12 +347,17 @@ int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, 
     return pb_check_launch(what);
 }
 
-// P [B, L, Mtot], Q [B, L, Ntot]  ->  out[m, n, t] += sum_{b,l} P[b,l,m] Q[b,l+shift(t),n]
-int launch_wgrad(const void* P, const void* Q, float* out, long stride_m, long stride_n, long stride_t, int B, int L, int Mtot,
-                 int Ntot, int ntaps, int dil, cudaStream_t st, const char* what) {
-    CUtensorMap mP, mQ;
+// P{0,1} [B, L, Mtot], Q [B, L, Ntot]  ->  out{0,1}[m, n, t] (+)= sum_{b,l} P[b,l,m] Q[b,l+shift(t),n]
+// With a workspace the split-K partial tiles are stored and reduced by a second kernel (out is overwritten);
+// without one they are accumulated with atomics into a zeroed `out`.
+int launch_wgrad(const void* P0, const void* P1, const void* Q, float* out0, float* out1, long stride_m, long stride_n,
+                 long stride_t, int B, int L, int Mtot, int Ntot, int ntaps, int dil0, int dil1, void* ws, size_t ws_bytes,
+                 cudaStream_t st, const char* what) {
+    CUtensorMap mP0, mP1, mQ;
     int rc;
-    if ((rc = make_act_map(&mP, P, B, L, Mtot, 64))) return rc;
+    const int nsrc = P1 != nullptr ? 2 : 1;
+    if ((rc = make_act_map(&mP0, P0, B, L, Mtot, 64))) return rc;
+    if ((rc = make_act_map(&mP1, nsrc == 2 ? P1 : P0, B, L, Mtot, 64))) return rc;
     if ((rc = make_act_map(&mQ, Q, B, L, Ntot, 64))) return rc;
     static bool attr_set = false;
     if (!attr_set) {
@@ -327,17 +365,30 @@ int launch_wgrad(const void* P, const void* Q, float* out, long stride_m, long s
         attr_set = true;
     }
     WgradParams wp;
-    wp.out = out; wp.stride_m = stride_m; wp.stride_n = stride_n; wp.stride_t = stride_t;
-    wp.L = L; wp.dil = dil; wp.half = ntaps / 2;
+    wp.out[0] = out0; wp.out[1] = out1; wp.stride_m = stride_m; wp.stride_n = stride_n; wp.stride_t = stride_t;
+    wp.L = L; wp.dil[0] = dil0; wp.dil[1] = dil1; wp.half = ntaps / 2; wp.ntaps = ntaps;
     wp.chunks_total = B * (L / 64);
-    const int tiles = (Mtot / kBM) * (Ntot / kBN) * ntaps;
-    int splits = (2 * 148 + tiles - 1) / tiles;
-    if (splits > wp.chunks_total) splits = wp.chunks_total;
+    const int tiles_m = Mtot / kBM, tiles_n = Ntot / kBN, ny = nsrc * ntaps;
+    const int tiles = tiles_m * tiles_n * ny;
+    // one resident wave: about one CTA per SM, at least 8 chunks (512 rows) per CTA
+    int splits = 148 / tiles;
     if (splits < 1) splits = 1;
+    if (splits > wp.chunks_total / 8) splits = wp.chunks_total / 8 > 0 ? wp.chunks_total / 8 : 1;
     wp.chunks_per_split = (wp.chunks_total + splits - 1) / splits;
     splits = (wp.chunks_total + wp.chunks_per_split - 1) / wp.chunks_per_split;
-    tc_wgrad_kernel<<<dim3((Mtot / kBM) * (Ntot / kBN), ntaps, splits), kThreads, kSmemBytes, st>>>(mP, mQ, wp, Ntot / kBN);
+    const size_t need = (size_t)splits * tiles * kBM * kBN * sizeof(float);
+    wp.ws = (ws != nullptr && ws_bytes >= need) ? (float*)ws : nullptr;
+    if (wp.ws == nullptr) {           // atomics path needs zeroed outputs
+        PB_CUDA(cudaMemsetAsync(out0, 0, (size_t)Mtot * stride_m * sizeof(float), st));
+        if (nsrc == 2) PB_CUDA(cudaMemsetAsync(out1, 0, (size_t)Mtot * stride_m * sizeof(float), st));
+    }
+    tc_wgrad_kernel<<<dim3(tiles_m * tiles_n, ny, splits), kThreads, kSmemBytes, st>>>(mP0, mP1, mQ, wp, tiles_n);
     pb_count_launch(1);
+    if (wp.ws != nullptr) {
+        const long long total = (long long)tiles * kBM * kBN;
+        wgrad_reduce_kernel<<<(int)min((long long)ceil_div(total, 256), 148LL * 8), 256, 0, st>>>(wp, tiles_m, tiles_n, ny, splits);
+        pb_count_launch(1);
+    }
     return pb_check_launch(what);
 }
 
@@ -347,11 +398,9 @@ bool pb_tc_linear_ok(int B, int L, int C) { return pb_tc_enabled() && C % 128 ==
 bool pb_tc_attn_ok(int B, int L, int C, int G) { return pb_tc_enabled() && C % 128 == 0 && G % 128 == 0 && L % 128 == 0 && B >= 1; }
 
 int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int C, int ksize,
-                     int dil, cudaStream_t st) {
-    // dW[co, ci, t] = sum_{b,l} dz[b,l,co] x[b,l+(t-half)*d,ci]   (dW zeroed by the caller)
-    int rc = launch_wgrad(dzn, x, dWn, (long)C * ksize, ksize, 1, B, L, C, C, ksize, 1, st, "tc_conv_wgrad(narrow)");
-    if (rc) return rc;
-    return launch_wgrad(dzw, x, dWw, (long)C * ksize, ksize, 1, B, L, C, C, ksize, dil, st, "tc_conv_wgrad(wide)");
+                     int dil, void* ws, size_t ws_bytes, cudaStream_t st) {
+    // dW[co, ci, t] = sum_{b,l} dz[b,l,co] x[b,l+(t-half)*d,ci]; both convolutions (2 x ksize taps) in one launch
+    return launch_wgrad(dzn, dzw, x, dWn, dWw, (long)C * ksize, ksize, 1, B, L, C, C, ksize, 1, dil, ws, ws_bytes, st, "tc_conv_wgrad");
 }
 
 int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L,
@@ -362,13 +411,13 @@ int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void
 }
 
 int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* Wt, void* dh, float* dW, int B, int L,
-                           int C, cudaStream_t st) {
+                           int C, void* ws, size_t ws_bytes, cudaStream_t st) {
     // dh = du2 + dz W   (B operand = W^T [C_in, C_out], K-major)   ;   dW[n, c] = sum_rows dz[row, n] h[row, c]
     GemmEpi ep{};
     ep.ldn = C; ep.L = L; ep.base = (const bf16*)du2; ep.out0 = (bf16*)dh;
     int rc = launch_gemm<EPI_ADD_STORE>(dz, Wt, ep, B * L, C, C, st, "tc_local_linear_bwd(dh)");
     if (rc) return rc;
-    return launch_wgrad(dz, h, dW, C, 1, 0, B, L, C, C, 1, 1, st, "tc_local_linear_bwd(dW)");
+    return launch_wgrad(dz, nullptr, h, dW, nullptr, C, 1, 0, B, L, C, C, 1, 1, 1, ws, ws_bytes, st, "tc_local_linear_bwd(dW)");
 }
 
 int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st) {
@@ -378,7 +427,7 @@ int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int 
 }
 
 int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv,
-                        void* dh_out, float* dWvT, int B, int L, int C, int G, cudaStream_t st) {
+                        void* dh_out, float* dWvT, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st) {
     GemmEpi e1{};
     e1.ldn = G; e1.L = L; e1.dpool = dpool; e1.out0 = (bf16*)dzv;
     int rc = launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
@@ -387,6 +436,6 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
     e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
     rc = launch_gemm<EPI_ADD_STORE>(dzv, wv, e2, B * L, C, G, st, "tc_attn_pool_bwd(dh)");
     if (rc) return rc;
-    if (dWvT) rc = launch_wgrad(dzv, h, dWvT, C, 1, 0, B, L, G, C, 1, 1, st, "tc_attn_pool_bwd(dWv)");
+    if (dWvT) rc = launch_wgrad(dzv, nullptr, h, dWvT, nullptr, C, 1, 0, B, L, G, C, 1, 1, 1, ws, ws_bytes, st, "tc_attn_pool_bwd(dWv)");
     return rc;
 }

@@ -71,6 +71,11 @@ def _workspace(nbytes: int, device) -> torch.Tensor:
     return buf
 
 
+def _wgrad_ws(device):
+    ws = _workspace(lib().pb_workspace_bytes(b"wgrad", 0, 0, 0), device)
+    return ws.data_ptr(), ws.numel()
+
+
 def to_wt(w: torch.Tensor, dt: int) -> torch.Tensor:
     """fp32 master weight -> the storage type the big contractions read (`wt` in pb_b200.h)."""
     w = w.contiguous()
@@ -249,7 +254,7 @@ class LocalTrackFn(torch.autograd.Function):
         dzv = torch.empty((B * L, G), dtype=adt, device=dev)
         dh2t = torch.empty_like(x)
         dWvT = f32(G, C) if head_grads else None
-        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, st)
+        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, *_wgrad_ws(dev), st)
         del dzv
         # LN2
         sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
@@ -261,7 +266,7 @@ class LocalTrackFn(torch.autograd.Function):
         dz2 = dh2t                      # reuse as scratch
         dh1 = torch.empty_like(x)
         dW2, db2 = f32(C, C), f32(C)
-        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, st)
+        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, *_wgrad_ws(dev), st)
         # LN1
         du1 = du2                       # du2 is dead after the linear backward
         dln1w, dln1b = f32(L, C), f32(L, C)
@@ -274,7 +279,7 @@ class LocalTrackFn(torch.autograd.Function):
         dbn, dbw = f32(C), f32(C)
         dg2l = f32(B, C)
         _call("pb_conv_pair_bwd", _p(du1), _p(zn), _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), _p(dx), _p(dWn),
-                                  _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, st)
+                                  _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, *_wgrad_ws(dev), st)
         return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, dWvT, None, None, None)
 
 
@@ -307,7 +312,7 @@ class AttnPoolFn(torch.autograd.Function):
         dh = torch.empty_like(h)
         dWvT = torch.empty((G, C), dtype=torch.float32, device=dev)
         _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(wvw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), B, L, C, G,
-                                     dt, _st())
+                                     dt, *_wgrad_ws(dev), _st())
         return dh, dWvT
 
 

@@ -41,6 +41,11 @@ def compare(names, simt, tc, tol_bf16=3e-3):
     assert not bad, bad
 
 
+def wsargs(pb):
+    from proteinbert_b200 import ops
+    return ops._wgrad_ws(torch.device("cuda", torch.cuda.current_device()))
+
+
 def rnd(*shape, scale=1.0, seed=0):
     g = torch.Generator().manual_seed(seed)
     return (torch.randn(*shape, generator=g) * scale)
@@ -85,7 +90,7 @@ def test_conv_pair_backward(pb):
         dbn, dbw, dg2l = torch.empty(C, device="cuda"), torch.empty(C, device="cuda"), torch.empty(B, C, device="cuda")
         ops._call("pb_conv_pair_bwd", du.data_ptr(), zn.data_ptr(), zw.data_ptr(), x.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(),
                   dzn.data_ptr(), dzw.data_ptr(), dx.data_ptr(), dWn.data_ptr(), dWw.data_ptr(), dbn.data_ptr(), dbw.data_ptr(),
-                  dg2l.data_ptr(), B, L, C, KS, DIL, 1, torch.cuda.current_stream().cuda_stream)
+                  dg2l.data_ptr(), B, L, C, KS, DIL, 1, *wsargs(pb), torch.cuda.current_stream().cuda_stream)
         return dx, dWn, dWw, dbn, dbw, dg2l
 
     simt, tc = both_engines(pb, run)
@@ -108,7 +113,7 @@ def test_local_linear(pb):
         dz, dh = torch.empty_like(h), torch.empty_like(h)
         dW, db = torch.empty(C, C, device="cuda"), torch.empty(C, device="cuda")
         ops._call("pb_local_linear_bwd", du2.data_ptr(), z.data_ptr(), h.data_ptr(), Ww.data_ptr(), WTw.data_ptr(), dz.data_ptr(),
-                  dh.data_ptr(), dW.data_ptr(), db.data_ptr(), B, L, C, 1, st)
+                  dh.data_ptr(), dW.data_ptr(), db.data_ptr(), B, L, C, 1, *wsargs(pb), st)
         return z, u2, stats, dh, dW, db
 
     simt, tc = both_engines(pb, run)
@@ -131,7 +136,7 @@ def test_attention_pool(pb):
         dh = torch.empty_like(h)
         dWvT = torch.empty(G, C, device="cuda")
         ops._call("pb_attn_pool_bwd", h.data_ptr(), wvTw.data_ptr(), wvw.data_ptr(), dpool.data_ptr(), dh_in.data_ptr(), dzv.data_ptr(),
-                  dh.data_ptr(), dWvT.data_ptr(), B, L, C, G, 1, st)
+                  dh.data_ptr(), dWvT.data_ptr(), B, L, C, G, 1, *wsargs(pb), st)
         return pool, dzv, dh, dWvT
 
     simt, tc = both_engines(pb, run)
