@@ -54,19 +54,29 @@ __global__ void partial_reduce_kernel(const float* __restrict__ ws, float* out, 
     }
 }
 
-// dZ = dY * act'(ZY); db[n] = sum_m dZ[m,n].  One thread per column n.
+// dZ = dY * act'(ZY); db[n] = sum_m dZ[m,n].  block = (32 columns, 8 row groups): the rows of a column are
+// split over threadIdx.y and combined through shared memory, so the dependent-load chain is M/8 long.
 __global__ void linear_dz_kernel(const float* __restrict__ dY, const float* __restrict__ ZY, float* __restrict__ dZ,
                                  float* __restrict__ db, int M, int N, int act) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= N) return;
+    __shared__ float part[8][33];
+    const int n = blockIdx.x * 32 + threadIdx.x;
     float s = 0.f;
-    for (int m = 0; m < M; ++m) {
-        const size_t i = (size_t)m * N + n;
-        const float g = dY[i] * (act == PB_ACT_NONE ? 1.f : act_bwd(act, ZY[i]));
-        dZ[i] = g;
-        s += g;
+    if (n < N) {
+        for (int m = threadIdx.y; m < M; m += 8) {
+            const size_t i = (size_t)m * N + n;
+            const float g = dY[i] * (act == PB_ACT_NONE ? 1.f : act_bwd(act, ZY[i]));
+            dZ[i] = g;
+            s += g;
+        }
     }
-    if (db) db[n] = s;
+    part[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && n < N && db) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += part[k][threadIdx.x];
+        db[n] = t;
+    }
 }
 
 int pick_split(int tiles, int K) {
@@ -185,7 +195,7 @@ int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float*
     PB_REQUIRE(dZ_buf != nullptr, PB_ERR_WORKSPACE, "linear_bwd: dZ_buf is required");
     PB_REQUIRE(act == PB_ACT_NONE || ZY != nullptr, PB_ERR_SHAPE, "linear_bwd: ZY required for act=%d", act);
     cudaStream_t st = (cudaStream_t)stream;
-    linear_dz_kernel<<<ceil_div(N, 128), 128, 0, st>>>(dY, ZY, dZ_buf, db, M, N, act);
+    linear_dz_kernel<<<ceil_div(N, 32), dim3(32, 8), 0, st>>>(dY, ZY, dZ_buf, db, M, N, act);
     pb_count_launch(1);
     if (dX) {
         // dX[m,k] = sum_n dZ[m,n] W[n,k]

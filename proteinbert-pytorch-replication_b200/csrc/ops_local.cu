@@ -275,6 +275,185 @@ __global__ void gelu_bwd_colsum_kernel(const T* __restrict__ dy, const T* __rest
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// vectorised (8 elements per thread) versions of the HBM-bound kernels, used whenever C % 8 == 0
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct V8;
+template <> struct V8<float> {
+    static __device__ __forceinline__ void ld(const float* p, float (&v)[8]) {
+        const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+    static __device__ __forceinline__ void st(float* p, const float (&v)[8]) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
+    static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_f(z); }
+};
+template <> struct V8<bf16> {
+    static __device__ __forceinline__ void ld(const bf16* p, float (&v)[8]) {
+        const uint4 r = *reinterpret_cast<const uint4*>(p);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+    }
+    // stores the rounded values and returns them in v (sums are taken of stored values)
+    static __device__ __forceinline__ void st(bf16* p, float (&v)[8]) {
+        uint4 r;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+            const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y;
+        }
+        *reinterpret_cast<uint4*>(p) = r;
+    }
+    static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_fast(z); }
+};
+__device__ __forceinline__ void ldf8(const float* p, float (&v)[8]) { V8<float>::ld(p, v); }
+
+// per-sample sums s1 = sum dy*gamma, s2 = sum dy*gamma*xhat.  grid = (chunks, B)
+template <typename T>
+__global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
+                                       const float* __restrict__ gamma, double* __restrict__ sums, long long n, float eps) {
+    __shared__ double red[32];
+    const int b = blockIdx.y;
+    const LnStat st = ln_stat(stats, b, (double)n, eps);
+    const long long nv = n / 8;
+    float s1 = 0.f, s2 = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+        float d[8], x[8], g[8];
+        V8<T>::ld(dy + (size_t)b * n + i * 8, d);
+        V8<T>::ld(u + (size_t)b * n + i * 8, x);
+        ldf8(gamma + i * 8, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float a = d[j] * g[j];
+            s1 += a;
+            s2 += a * ((x[j] - st.mean) * st.rstd);
+        }
+    }
+    const double d1 = block_sum((double)s1, red), d2 = block_sum((double)s2, red);
+    if (threadIdx.x == 0) { atomicAdd(&sums[2 * b], d1); atomicAdd(&sums[2 * b + 1], d2); }
+}
+
+// du = rstd*(dy*gamma - m1 - xhat*m2); dgamma/dbeta accumulated over this CTA's group of samples.
+// grid = (ceil(nv/256), groups); thread owns one 8-wide (l,c) vector and walks `per_group` samples.
+template <typename T>
+__global__ void ln_bwd_apply_vec_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
+                                        const float* __restrict__ gamma, const double* __restrict__ sums, T* __restrict__ du,
+                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int B, long long n, float eps,
+                                        int per_group, int use_atomics) {
+    extern __shared__ float prm[];       // [per_group][4]: mean, rstd, m1, m2
+    const int b0 = blockIdx.y * per_group;
+    const int nb = min(per_group, B - b0);
+    for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+        const LnStat st = ln_stat(stats, b0 + k, (double)n, eps);
+        prm[4 * k] = st.mean; prm[4 * k + 1] = st.rstd;
+        prm[4 * k + 2] = (float)(sums[2 * (b0 + k)] / (double)n);
+        prm[4 * k + 3] = (float)(sums[2 * (b0 + k) + 1] / (double)n);
+    }
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n / 8) return;
+    float g[8], ag[8], ab[8];
+    ldf8(gamma + i * 8, g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { ag[j] = 0.f; ab[j] = 0.f; }
+    for (int k = 0; k < nb; ++k) {
+        const size_t off = (size_t)(b0 + k) * n + i * 8;
+        float d[8], x[8], o[8];
+        V8<T>::ld(dy + off, d);
+        V8<T>::ld(u + off, x);
+        const float mean = prm[4 * k], rstd = prm[4 * k + 1], m1 = prm[4 * k + 2], m2 = prm[4 * k + 3];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float xh = (x[j] - mean) * rstd;
+            o[j] = rstd * (d[j] * g[j] - m1 - xh * m2);
+            ag[j] += d[j] * xh;
+            ab[j] += d[j];
+        }
+        V8<T>::st(du + off, o);
+    }
+    if (use_atomics) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { atomicAdd(&dgamma[i * 8 + j], ag[j]); atomicAdd(&dbeta[i * 8 + j], ab[j]); }
+    } else {
+        V8<float>::st(dgamma + i * 8, ag);
+        V8<float>::st(dbeta + i * 8, ab);
+    }
+}
+
+// dz = dy * gelu'(z) for one or two z tensors, plus per-sample column sums of dy and global column sums of dz.
+// block = 256 threads = (C/8) channel vectors x rows; grid = (row chunks, B).
+template <typename T>
+__global__ void gelu_bwd_colsum_vec_kernel(const T* __restrict__ dy, const T* __restrict__ z0, const T* __restrict__ z1,
+                                           T* __restrict__ dz0, T* __restrict__ dz1, float* __restrict__ dsample,
+                                           float* __restrict__ db0, float* __restrict__ db1, int L, int C) {
+    extern __shared__ float sm[];        // [3][C]
+    const int b = blockIdx.y;
+    const int vpr = C / 8;                        // vectors per row
+    const int rows_pb = blockDim.x / vpr;         // rows handled concurrently
+    const int tv = threadIdx.x % vpr, tr = threadIdx.x / vpr;
+    const int rows_per = (L + gridDim.x - 1) / gridDim.x;
+    const int l0 = blockIdx.x * rows_per, l1 = min(L, l0 + rows_per);
+    for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sm[i] = 0.f;
+    __syncthreads();
+    float sy[8], s0[8], s1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { sy[j] = 0.f; s0[j] = 0.f; s1[j] = 0.f; }
+    if (tr < rows_pb) {
+        for (int l = l0 + tr; l < l1; l += rows_pb) {
+            const size_t off = ((size_t)b * L + l) * C + tv * 8;
+            float d[8], z[8], o[8];
+            V8<T>::ld(dy + off, d);
+            V8<T>::ld(z0 + off, z);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sy[j] += d[j]; o[j] = d[j] * V8<T>::gelu_grad(z[j]); }
+            V8<T>::st(dz0 + off, o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s0[j] += o[j];
+            if (z1) {
+                V8<T>::ld(z1 + off, z);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = d[j] * V8<T>::gelu_grad(z[j]);
+                V8<T>::st(dz1 + off, o);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s1[j] += o[j];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            atomicAdd(&sm[tv * 8 + j], sy[j]);
+            atomicAdd(&sm[C + tv * 8 + j], s0[j]);
+            if (z1) atomicAdd(&sm[2 * C + tv * 8 + j], s1[j]);
+        }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        if (dsample) atomicAdd(&dsample[(size_t)b * C + c], sm[c]);
+        atomicAdd(&db0[c], sm[C + c]);
+        if (z1) atomicAdd(&db1[c], sm[2 * C + c]);
+    }
+}
+
+template <typename T>
+int launch_gelu_bwd_colsum(const void* dy, const void* z0, const void* z1, void* dz0, void* dz1, float* dsample, float* db0,
+                           float* db1, int B, int L, int C, cudaStream_t st) {
+    if (C % 8 == 0 && C / 8 <= 256 && 256 % (C / 8) == 0) {
+        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
+        gelu_bwd_colsum_vec_kernel<T><<<grid, 256, 3 * C * sizeof(float), st>>>((const T*)dy, (const T*)z0, (const T*)z1, (T*)dz0,
+                                                                               (T*)dz1, dsample, db0, db1, L, C);
+    } else {
+        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
+        gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>((const T*)dy, (const T*)z0, (const T*)z1, (T*)dz0,
+                                                                                   (T*)dz1, dsample, db0, db1, L, C);
+    }
+    pb_count_launch(1);
+    return PB_OK;
+}
+
 int split_for(int tiles, long K) {
     int s = 592 / (tiles > 0 ? tiles : 1);
     if (s < 1) s = 1;
@@ -314,10 +493,31 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
     cudaStream_t st = (cudaStream_t)stream;
     PB_CUDA(cudaMemsetAsync(sums, 0, (size_t)B * 2 * sizeof(double), st));
     const long long n = (long long)L * C;
-    DISPATCH_DT(dt, (ln_bwd_pass1_kernel<T><<<ceil_div(n, 128), 128, 4 * B * sizeof(float), st>>>(
-                        (const T*)dy, (const T*)u, stats, gamma, dgamma, dbeta, sums, B, L, C, eps)));
-    dim3 grid(max(1, min(ceil_div(n, 1024), 32)), B);
-    DISPATCH_DT(dt, (ln_bwd_pass2_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)u, stats, gamma, sums, (T*)du, L, C, eps)));
+    if (n % 8 == 0) {
+        const long long nv = n / 8;
+        // enough sample groups to put >= ~150k threads in flight
+        int groups = (int)((151552 + nv - 1) / nv);
+        if (groups > B) groups = B;
+        if (groups < 1) groups = 1;
+        const int per_group = (B + groups - 1) / groups;
+        groups = (B + per_group - 1) / per_group;
+        if (groups > 1) {
+            PB_CUDA(cudaMemsetAsync(dgamma, 0, n * sizeof(float), st));
+            PB_CUDA(cudaMemsetAsync(dbeta, 0, n * sizeof(float), st));
+        }
+        dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
+        dim3 g2((unsigned)ceil_div(nv, 256), groups);
+        DISPATCH_DT(dt, {
+            ln_bwd_sums_vec_kernel<T><<<g1, 256, 0, st>>>((const T*)dy, (const T*)u, stats, gamma, sums, n, eps);
+            ln_bwd_apply_vec_kernel<T><<<g2, 256, 4 * per_group * sizeof(float), st>>>(
+                (const T*)dy, (const T*)u, stats, gamma, sums, (T*)du, dgamma, dbeta, B, n, eps, per_group, groups > 1 ? 1 : 0);
+        });
+    } else {
+        DISPATCH_DT(dt, (ln_bwd_pass1_kernel<T><<<ceil_div(n, 128), 128, 4 * B * sizeof(float), st>>>(
+                            (const T*)dy, (const T*)u, stats, gamma, dgamma, dbeta, sums, B, L, C, eps)));
+        dim3 grid(max(1, min(ceil_div(n, 1024), 32)), B);
+        DISPATCH_DT(dt, (ln_bwd_pass2_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)u, stats, gamma, sums, (T*)du, L, C, eps)));
+    }
     pb_count_launch(2);
     return pb_check_launch("pb_ln_joint_bwd");
 }
@@ -357,10 +557,7 @@ int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void*
         PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
     }
     DISPATCH_DT(dt, {
-        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
-        gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
-            (const T*)du, (const T*)zn, (const T*)zw, (T*)dzn, (T*)dzw, dg2l, dbn, dbw, L, C);
-        pb_count_launch(1);
+        launch_gelu_bwd_colsum<T>(du, zn, zw, dzn, dzw, dg2l, dbn, dbw, B, L, C, st);
         if (tc) {
             int rc = pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st);
             if (rc) return rc;
@@ -407,10 +604,7 @@ int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const voi
     const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
     if (!tc) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     DISPATCH_DT(dt, {
-        dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
-        gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>(
-            (const T*)du2, (const T*)z, (const T*)nullptr, (T*)dz, (T*)nullptr, (float*)nullptr, db, (float*)nullptr, L, C);
-        pb_count_launch(1);
+        launch_gelu_bwd_colsum<T>(du2, z, nullptr, dz, nullptr, nullptr, db, nullptr, B, L, C, st);
         if (tc) {
             int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, ws, ws_bytes, st);
             if (rc) return rc;

@@ -132,7 +132,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) {
                     const bf16 z = __float2bfloat16_rn(acc[j] + __ldg(ep.bias + n0 + c0 + j));
                     oz[j] = z;
-                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_f(__bfloat162float(z)));
+                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_fast(__bfloat162float(z)));
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;
@@ -144,14 +144,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
             } else if (EPI == EPI_POOL_FWD) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) acc[j] = gelu_f(acc[j]);
+                for (int j = 0; j < 32; ++j) acc[j] = gelu_fast(acc[j]);
                 const float cs = warp_transpose_sum(acc, lane);
                 colsum[q * kBN + c0 + lane] = cs;
             } else if (EPI == EPI_POOL_DZ) {
                 __align__(16) bf16 od[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    od[j] = __float2bfloat16_rn(__ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + j) * gelu_grad_f(acc[j]));
+                    od[j] = __float2bfloat16_rn(__ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + j) * gelu_grad_fast(acc[j]));
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
                     *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(od)[v];
