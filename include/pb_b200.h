@@ -61,6 +61,18 @@ int pb_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
  *   fwd_pack [k][Co][Ci]  (forward / wgrad)  and  bwd_pack [k][Ci][Co] (data gradient), dtype dt. */
 int pb_conv_weight_pack(const float* w, void* fwd_pack, void* bwd_pack, int C, int k, int dt, void* stream);
 
+/* All per-step weight staging of the local track in ONE launch.  jobs_dev is a DEVICE array of n jobs:
+ *   kind 0: src float [d0, d1] -> dst0[r*ld0 + c] (cast) and dst1[c*ld1 + r] (transposed cast); either may be NULL
+ *   kind 1: src float [Co=d0, Ci=d1, k=d2] -> dst0 [k][Co][Ci] and dst1 [k][Ci][Co] (the two conv packs)
+ * destinations have type dt.  Used for the conv packs, W2 / W2^T and Wv_all / Wv_all^T of every block. */
+typedef struct pb_stage_desc {
+    const float* src;
+    void* dst0;
+    void* dst1;
+    int kind, d0, d1, d2, ld0, ld1, reserved;
+} pb_stage_desc;
+int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream);
+
 /* ---- a2: token embedding (modules.py:249-253,300; backward = embedding_dense_backward) ------ */
 int pb_embedding_fwd(const int64_t* tok, const float* table, void* out_act, long long n_tok, int C, int V,
                      int dt, void* stream);
@@ -109,7 +121,7 @@ int pb_conv_pair_fwd(const void* x_act, const void* wn_pack, const void* ww_pack
                      int ksize, int dil, int dt, void* stream);
 /* backward of the above given du: dzn = du*gelu'(zn), dzw = du*gelu'(zw) (scratch, act type),
  * dx = du + dgrad_n(dzn) + dgrad_w(dzw) (+ dx_extra when non-NULL), dWn/dWw [Co,Ci,k] float, dbn/dbw,
- * dg2l[b,c] = sum_l du.  wn_bwd/ww_bwd are bwd packs.  ws: split-K partial tiles of the weight-gradient
+ * dg2l[b,c] = sum_l du (dbn, dbw, dg2l are ACCUMULATED: zero on entry).  wn_bwd/ww_bwd are bwd packs.  ws: split-K partial tiles of the weight-gradient
  * GEMMs, pb_workspace_bytes("wgrad", 0, 0, 0) bytes (NULL or too small: atomics are used instead).   */
 int pb_conv_pair_bwd(const void* du_act, const void* zn_act, const void* zw_act, const void* x_act,
                      const void* wn_bwd, const void* ww_bwd, void* dzn_act, void* dzw_act, void* dx_act,
@@ -120,7 +132,8 @@ int pb_conv_pair_bwd(const void* du_act, const void* zn_act, const void* zw_act,
 int pb_ln_joint_stats(const void* u_act, double* stats, int B, int L, int C, int dt, void* stream);
 int pb_ln_joint_apply(const void* u_act, const double* stats, const float* gamma, const float* beta, void* h_act,
                       int B, int L, int C, float eps, int dt, void* stream);
-/* du, dgamma[L,C], dbeta[L,C] from dy; sums [B,2] double is caller scratch. */
+/* du, dgamma[L,C], dbeta[L,C] from dy; sums [B,2] double is caller scratch.  sums, dgamma and dbeta are
+ * ACCUMULATED into: zero on entry. */
 int pb_ln_joint_bwd(const void* dy_act, const void* u_act, const double* stats, const float* gamma, void* du_act,
                     float* dgamma, float* dbeta, double* sums, int B, int L, int C, float eps, int dt, void* stream);
 
@@ -128,7 +141,7 @@ int pb_ln_joint_bwd(const void* dy_act, const void* u_act, const double* stats, 
  * z = h W^T + b, u2 = h + gelu(z), stats2[b] += (sum, sumsq) of u2.  W is [C,C] of type wt.        */
 int pb_local_linear_fwd(const void* h_act, const void* W_wt, const float* bias, void* z_act, void* u2_act,
                         double* stats2, int B, int L, int C, int dt, void* stream);
-/* dz = du2*gelu'(z) (scratch), dh = du2 + dz W, dW = dz^T h, db = sum dz.  Wt_wt = W transposed ([C_in, C_out],
+/* dz = du2*gelu'(z) (scratch), dh = du2 + dz W, dW = dz^T h, db = sum dz (db ACCUMULATED: zero on entry).  Wt_wt = W transposed ([C_in, C_out],
  * the K-major operand of the tensor-core data-gradient GEMM); may be NULL, which selects the SIMT engine.   */
 int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_act, const void* W_wt, const void* Wt_wt,
                         void* dz_act,
@@ -138,7 +151,7 @@ int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_ac
 /* ---- a11/a12: global attention (modules.py:21-92) under the reference's softmax axis ------------
  * pool[b,g] = sum_l gelu(h[b,l,:] . Wv_all[:,g]); the layer output is (sum W_parameter / K) * pool
  * (Softmax(dim=1) over K identical query rows makes every weight exactly 1/K).
- * wvT is Wv_all transposed, [G, C], type wt.                                                       */
+ * wvT is Wv_all transposed, [G, C], type wt.  pool is ACCUMULATED into: zero on entry.                                                     */
 int pb_attn_pool_fwd(const void* h_act, const void* wvT_wt, float* pool, int B, int L, int C, int G, int dt,
                      void* stream);
 /* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip).

@@ -55,7 +55,48 @@ __global__ void conv_pack_kernel(const float* __restrict__ w, T* __restrict__ fw
     }
 }
 
+// One launch stages every weight of the local track: blockIdx.y walks a device table of jobs.
+//   kind 0: src [d0, d1] row-major -> dst0[r*ld0 + c] (copy/cast) and dst1[c*ld1 + r] (transposed copy/cast)
+//   kind 1: src [Co=d0, Ci=d1, k=d2] -> dst0 [k][Co][Ci], dst1 [k][Ci][Co]
+template <typename T>
+__global__ void stage_weights_kernel(const pb_stage_desc* __restrict__ jobs) {
+    const pb_stage_desc j = jobs[blockIdx.y];
+    T* d0 = (T*)j.dst0;
+    T* d1 = (T*)j.dst1;
+    if (j.kind == 0) {
+        const long long n = (long long)j.d0 * j.d1;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            const int r = (int)(i / j.d1), c = (int)(i % j.d1);
+            const float v = j.src[i];
+            if (d0) stf(d0, (size_t)r * j.ld0 + c, v);
+            if (d1) stf(d1, (size_t)c * j.ld1 + r, v);
+        }
+    } else {
+        const int C0 = j.d0, C1 = j.d1, k = j.d2;
+        const long long n = (long long)C0 * C1 * k;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+            const int t = (int)(i % k);
+            const int ci = (int)((i / k) % C1);
+            const int co = (int)(i / ((long long)k * C1));
+            const float v = j.src[i];
+            if (d0) stf(d0, ((size_t)t * C0 + co) * C1 + ci, v);
+            if (d1) stf(d1, ((size_t)t * C1 + ci) * C0 + co, v);
+        }
+    }
+}
+
 extern "C" {
+
+int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream) {
+    if (n <= 0) return PB_OK;
+    PB_REQUIRE(jobs_dev != nullptr, PB_ERR_SHAPE, "stage_weights: null job table");
+    dim3 grid(32, n);
+    if (dt == PB_F32) stage_weights_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);
+    else if (dt == PB_BF16) stage_weights_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);
+    else { pb_set_error("stage_weights: unknown dtype code %d", dt); return PB_ERR_UNSUPPORTED; }
+    pb_count_launch(1);
+    return pb_check_launch("pb_stage_weights");
+}
 
 int pb_version(void) { return 100; }
 const char* pb_last_error(void) { return g_err; }

@@ -491,7 +491,6 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
     PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "ln_joint_bwd: bad shape");
     PB_REQUIRE(B <= 4096, PB_ERR_SHAPE, "ln_joint_bwd: batch %d exceeds the 4096 supported per call", B);
     cudaStream_t st = (cudaStream_t)stream;
-    PB_CUDA(cudaMemsetAsync(sums, 0, (size_t)B * 2 * sizeof(double), st));
     const long long n = (long long)L * C;
     if (n % 8 == 0) {
         const long long nv = n / 8;
@@ -501,10 +500,6 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
         if (groups < 1) groups = 1;
         const int per_group = (B + groups - 1) / groups;
         groups = (B + per_group - 1) / per_group;
-        if (groups > 1) {
-            PB_CUDA(cudaMemsetAsync(dgamma, 0, n * sizeof(float), st));
-            PB_CUDA(cudaMemsetAsync(dbeta, 0, n * sizeof(float), st));
-        }
         dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
         dim3 g2((unsigned)ceil_div(nv, 256), groups);
         DISPATCH_DT(dt, {
@@ -548,9 +543,6 @@ int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void*
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && ksize > 0 && (ksize & 1) && dil > 0, PB_ERR_SHAPE, "conv_pair_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L, K = ksize * C, half = ksize / 2;
-    PB_CUDA(cudaMemsetAsync(dbn, 0, C * sizeof(float), st));
-    PB_CUDA(cudaMemsetAsync(dbw, 0, C * sizeof(float), st));
-    PB_CUDA(cudaMemsetAsync(dg2l, 0, (size_t)B * C * sizeof(float), st));
     const bool tc = dt == PB_BF16 && pb_tc_conv_ok(B, L, C, ksize, dil);
     if (!tc) {
         PB_CUDA(cudaMemsetAsync(dWn, 0, (size_t)C * C * ksize * sizeof(float), st));
@@ -600,7 +592,6 @@ int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const voi
     PB_REQUIRE(B > 0 && L > 0 && C > 0, PB_ERR_SHAPE, "local_linear_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
-    PB_CUDA(cudaMemsetAsync(db, 0, C * sizeof(float), st));
     const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
     if (!tc) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     DISPATCH_DT(dt, {
@@ -622,7 +613,6 @@ int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const voi
 int pb_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, int dt, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_fwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
-    PB_CUDA(cudaMemsetAsync(pool, 0, (size_t)B * G * sizeof(float), st));
     if (dt == PB_BF16 && pb_tc_attn_ok(B, L, C, G)) return pb_tc_attn_pool_fwd(h, wvT, pool, B, L, C, G, st);
     DISPATCH_DT(dt, gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPool{pool, L, G}, B * L, G, C, 1, 1, st));
     return pb_check_launch("pb_attn_pool_fwd");

@@ -126,12 +126,18 @@ class ProteinBERTBlock(nn.Module):
         lin = self.local_linear_layer[0]
         att = self.global_attention_layer
         g2l_lin = self.global_to_local_linear_layer[0]
+        dt = ops.dt_of(xl)
+        if getattr(self, "_prestaged", None) == dt:          # ProteinBERT.forward staged all blocks in one launch
+            staged, self._prestaged = self._staged, None
+        else:
+            staged = ops.stage_blocks(self, [self], dt)[0]
         g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                        # modules.py:208
         h, pool = ops.LocalTrackFn.apply(                                                      # :205-219
             xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
             self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
-            self.local_norm_2.weight, self.local_norm_2.bias, att.wv_all_t(),
-            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads)
+            self.local_norm_2.weight, self.local_norm_2.bias, staged,
+            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads,
+            *[hd.Wv_parameter for hd in att.global_attention_heads])
         gl1, gl2 = self.global_linear_layer_1[0], self.global_linear_layer_2[0]
         gh = ops.linear_act(g, gl1.weight, gl1.bias, ACT_GELU)                                  # :221
         g1 = ops.ResLnRowsFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224
@@ -199,7 +205,10 @@ class ProteinBERT(nn.Module):
         h = ops.EmbeddingFn.apply(x_local, self.local_embedding.weight, dt)                     # modules.py:300
         gin = self.global_linear_layer[0]
         g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU)                    # :301
-        for blk in self.proteinBERT_blocks:
+        blocks = list(self.proteinBERT_blocks)
+        ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
+        for blk in blocks:
+            blk._prestaged = dt
             h, g = blk.forward_channels_last(h, g)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
         p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284

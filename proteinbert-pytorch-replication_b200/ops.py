@@ -96,6 +96,70 @@ def conv_pack(w: torch.Tensor, dt: int):
     return fwd, bwd
 
 
+class StagedBlockWeights:
+    """Persistent staging buffers of one block's local-track weights in the `wt` storage type: the tap-major conv
+    packs, W2 / W2^T and Wv_all / Wv_all^T.  Filled every forward by ONE pb_stage_weights launch for all blocks
+    (see stage_blocks); the fp32 masters stay in the nn.Module."""
+
+    def __init__(self, block, dt):
+        nconv, wconv = block.local_narrow_conv_layer[0], block.local_wide_conv_layer[0]
+        lin = block.local_linear_layer[0]
+        heads = block.global_attention_layer.global_attention_heads
+        C, _, k = nconv.weight.shape
+        Dv = heads[0].Wv_parameter.shape[1]
+        G = Dv * len(heads)
+        dev, adt = nconv.weight.device, act_dtype(dt)
+        e = lambda *shape: torch.empty(shape, dtype=adt, device=dev)
+        self.dt = dt
+        self.wn_f, self.wn_b, self.ww_f, self.ww_b = e(k, C, C), e(k, C, C), e(k, C, C), e(k, C, C)
+        self.W2w, self.W2Tw = e(C, C), e(C, C)
+        self.wv, self.wvT = e(C, G), e(G, C)
+        self.srcs = [nconv.weight, wconv.weight, lin.weight] + [h.Wv_parameter for h in heads]
+        es = self.wv.element_size()
+        self.jobs = [(nconv.weight, self.wn_f.data_ptr(), self.wn_b.data_ptr(), 1, C, C, k, 0, 0),
+                     (wconv.weight, self.ww_f.data_ptr(), self.ww_b.data_ptr(), 1, C, C, k, 0, 0),
+                     (lin.weight, self.W2w.data_ptr(), self.W2Tw.data_ptr(), 0, C, C, 0, C, C)]
+        for h, head in enumerate(heads):
+            self.jobs.append((head.Wv_parameter, self.wv.data_ptr() + h * Dv * es, self.wvT.data_ptr() + h * Dv * C * es,
+                              0, C, Dv, 0, G, C))
+
+    def key(self):
+        return (self.dt,) + tuple(t.data_ptr() for t in self.srcs)
+
+
+_STAGE_DTYPE = [("src", "<u8"), ("dst0", "<u8"), ("dst1", "<u8"), ("kind", "<i4"), ("d0", "<i4"), ("d1", "<i4"),
+                ("d2", "<i4"), ("ld0", "<i4"), ("ld1", "<i4"), ("reserved", "<i4"), ("pad", "<i4")]   # 56 B = sizeof(pb_stage_desc)
+
+
+def stage_blocks(owner, blocks, dt):
+    """Stage the local-track weights of `blocks` with one kernel launch.  The device job table is cached on
+    `owner` and rebuilt only when a parameter's storage or the precision changes."""
+    import numpy as np
+    staged = []
+    for blk in blocks:
+        sw = getattr(blk, "_staged", None)
+        if sw is None or sw.key() != (dt,) + tuple(t.data_ptr() for t in sw.srcs):
+            sw = StagedBlockWeights(blk, dt)
+            blk._staged = sw
+        staged.append(sw)
+    key = tuple(sw.key() for sw in staged)
+    cache = getattr(owner, "_stage_table", None)
+    if cache is None or cache[0] != key:
+        rows = []
+        for sw in staged:
+            for (src, d0p, d1p, kind, a, b, c, ld0, ld1) in sw.jobs:
+                if not src.is_contiguous():
+                    raise _lib.PBError("parameters must be contiguous")
+                rows.append((src.data_ptr(), d0p, d1p, kind, a, b, c, ld0, ld1, 0, 0))
+        arr = np.array(rows, dtype=_STAGE_DTYPE)
+        table = torch.from_numpy(arr.view(np.uint8).copy()).to(staged[0].wv.device)
+        cache = (key, table, len(rows))
+        owner._stage_table = cache
+    _need_cuda(cache[1])
+    _call("pb_stage_weights", _p(cache[1]), cache[2], dt, _st())
+    return staged
+
+
 # ------------------------------------------------------------------------------------------------
 class EmbeddingFn(torch.autograd.Function):
     """nn.Embedding forward / embedding_dense_backward (modules.py:249-253,300)."""
@@ -203,24 +267,23 @@ class LocalTrackFn(torch.autograd.Function):
     -> pool[b,g] = sum_l gelu(h . Wv).  Returns (h2 [B,L,C] act, pool [B,G] f32)."""
 
     @staticmethod
-    def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, wvT, ksize, dil, head_grads):
+    def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, staged, ksize, dil, head_grads, *head_wv):
         _need_cuda(x, g2l, Wn)
         x = x.contiguous()
         dt = dt_of(x)
+        if staged.dt != dt:
+            raise _lib.PBError("activation dtype does not match the staged weights' precision")
         B, L, C = x.shape
-        G = wvT.shape[0]
+        G = staged.wvT.shape[0]
         L_ = lib()
         st = _st()
         dev = x.device
-        wn_f, wn_b = conv_pack(Wn, dt)
-        ww_f, ww_b = conv_pack(Ww, dt)
-        W2w = to_wt(W2, dt)
-        wvTw = to_wt(wvT, dt)
-        # transposed copies: the K-major operands of the tensor-core data-gradient GEMMs (bf16 mode only)
-        W2Tw = to_wt(W2.t(), dt) if dt == BF16 else None
-        wvw = to_wt(wvT.t(), dt) if dt == BF16 else None
-        stats1 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
-        stats2 = torch.zeros((B, 2), dtype=torch.float64, device=dev)
+        wn_f, wn_b, ww_f, ww_b = staged.wn_f, staged.wn_b, staged.ww_f, staged.ww_b
+        W2w, wvTw = staged.W2w, staged.wvT
+        # transposed copies: the K-major operands of the tensor-core data-gradient GEMMs
+        W2Tw, wvw = staged.W2Tw, staged.wv
+        stats = torch.zeros((2, B, 2), dtype=torch.float64, device=dev)
+        stats1, stats2 = stats[0], stats[1]
         zn, zw, u1, h1, z2, u2, h2 = (torch.empty_like(x) for _ in range(7))
         g2l = g2l.contiguous()
         _call("pb_conv_pair_fwd", _p(x), _p(wn_f), _p(ww_f), _p(bn), _p(bw), _p(g2l), _p(zn), _p(zw), _p(u1), _p(stats1),
@@ -228,16 +291,19 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_ln_joint_apply", _p(u1), _p(stats1), _p(ln1w), _p(ln1b), _p(h1), B, L, C, LN_EPS, dt, st)
         _call("pb_local_linear_fwd", _p(h1), _p(W2w), _p(b2), _p(z2), _p(u2), _p(stats2), B, L, C, dt, st)
         _call("pb_ln_joint_apply", _p(u2), _p(stats2), _p(ln2w), _p(ln2b), _p(h2), B, L, C, LN_EPS, dt, st)
-        pool = torch.empty((B, G), dtype=torch.float32, device=dev)
+        pool = torch.zeros((B, G), dtype=torch.float32, device=dev)
         _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
-        ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w, W2Tw, wvw)
-        ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads))
+        ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, ln1w, ln2w)
+        ctx.staged = staged
+        ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads), len(head_wv))
         return h2, pool
 
     @staticmethod
     def backward(ctx, dh2, dpool):
-        x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, wn_b, ww_b, W2w, wvTw, ln1w, ln2w, W2Tw, wvw = ctx.saved_tensors
-        B, L, C, G, ksize, dil, dt, head_grads = ctx.cfg
+        x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, ln1w, ln2w = ctx.saved_tensors
+        sw = ctx.staged
+        wn_b, ww_b, W2w, wvTw, W2Tw, wvw = sw.wn_b, sw.ww_b, sw.W2w, sw.wvT, sw.W2Tw, sw.wv
+        B, L, C, G, ksize, dil, dt, head_grads, n_heads = ctx.cfg
         L_ = lib()
         st = _st()
         dev = x.device
@@ -250,6 +316,16 @@ class LocalTrackFn(torch.autograd.Function):
         def f32(*shape):
             return torch.empty(shape, dtype=torch.float32, device=dev)
 
+        # every accumulated ("zero on entry") output of this backward lives in one arena cleared by one fill
+        n_acc = (4 * L * C + 3 * C + B * C + 3) // 4 * 4                 # keeps the double area 16-byte aligned
+        arena = torch.zeros(n_acc + 8 * B, dtype=torch.float32, device=dev)
+        dln1w, dln1b = arena[0:L * C].view(L, C), arena[L * C:2 * L * C].view(L, C)
+        dln2w, dln2b = arena[2 * L * C:3 * L * C].view(L, C), arena[3 * L * C:4 * L * C].view(L, C)
+        o = 4 * L * C
+        dbn, dbw, db2 = arena[o:o + C], arena[o + C:o + 2 * C], arena[o + 2 * C:o + 3 * C]
+        dg2l = arena[o + 3 * C:o + 3 * C + B * C].view(B, C)
+        sums_all = arena[n_acc:].view(torch.float64).view(2, B, 2)          # two [B,2] double scratch areas
+
         # attention pooling
         dzv = torch.empty((B * L, G), dtype=adt, device=dev)
         dh2t = torch.empty_like(x)
@@ -257,30 +333,30 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, *_wgrad_ws(dev), st)
         del dzv
         # LN2
-        sums = torch.empty((B, 2), dtype=torch.float64, device=dev)
         du2 = torch.empty_like(x)
-        dln2w, dln2b = f32(L, C), f32(L, C)
-        _call("pb_ln_joint_bwd", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(du2), _p(dln2w), _p(dln2b), _p(sums), B, L, C,
+        _call("pb_ln_joint_bwd", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(du2), _p(dln2w), _p(dln2b), _p(sums_all[0]), B, L, C,
                                  LN_EPS, dt, st)
         # local linear
         dz2 = dh2t                      # reuse as scratch
         dh1 = torch.empty_like(x)
-        dW2, db2 = f32(C, C), f32(C)
+        dW2 = f32(C, C)
         _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, *_wgrad_ws(dev), st)
         # LN1
         du1 = du2                       # du2 is dead after the linear backward
-        dln1w, dln1b = f32(L, C), f32(L, C)
-        _call("pb_ln_joint_bwd", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(du1), _p(dln1w), _p(dln1b), _p(sums), B, L, C,
+        _call("pb_ln_joint_bwd", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(du1), _p(dln1w), _p(dln1b), _p(sums_all[1]), B, L, C,
                                  LN_EPS, dt, st)
         # conv pair
         dzn, dzw = dz2, dh1             # both dead by now
         dx = torch.empty_like(x)
         dWn, dWw = f32(C, C, ksize), f32(C, C, ksize)
-        dbn, dbw = f32(C), f32(C)
-        dg2l = f32(B, C)
         _call("pb_conv_pair_bwd", _p(du1), _p(zn), _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), _p(dx), _p(dWn),
                                   _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, *_wgrad_ws(dev), st)
-        return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, dWvT, None, None, None)
+        if head_grads:
+            Dv = G // n_heads
+            dheads = tuple(dWvT[h * Dv:(h + 1) * Dv].t() for h in range(n_heads))
+        else:
+            dheads = (None,) * n_heads
+        return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, None, None, None, None) + dheads
 
 
 class AttnPoolFn(torch.autograd.Function):
@@ -295,7 +371,7 @@ class AttnPoolFn(torch.autograd.Function):
         G = wvT.shape[0]
         wvTw = to_wt(wvT, dt)
         wvw = to_wt(wvT.t(), dt) if dt == BF16 else None
-        pool = torch.empty((B, G), dtype=torch.float32, device=h.device)
+        pool = torch.zeros((B, G), dtype=torch.float32, device=h.device)
         _call("pb_attn_pool_fwd", _p(h), _p(wvTw), _p(pool), B, L, C, G, dt, _st())
         ctx.save_for_backward(h, wvTw, wvw)
         return pool

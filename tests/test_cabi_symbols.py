@@ -52,3 +52,17 @@ def test_python_prototypes_cover_the_header(libpath):
 def test_native_code_is_sm100a(libpath):
     out = subprocess.run(["cuobjdump", "-lelf", libpath], capture_output=True, text=True).stdout
     assert "sm_100a" in out
+
+
+def test_stage_desc_layout_matches_python_table():
+    """The numpy record the host builds must be byte-compatible with `struct pb_stage_desc`."""
+    import numpy as np
+    import proteinbert_b200 as pb
+
+    class Desc(ctypes.Structure):
+        _fields_ = [("src", ctypes.c_void_p), ("dst0", ctypes.c_void_p), ("dst1", ctypes.c_void_p)] + \
+                   [(n, ctypes.c_int) for n in ("kind", "d0", "d1", "d2", "ld0", "ld1", "reserved")]
+    dt = np.dtype(pb.ops._STAGE_DTYPE)
+    assert dt.itemsize == ctypes.sizeof(Desc) == 56
+    for name in ("src", "dst0", "dst1", "kind", "d0", "d1", "d2", "ld0", "ld1", "reserved"):
+        assert dt.fields[name][1] == getattr(Desc, name).offset, name

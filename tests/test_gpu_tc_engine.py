@@ -87,7 +87,7 @@ def test_conv_pair_backward(pb):
     def run():
         dzn, dzw, dx = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
         dWn, dWw = torch.empty(C, C, KS, device="cuda"), torch.empty(C, C, KS, device="cuda")
-        dbn, dbw, dg2l = torch.empty(C, device="cuda"), torch.empty(C, device="cuda"), torch.empty(B, C, device="cuda")
+        dbn, dbw, dg2l = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(B, C, device="cuda")   # accumulated outputs
         ops._call("pb_conv_pair_bwd", du.data_ptr(), zn.data_ptr(), zw.data_ptr(), x.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(),
                   dzn.data_ptr(), dzw.data_ptr(), dx.data_ptr(), dWn.data_ptr(), dWw.data_ptr(), dbn.data_ptr(), dbw.data_ptr(),
                   dg2l.data_ptr(), B, L, C, KS, DIL, 1, *wsargs(pb), torch.cuda.current_stream().cuda_stream)
@@ -111,7 +111,7 @@ def test_local_linear(pb):
         st = torch.cuda.current_stream().cuda_stream
         ops._call("pb_local_linear_fwd", h.data_ptr(), Ww.data_ptr(), bias.data_ptr(), z.data_ptr(), u2.data_ptr(), stats.data_ptr(), B, L, C, 1, st)
         dz, dh = torch.empty_like(h), torch.empty_like(h)
-        dW, db = torch.empty(C, C, device="cuda"), torch.empty(C, device="cuda")
+        dW, db = torch.empty(C, C, device="cuda"), torch.zeros(C, device="cuda")
         ops._call("pb_local_linear_bwd", du2.data_ptr(), z.data_ptr(), h.data_ptr(), Ww.data_ptr(), WTw.data_ptr(), dz.data_ptr(),
                   dh.data_ptr(), dW.data_ptr(), db.data_ptr(), B, L, C, 1, *wsargs(pb), st)
         return z, u2, stats, dh, dW, db
@@ -130,7 +130,7 @@ def test_attention_pool(pb):
 
     def run():
         st = torch.cuda.current_stream().cuda_stream
-        pool = torch.empty(B, G, device="cuda")
+        pool = torch.zeros(B, G, device="cuda")
         ops._call("pb_attn_pool_fwd", h.data_ptr(), wvTw.data_ptr(), pool.data_ptr(), B, L, C, G, 1, st)
         dzv = torch.empty(B * L, G, device="cuda", dtype=torch.bfloat16)
         dh = torch.empty_like(h)
