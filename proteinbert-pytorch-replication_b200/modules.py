@@ -98,6 +98,7 @@ class ProteinBERTBlock(nn.Module):
         self.wide_conv_dilation = wide_conv_dilation
         self.precision = precision
         self.head_grads = True          # the reference's autograd also fills the (unregistered) heads' .grad
+        self.fuse_global = os.environ.get("PB_B200_FUSE_GLOBAL", "0") == "1"   # 4-launch global track (ops_global_fused.cu)
 
         self.global_attention_layer = GlobalAttention(num_heads=num_heads, local_dim=local_dim, global_dim=global_dim,
                                                       value_dim=int(global_dim / num_heads), key_dim=key_dim, device=device)
@@ -131,14 +132,22 @@ class ProteinBERTBlock(nn.Module):
             staged, self._prestaged = self._staged, None
         else:
             staged = ops.stage_blocks(self, [self], dt)[0]
-        g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                        # modules.py:208
+        gl1, gl2 = self.global_linear_layer_1[0], self.global_linear_layer_2[0]
+        fused = self.fuse_global and ops.global_fused_ok(g.shape[0], g.shape[1], g2l_lin.weight.shape[0])
+        if fused:       # both linears that read the block's input g in one launch
+            g2l, gh = ops.GlobalPreFn.apply(g, g2l_lin.weight, g2l_lin.bias, gl1.weight, gl1.bias)   # :208, :221
+        else:
+            g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                    # modules.py:208
         h, pool = ops.LocalTrackFn.apply(                                                      # :205-219
             xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
             self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
             self.local_norm_2.weight, self.local_norm_2.bias, staged,
             self.conv_kernel_size, self.wide_conv_dilation, self.head_grads,
             *[hd.Wv_parameter for hd in att.global_attention_heads])
-        gl1, gl2 = self.global_linear_layer_1[0], self.global_linear_layer_2[0]
+        if fused:       # LN(g + gh + att), Linear+GELU, LN in one launch                       # :223-229
+            g2 = ops.GlobalPostFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias,
+                                        gl2.weight, gl2.bias, self.global_norm_2.weight, self.global_norm_2.bias)
+            return h, g2
         gh = ops.linear_act(g, gl1.weight, gl1.bias, ACT_GELU)                                  # :221
         g1 = ops.ResLnRowsFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224
         gh2 = ops.linear_act(g1, gl2.weight, gl2.bias, ACT_GELU)                                # :226

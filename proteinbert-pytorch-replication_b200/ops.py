@@ -261,6 +261,87 @@ class ResLnRowsFn(torch.autograd.Function):
         return dx, (dx if has_b else None), dc, dwp, dgamma, dbeta
 
 
+class GlobalPreFn(torch.autograd.Function):
+    """(g2l, gh) = (gelu(g W1^T + b1), gelu(g W3^T + b3)) in one launch (modules.py:208,221)."""
+
+    @staticmethod
+    def forward(ctx, g, W1, b1, W3, b3):
+        _need_cuda(g, W1, W3)
+        g = g.contiguous()
+        B, G = g.shape
+        C = W1.shape[0]
+        dev = g.device
+        zg = torch.empty((2, B, C), dtype=torch.float32, device=dev)
+        z3 = torch.empty((2, B, G), dtype=torch.float32, device=dev)
+        _call("pb_global_pre_fwd", _p(g), _p(W1), _p(b1), _p(W3), _p(b3), _p(zg[0]), _p(zg[1]), _p(z3[0]), _p(z3[1]),
+              B, G, C, _st())
+        ctx.save_for_backward(g, W1, W3, zg, z3)
+        return zg[1], z3[1]
+
+    @staticmethod
+    def backward(ctx, dg2l, dgh):
+        g, W1, W3, zg, z3 = ctx.saved_tensors
+        B, G = g.shape
+        C = W1.shape[0]
+        dev = g.device
+        dg2l = torch.zeros((B, C), dtype=torch.float32, device=dev) if dg2l is None else dg2l.contiguous()
+        dgh = torch.zeros((B, G), dtype=torch.float32, device=dev) if dgh is None else dgh.contiguous()
+        dg = torch.empty_like(g)
+        dW1, db1 = torch.empty_like(W1), torch.empty((C,), dtype=torch.float32, device=dev)
+        dW3, db3 = torch.empty_like(W3), torch.empty((G,), dtype=torch.float32, device=dev)
+        _call("pb_global_pre_bwd", _p(dg2l), _p(dgh), _p(zg[0]), _p(z3[0]), _p(g), _p(W1), _p(W3), _p(dg), _p(dW1), _p(db1),
+              _p(dW3), _p(db3), B, G, C, _st())
+        return dg, dW1, db1, dW3, db3
+
+
+_COUNTERS = {}
+
+
+def _counter(device):
+    c = _COUNTERS.get(device)
+    if c is None:
+        c = torch.zeros((16,), dtype=torch.int32, device=device)
+        _COUNTERS[device] = c
+    return c
+
+
+class GlobalPostFn(torch.autograd.Function):
+    """g2 = LN(g1 + gelu(g1 W4^T + b4)), g1 = LN(g + gh + (sum(Wp)/K) pool) in one launch (modules.py:92,223-229)."""
+
+    @staticmethod
+    def forward(ctx, g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2):
+        _need_cuda(g, gh, pool, W4)
+        g, gh, pool = g.contiguous(), gh.contiguous(), pool.contiguous()
+        B, G = g.shape
+        dev = g.device
+        buf = torch.empty((5, B, G), dtype=torch.float32, device=dev)      # g1, xhat1, z4, xhat2, g2
+        rstd = torch.empty((2, B), dtype=torch.float32, device=dev)
+        _call("pb_global_post_fwd", _p(g), _p(gh), _p(pool), _p(Wp), Wp.numel(), _p(gamma1), _p(beta1), _p(W4), _p(b4),
+              _p(gamma2), _p(beta2), _p(buf[0]), _p(buf[1]), _p(rstd[0]), _p(buf[2]), _p(buf[3]), _p(rstd[1]), _p(buf[4]),
+              _p(_counter(dev)), B, G, _st())
+        ctx.save_for_backward(pool, Wp, gamma1, W4, gamma2, buf, rstd)
+        return buf[4]
+
+    @staticmethod
+    def backward(ctx, dg2):
+        pool, Wp, gamma1, W4, gamma2, buf, rstd = ctx.saved_tensors
+        B, G = pool.shape
+        dev = pool.device
+        dg2 = dg2.contiguous()
+        out = torch.empty((3, B, G), dtype=torch.float32, device=dev)      # dg1 scratch, dx1, dpool
+        dWp = torch.empty_like(Wp)
+        vec = torch.empty((5, G), dtype=torch.float32, device=dev)         # dgamma1, dbeta1, db4, dgamma2, dbeta2
+        dW4 = torch.empty_like(W4)
+        _call("pb_global_post_bwd", _p(dg2), _p(gamma2), _p(buf[3]), _p(rstd[1]), _p(buf[2]), _p(buf[0]), _p(W4), _p(gamma1),
+              _p(buf[1]), _p(rstd[0]), _p(pool), _p(Wp), Wp.numel(), _p(out[0]), _p(out[1]), _p(out[2]), _p(dWp), _p(vec[0]),
+              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), _p(_counter(dev)), B, G, _st())
+        return out[1], out[1], out[2], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4]
+
+
+def global_fused_ok(B, G, C) -> bool:
+    return bool(lib().pb_global_fused_ok(B, G, C))
+
+
 class LocalTrackFn(torch.autograd.Function):
     """The local track of one ProteinBERTBlock plus the attention pooling it feeds
     (modules.py:205-219): conv pair + GELU + 4-way add -> joint LN -> Linear+GELU+residual -> joint LN
@@ -455,4 +536,4 @@ def linear_act(x, W, b, act):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]

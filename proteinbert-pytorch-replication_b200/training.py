@@ -34,6 +34,51 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None)
     return loss.detach()
 
 
+class GraphedPretrainStep:
+    """forward + loss + backward captured once in a CUDA graph and replayed per step.
+
+    The step is ~170 short kernel launches; issued one by one from Python they cost more host time than the GPU
+    needs to run them, so the public fast path is: copy the batch into static device buffers (one async H2D per
+    tensor, from pinned memory if the caller provides it), replay the graph, read the loss.  Gradients are
+    written to the parameters' static ``.grad`` tensors, ready for ``optimizer.step()``.  Single-GPU only (a
+    collective inside the captured region is not used); shapes are fixed at construction.
+
+        step = GraphedPretrainStep(model, X, Y, W)      # example batch fixes shapes / dtypes
+        loss = step(X, Y, W)                            # host or device tensors
+    """
+
+    def __init__(self, model, X, Y, W, warmup: int = 3):
+        dev = next(model.parameters()).device
+        self.model = model
+        self.device = dev
+        self.static = [t.to(dev).clone() for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])]
+        sx, sy, sw = self._dicts()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                pretraining_step(model, sx, sy, sw)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        for p in model.parameters():
+            p.grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = pretraining_step(model, sx, sy, sw)
+
+    def _dicts(self):
+        s = self.static
+        return ({"local": s[0], "global": s[1]}, {"local": s[2], "global": s[3]}, {"local": s[4], "global": s[5]})
+
+    def __call__(self, X, Y, W):
+        src = (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])
+        for dst, t in zip(self.static, src):
+            if t is not dst:
+                dst.copy_(t, non_blocking=True)
+        self.graph.replay()
+        return self.loss
+
+
 class GradAllReducer:
     """Data-parallel gradient averaging overlapped with backward.
 

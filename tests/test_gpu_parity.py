@@ -79,6 +79,19 @@ def test_golden_fp32_full_step(pb):
     check_fp32(grads, {k: torch.from_numpy(v) for k, v in gold["g64"].items()})
 
 
+def test_golden_fp32_fused_global_track(pb):
+    """Same step with the four-launch fused global-track kernels (ops_global_fused.cu) switched on."""
+    gold = load_model_golden()
+    cfg = {k: int(v) for k, v in gold["cfg"].items()}
+    model = build_model(pb, cfg, golden_params(gold), "fp32")
+    for blk in model.proteinBERT_blocks:
+        blk.fuse_global = True
+    p_local, p_global, loss, grads = run_step(pb, model, golden_batch(gold))
+    assert_close_rel(p_global, gold["out64"]["p_global"], 1e-4, what="p_global")
+    assert abs(float(loss) - float(gold["out64"]["loss"])) <= 1e-4 * abs(float(gold["out64"]["loss"]))
+    check_fp32(grads, {k: torch.from_numpy(v) for k, v in gold["g64"].items()})
+
+
 def test_golden_fp32_through_reference_style_loss(pb):
     """The reference loop applies torch's CrossEntropyLoss / BCELoss to the model outputs (utils.py:293-294);
     the drop-in must be differentiable through that route too."""
@@ -142,9 +155,12 @@ def wide_ref():
     return params, batch, model_oracle.loss_and_grads(p64, b64, attention="closed_form")
 
 
-def test_wide_fp32(pb, wide_ref):
+@pytest.mark.parametrize("fuse_global", [False, True])
+def test_wide_fp32(pb, wide_ref, fuse_global):
     params, batch, ref = wide_ref
     model = build_model(pb, WIDE, params, "fp32")
+    for blk in model.proteinBERT_blocks:
+        blk.fuse_global = fuse_global
     p_local, p_global, loss, grads = run_step(pb, model, batch)
     assert_close_rel(p_local, ref[0], 1e-4, what="p_local")
     assert_close_rel(p_global, ref[1], 1e-4, what="p_global")
