@@ -205,10 +205,11 @@ def main():
         step()
     barrier()
 
-    # ---- CUDA graph of the whole step (single GPU: no collective inside), the package's public fast path -------
+    # ---- CUDA graph of forward+loss+backward, the package's public fast path; for N > 1 every call adds the
+    #      flat-bucket gradient all-reduce (gather kernel, NCCL all-reduce, scatter kernel) after the replay ----------
     graph = None
     launches_per_step = None
-    if args.graph and world == 1:
+    if args.graph:
         try:
             n0 = pb.launch_count()
             graph = pb.GraphedPretrainStep(model, X, Y, W, warmup=1)
@@ -229,14 +230,16 @@ def main():
     n0 = pb.launch_count()
     e0.record()
     for _ in range(args.steps):
-        if graph is not None:
+        if graph is not None and world == 1:
             graph.graph.replay()
+        elif graph is not None:
+            graph(X, Y, W)               # replay + gradient bucket all-reduce
         else:
             step()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
-    launches = (launches_per_step * args.steps) if graph is not None else (pb.launch_count() - n0)
+    launches = ((launches_per_step + (2 if world > 1 else 0)) * args.steps) if graph is not None else (pb.launch_count() - n0)
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -73,6 +73,16 @@ typedef struct pb_stage_desc {
 } pb_stage_desc;
 int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream);
 
+/* Gradient bucket of the data-parallel step: gather n float tensors into one flat
+ * buffer (to_flat = 1) or scatter the buffer back, multiplied by `scale` (to_flat = 0), in one launch.  The
+ * reference is single-process; this serves the one exchange step of the batch-sharded path (NCCL all-reduce). */
+typedef struct pb_chunk_desc {
+    float* ptr;
+    long long offset; /* element offset inside the flat buffer */
+    long long numel;
+} pb_chunk_desc;
+int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream);
+
 /* ---- a2: token embedding (modules.py:249-253,300; backward = embedding_dense_backward) ------ */
 int pb_embedding_fwd(const int64_t* tok, const float* table, void* out_act, long long n_tok, int C, int V,
                      int dt, void* stream);

@@ -85,7 +85,36 @@ __global__ void stage_weights_kernel(const pb_stage_desc* __restrict__ jobs) {
     }
 }
 
+// flat <-> scattered copies of many float tensors in one launch (gradient bucket of the data-parallel step)
+__global__ void flat_copy_kernel(const pb_chunk_desc* __restrict__ chunks, float* __restrict__ flat, int to_flat, float scale) {
+    const pb_chunk_desc c = chunks[blockIdx.y];
+    float* t = c.ptr;
+    float* f = flat + c.offset;
+    const long long n4 = ((((uintptr_t)t | (uintptr_t)f) & 15) == 0) ? c.numel / 4 : 0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (to_flat) {
+        for (long long i = tid; i < n4; i += stride) reinterpret_cast<float4*>(f)[i] = reinterpret_cast<const float4*>(t)[i];
+        for (long long i = n4 * 4 + tid; i < c.numel; i += stride) f[i] = t[i];
+    } else {
+        for (long long i = tid; i < n4; i += stride) {
+            float4 v = reinterpret_cast<const float4*>(f)[i];
+            v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            reinterpret_cast<float4*>(t)[i] = v;
+        }
+        for (long long i = n4 * 4 + tid; i < c.numel; i += stride) t[i] = f[i] * scale;
+    }
+}
+
 extern "C" {
+
+int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream) {
+    if (n <= 0) return PB_OK;
+    PB_REQUIRE(chunks_dev != nullptr && flat != nullptr, PB_ERR_SHAPE, "flat_copy: null argument");
+    flat_copy_kernel<<<dim3(8, n), 256, 0, (cudaStream_t)stream>>>(chunks_dev, flat, to_flat, scale);
+    pb_count_launch(1);
+    return pb_check_launch("pb_flat_copy");
+}
 
 int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream) {
     if (n <= 0) return PB_OK;

@@ -34,14 +34,63 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None)
     return loss.detach()
 
 
+class FlatGradBucket:
+    """All registered gradients as ONE flat buffer: a gather kernel after backward, one NCCL all-reduce over
+    NVLink/NVSwitch, a scatter kernel that also applies 1/world.  Used by GraphedPretrainStep when the job is
+    data-parallel (the gradient tensors have fixed addresses once the step is captured)."""
+
+    def __init__(self, params, group=None):
+        import numpy as np
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.params = [p for p in params if p.requires_grad]
+        if any(p.grad is None for p in self.params):
+            raise RuntimeError("FlatGradBucket needs materialised .grad tensors (run one step first)")
+        dev = self.params[0].device
+        rows, off = [], 0
+        for p in self.params:
+            g = p.grad
+            if not g.is_contiguous() or g.dtype != torch.float32:
+                raise RuntimeError("gradients must be contiguous float32")
+            # big tensors are cut into 64k-element pieces so the one-launch copy spreads over the whole GPU
+            piece = 1 << 16
+            for s0 in range(0, g.numel(), piece):
+                rows.append((g.data_ptr() + 4 * s0, off + s0, min(piece, g.numel() - s0)))
+            off += (g.numel() + 3) // 4 * 4                      # keep every tensor 16-byte aligned in the bucket
+        self.numel = off
+        self.flat = torch.zeros((off,), dtype=torch.float32, device=dev)
+        arr = np.array(rows, dtype=[("ptr", "<u8"), ("offset", "<i8"), ("numel", "<i8")])
+        self.table = torch.from_numpy(arr.view(np.uint8).copy()).to(dev)
+        self.n = len(rows)
+        self._ptrs = [p.grad.data_ptr() for p in self.params]
+
+    def check(self):
+        if [p.grad.data_ptr() for p in self.params] != self._ptrs:
+            raise RuntimeError("gradient tensors moved since the bucket was built")
+
+    def gather(self):
+        ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 1, 1.0,
+                  torch.cuda.current_stream().cuda_stream)
+
+    def all_reduce(self):
+        if self.world > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+
+    def scatter(self):
+        ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 0, 1.0 / self.world,
+                  torch.cuda.current_stream().cuda_stream)
+
+
 class GraphedPretrainStep:
     """forward + loss + backward captured once in a CUDA graph and replayed per step.
 
     The step is ~170 short kernel launches; issued one by one from Python they cost more host time than the GPU
     needs to run them, so the public fast path is: copy the batch into static device buffers (one async H2D per
     tensor, from pinned memory if the caller provides it), replay the graph, read the loss.  Gradients are
-    written to the parameters' static ``.grad`` tensors, ready for ``optimizer.step()``.  Single-GPU only (a
-    collective inside the captured region is not used); shapes are fixed at construction.
+    written to the parameters' static ``.grad`` tensors, ready for ``optimizer.step()``.  Shapes are fixed at
+    construction.  Under torch.distributed (world > 1) the captured region ends with a gather of all 133
+    gradients into one flat bucket; each call then all-reduces the bucket (NCCL, outside the graph) and scatters
+    it back scaled by 1/world, so every rank ends the step with the averaged gradients.
 
         step = GraphedPretrainStep(model, X, Y, W)      # example batch fixes shapes / dtypes
         loss = step(X, Y, W)                            # host or device tensors
@@ -63,8 +112,12 @@ class GraphedPretrainStep:
         for p in model.parameters():
             p.grad = None
         self.graph = torch.cuda.CUDAGraph()
+        self.bucket = None
+        distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
         with torch.cuda.graph(self.graph):
             self.loss = pretraining_step(model, sx, sy, sw)
+        if distributed:            # the captured backward fixed the gradient addresses: build the flat bucket over them
+            self.bucket = FlatGradBucket(model.parameters())
 
     def _dicts(self):
         s = self.static
@@ -76,6 +129,10 @@ class GraphedPretrainStep:
             if t is not dst:
                 dst.copy_(t, non_blocking=True)
         self.graph.replay()
+        if self.bucket is not None:
+            self.bucket.gather()
+            self.bucket.all_reduce()
+            self.bucket.scatter()
         return self.loss
 
 
