@@ -125,8 +125,9 @@ int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, c
 /* ---- a7/a13/a14 fused: the global side of one block in four launches (all float) ----------------------------
  * pre  : zg = g W1^T + b1, g2l = gelu(zg) (modules.py:208) and z3 = g W3^T + b3, gh = gelu(z3) (:221) in one GEMM pass.
  * post : g1 = LN(g + gh + coef*pool) (:92,:223-224), z4 = g1 W4^T + b4, g2 = LN(g1 + gelu(z4)) (:226-229).
- * counter: one int, zero before the first call (the kernels leave it at zero).  pb_global_fused_ok says whether
- * the shapes are covered (G, C multiples of 8, G <= 1024); otherwise compose pb_linear_* and pb_res_ln_rows_*. */
+ * The post kernels are cooperative launches (row phases and column phases separated by a grid barrier; at most
+ * 148 CTAs).  pb_global_fused_ok says whether the shapes are covered (G, C multiples of 8, G <= 1024, G + C <=
+ * 1184); otherwise compose pb_linear_* and pb_res_ln_rows_*. */
 int pb_global_fused_ok(int B, int G, int C);
 int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const float* W3, const float* b3, float* zg,
                       float* g2l, float* z3, float* gh, int B, int G, int C, void* stream);
@@ -136,13 +137,13 @@ int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, cons
 int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const float* Wp, int Kdim,
                        const float* gamma1, const float* beta1, const float* W4, const float* b4, const float* gamma2,
                        const float* beta2, float* g1, float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2,
-                       float* g2, int* counter, int B, int G, void* stream);
-/* dg1_buf [B,G] is scratch; dx1 = d loss/d g (residual path) = d loss/d gh. */
+                       float* g2, int B, int G, void* stream);
+/* scratch3 [3,B,G] is scratch; dx1 = d loss/d g (residual path) = d loss/d gh. */
 int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2, const float* rstd2, const float* z4,
                        const float* g1, const float* W4, const float* gamma1, const float* xhat1, const float* rstd1,
-                       const float* pool, const float* Wp, int Kdim, float* dg1_buf, float* dx1, float* dpool,
+                       const float* pool, const float* Wp, int Kdim, float* scratch3, float* dx1, float* dpool,
                        float* dWp, float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2,
-                       float* dbeta2, int* counter, int B, int G, void* stream);
+                       float* dbeta2, int B, int G, void* stream);
 
 /* ---- a5/a6/a7: narrow + dilated Conv1d, GELU, 4-way add with the global broadcast ---------------
  * zn = conv(x, Wn, d=1)+bn, zw = conv(x, Ww, d=dil)+bw, u = x + gelu(zn) + gelu(zw) + g2l[b,:]

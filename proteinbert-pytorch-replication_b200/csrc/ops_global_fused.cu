@@ -8,22 +8,29 @@
 //                                          z4 = g1 W4^T + b4
 //                                          g2 = LN(g1 + gelu(z4))                (modules.py:226-229)
 //
-// Structure of every kernel: each CTA owns a slice of 8 output columns.  Whatever is row-wise and needed by
-// all slices (a LayerNorm of all rows, an activation derivative) is recomputed by every CTA into shared
-// memory, where it becomes the A operand [rows x K] of the CTA's small GEMM; what needs complete rows of a
-// GEMM result (the second LayerNorm, the first LayerNorm's backward) is done by the LAST CTA to finish
-// (threadfence + atomic ticket), so no grid-wide barrier or cooperative launch is needed.
+// Every kernel alternates between two decompositions of the same [B x G] problem:
+//   row phases    (LayerNorm forward/backward): one batch row per CTA, all 512 threads across its columns;
+//   column phases (the GEMMs): each CTA owns 8 output columns, stages all rows of the A operand in shared memory
+//                 ([rows x K] fp32) and contracts it against its [K x 8] weight slice.
+// Phases are separated by a cooperative grid barrier (the grids are <= 148 CTAs of one wave, launched with
+// cudaLaunchCooperativeKernel), so the row-wise results never have to be recomputed per column slice.
+#include <cooperative_groups.h>
 #include "common.cuh"
 #include "../../include/pb_b200.h"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
 constexpr int kNT = 8;            // output columns per CTA
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;
 constexpr float kEps = 1e-5f;
+constexpr int kQ = 2;             // row phases / dW row sweep: up to kQ * 512 = 1024 columns
 
-__device__ __forceinline__ int row_tile_of(int K) { return K <= 704 ? 64 : (K <= 1472 ? 32 : 16); }
-static int host_row_tile(int K) { return K <= 704 ? 64 : (K <= 1472 ? 32 : 16); }
+__host__ __device__ __forceinline__ int row_tile_of(int K) { return K <= 704 ? 64 : (K <= 1472 ? 32 : 16); }
+
+__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 ld4cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
 // ---- CTA-level product: out[r][j] = sum_k A_s[r*lda + k] * Bt_s[k*8 + j],  r < MT, j < 8, k < Kd ---------
 // thread (r = tid % MT, ks = tid / MT) accumulates the k = ks, ks + nks, ... slice; partials are combined through
@@ -35,6 +42,7 @@ __device__ __forceinline__ void cta_gemm8(const float* A_s, int lda, const float
 #pragma unroll
     for (int j = 0; j < kNT; ++j) acc[j] = 0.f;
     const float* a = A_s + (size_t)r * lda;
+#pragma unroll 8
     for (int k = ks; k < Kd; k += nks) {
         const float av = a[k];
         const float4 b0 = *reinterpret_cast<const float4*>(Bt_s + k * kNT);
@@ -58,32 +66,71 @@ __device__ __forceinline__ void cta_gemm8(const float* A_s, int lda, const float
     __syncthreads();
 }
 
-// Bt_s[k][j] = W[(n0 + j) * ldw + k]   (weight rows are the output columns: "X W^T")
-__device__ __forceinline__ void load_bt_rows(float* Bt_s, const float* __restrict__ W, int ldw, int n0, int nvalid, int Kd) {
-    for (int i = threadIdx.x; i < kNT * Kd; i += kThreads) {
-        const int j = i / Kd, k = i - j * Kd;
-        Bt_s[k * kNT + j] = j < nvalid ? W[(size_t)(n0 + j) * ldw + k] : 0.f;
+// Bt_s[k][j] = W[(n0 + j) * ldw + k]   (weight rows are the output columns: "X W^T").  Kd % 4 == 0, ldw % 4 == 0.
+__device__ __forceinline__ void load_bt_rows(float* Bt_s, const float* __restrict__ W, int ldw, int n0, int Kd) {
+    const int kv = Kd / 4, total = kNT * kv;
+#pragma unroll 2
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+        const int j = i / kv, k = (i - j * kv) * 4;
+        const float4 v = ld4(W + (size_t)(n0 + j) * ldw + k);
+        Bt_s[(k + 0) * kNT + j] = v.x; Bt_s[(k + 1) * kNT + j] = v.y;
+        Bt_s[(k + 2) * kNT + j] = v.z; Bt_s[(k + 3) * kNT + j] = v.w;
     }
 }
-// Bt_s[k][j] = W[k * ldw + c0 + j]     (weight columns are the output columns: "dZ W")
-__device__ __forceinline__ void load_bt_cols(float* Bt_s, const float* __restrict__ W, int ldw, int c0, int nvalid, int Kd) {
-    for (int i = threadIdx.x; i < kNT * Kd; i += kThreads) {
-        const int k = i / kNT, j = i - k * kNT;
-        Bt_s[i] = j < nvalid ? W[(size_t)k * ldw + c0 + j] : 0.f;
+// Bt_s[k][j] = W[k * ldw + c0 + j]     (weight columns are the output columns: "dZ W").  c0 % 8 == 0, ldw % 4 == 0.
+__device__ __forceinline__ void load_bt_cols(float* Bt_s, const float* __restrict__ W, int ldw, int c0, int Kd) {
+    const int total = Kd * 2;
+#pragma unroll 2
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+        const int k = i >> 1, h = (i & 1) * 4;
+        *reinterpret_cast<float4*>(Bt_s + k * kNT + h) = ld4(W + (size_t)k * ldw + c0 + h);
     }
 }
 
-// accumulate dW rows of this CTA's slice: acc[q][j] += sum_m D_s[m*8 + j] * X[(row0+m)*ldx + kcol], kcol = tid + q*256.
-// Rows are taken eight at a time with all global loads issued before the FMAs (latency is L2, ~600 cycles).
-template <int QMAX>
-__device__ __forceinline__ void dw_accumulate(float (&acc)[QMAX][kNT], const float* D_s, const float* __restrict__ X, int ldx,
+// Cooperative copy of rows [row0, row0 + mt) of a row-major [*, K] tensor into the shared tile (pitch lda), with an
+// optional element-wise transform of up to two sources; rows >= mt are zero-filled.  kCG: bypass L1 (data written
+// earlier in this kernel by other CTAs).
+template <int NSRC, bool kCG, class Combine>
+__device__ __forceinline__ void fill_tile(float* A_s, int lda, int MT, int mt, int K, const float* s0, const float* s1, size_t ld,
+                                          int row0, Combine combine) {
+    const int kv = K / 4, total = MT * kv;
+    constexpr int U = NSRC == 1 ? 8 : 4;
+    for (int base = threadIdx.x; base < total; base += kThreads * U) {
+        float4 v[U][2];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * kThreads;
+            const int r = i / kv, k = (i - r * kv) * 4;
+            if (i < total && r < mt) {
+                const size_t o = (size_t)(row0 + r) * ld + k;
+                v[u][0] = kCG ? ld4cg(s0 + o) : ld4(s0 + o);
+                if (NSRC == 2) v[u][1] = kCG ? ld4cg(s1 + o) : ld4(s1 + o);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = base + u * kThreads;
+            if (i < total) {
+                const int r = i / kv, k = (i - r * kv) * 4;
+                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < mt) o = combine(v[u][0], v[u][1]);
+                float* d = A_s + (size_t)r * lda + k;
+                d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w;
+            }
+        }
+    }
+}
+
+// dW rows of this CTA's slice: acc[q][j] += sum_m D_s[m*8 + j] * X[(row0+m)*ldx + kcol], kcol = tid + q*512.
+// Rows are taken eight at a time with all global loads issued before the FMAs.
+__device__ __forceinline__ void dw_accumulate(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
                                               int row0, int mt, int Kout) {
     for (int m0 = 0; m0 < mt; m0 += 8) {
-        float x[8][QMAX];
+        float x[8][kQ];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
-            for (int q = 0; q < QMAX; ++q) {
+            for (int q = 0; q < kQ; ++q) {
                 const int kc = threadIdx.x + q * kThreads;
                 x[i][q] = (m0 + i < mt && kc < Kout) ? __ldg(X + (size_t)(row0 + m0 + i) * ldx + kc) : 0.f;
             }
@@ -93,7 +140,7 @@ __device__ __forceinline__ void dw_accumulate(float (&acc)[QMAX][kNT], const flo
                 const float4 d0 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT);
                 const float4 d1 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT + 4);
 #pragma unroll
-                for (int q = 0; q < QMAX; ++q) {
+                for (int q = 0; q < kQ; ++q) {
                     const float xv = x[i][q];
                     acc[q][0] = fmaf(d0.x, xv, acc[q][0]); acc[q][1] = fmaf(d0.y, xv, acc[q][1]);
                     acc[q][2] = fmaf(d0.z, xv, acc[q][2]); acc[q][3] = fmaf(d0.w, xv, acc[q][3]);
@@ -104,53 +151,15 @@ __device__ __forceinline__ void dw_accumulate(float (&acc)[QMAX][kNT], const flo
         }
     }
 }
-
-// Cooperative fill of a [MT x K] shared tile (row pitch lda) from row-major global tensors, eight float4 per thread
-// in flight: F(row, k, i) returns the float4 of source i at (row, k..k+3); G(vals) combines them into the float4 to
-// store.  Rows >= mt are zero-filled.  K % 4 == 0.
-template <int NSRC, class Load, class Combine>
-__device__ __forceinline__ void fill_tile(float* A_s, int lda, int MT, int mt, int K, Load load, Combine combine) {
-    const int kv = K / 4, total = MT * kv;
-    constexpr int U = 4;
-    for (int base = threadIdx.x; base < total; base += kThreads * U) {
-        float4 v[U][NSRC];
+__device__ __forceinline__ void dw_store(const float (&acc)[kQ][kNT], float* __restrict__ dW, int ldw, int n0, int Kout) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int i = base + u * kThreads;
-            const int r = i / kv, k = (i - r * kv) * 4;
-            if (i < total && r < mt) {
-#pragma unroll
-                for (int sidx = 0; sidx < NSRC; ++sidx) v[u][sidx] = load(r, k, sidx);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int i = base + u * kThreads;
-            if (i < total) {
-                const int r = i / kv, k = (i - r * kv) * 4;
-                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r < mt) o = combine(v[u], r, k);
-                float* d = A_s + (size_t)r * lda + k;
-                d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w;
-            }
-        }
-    }
-}
-__device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
-__device__ __forceinline__ float4 ld4cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
-
-template <int QMAX>
-__device__ __forceinline__ void dw_store(const float (&acc)[QMAX][kNT], float* __restrict__ dW, int ldw, int n0, int nvalid, int Kout) {
-#pragma unroll
-    for (int q = 0; q < QMAX; ++q) {
+    for (int q = 0; q < kQ; ++q) {
         const int kc = threadIdx.x + q * kThreads;
         if (kc < Kout)
 #pragma unroll
-            for (int j = 0; j < kNT; ++j)
-                if (j < nvalid) dW[(size_t)(n0 + j) * ldw + kc] = acc[q][j];
+            for (int j = 0; j < kNT; ++j) dW[(size_t)(n0 + j) * ldw + kc] = acc[q][j];
     }
 }
-constexpr int kQ = 4;             // supports contraction-output widths up to 1024 per dW row
 
 __device__ __forceinline__ float coef_of(const float* __restrict__ Wp, int Kdim, float* red /* >= 32 */) {
     float t = 0.f;
@@ -158,23 +167,17 @@ __device__ __forceinline__ float coef_of(const float* __restrict__ Wp, int Kdim,
     return block_sum(t, red) / (float)Kdim;
 }
 
-// last-CTA ticket: returns true in every thread of the CTA that arrives last; resets the counter for reuse
-__device__ __forceinline__ bool last_cta_done(int* counter, int* flag_s) {
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const int ticket = atomicAdd(counter, 1);
-        *flag_s = (ticket == (int)gridDim.x - 1);
-        if (*flag_s) *counter = 0;
+struct MulGeluGrad4 {
+    __device__ float4 operator()(const float4 d, const float4 z) const {
+        return make_float4(d.x * gelu_grad_f(z.x), d.y * gelu_grad_f(z.y), d.z * gelu_grad_f(z.z), d.w * gelu_grad_f(z.w));
     }
-    __syncthreads();
-    const bool last = *flag_s != 0;
-    if (last) __threadfence();
-    return last;
-}
+};
+struct Copy4 {
+    __device__ float4 operator()(const float4 a, const float4) const { return a; }
+};
 
 // ============================================================================================================
-// pre forward:  [zg | z3] = g [W1 ; W3]^T + [b1 ; b3];  g2l = gelu(zg), gh = gelu(z3)
+// pre forward:  [zg | z3] = g [W1 ; W3]^T + [b1 ; b3];  g2l = gelu(zg), gh = gelu(z3)      (no row phase)
 // ============================================================================================================
 struct PreFwd {
     const float *g, *W1, *b1, *W3, *b3;
@@ -182,25 +185,23 @@ struct PreFwd {
     int B, G, C;
 };
 
-__global__ void __launch_bounds__(kThreads) global_pre_fwd_kernel(PreFwd p) {
+__global__ void __launch_bounds__(kThreads, 1) global_pre_fwd_kernel(PreFwd p) {
     extern __shared__ __align__(16) float sm[];
     const int K = p.G, MT = row_tile_of(K), lda = K + 1;
     float* A_s = sm;                                   // [MT][lda]
     float* Bt_s = A_s + (size_t)MT * lda;              // [K][8]
-    float* red_s = Bt_s + (size_t)K * kNT;             // [256/MT][MT][8] = [256*8]
+    float* red_s = Bt_s + (size_t)K * kNT;             // [512/MT][MT][8] = [512*8]
     const int n0 = blockIdx.x * kNT;                   // column in the concatenated [C + G] output
     const bool is_g2l = n0 < p.C;                      // slices never straddle (C % 8 == 0)
     const float* W = is_g2l ? p.W1 : p.W3;
     const float* bias = is_g2l ? p.b1 : p.b3;
     const int c0 = is_g2l ? n0 : n0 - p.C;
     const int ncols = is_g2l ? p.C : p.G;
-    load_bt_rows(Bt_s, W, K, c0, min(kNT, ncols - c0), K);
+    load_bt_rows(Bt_s, W, K, c0, K);
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<1>(A_s, lda, MT, mt, K,
-                     [&](int r, int k, int) { return ld4(p.g + (size_t)(row0 + r) * K + k); },
-                     [&](float4 (&v)[1], int, int) { return v[0]; });
+        fill_tile<1, false>(A_s, lda, MT, mt, K, p.g, nullptr, K, row0, Copy4());
         __syncthreads();
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, K, MT, red_s, out);
@@ -208,19 +209,20 @@ __global__ void __launch_bounds__(kThreads) global_pre_fwd_kernel(PreFwd p) {
             const int row = row0 + threadIdx.x;
             float* zo = (is_g2l ? p.zg : p.z3) + (size_t)row * ncols + c0;
             float* yo = (is_g2l ? p.g2l : p.gh) + (size_t)row * ncols + c0;
+            float z[kNT], y[kNT];
 #pragma unroll
-            for (int j = 0; j < kNT; ++j)
-                if (c0 + j < ncols) {
-                    const float z = out[j] + bias[c0 + j];
-                    zo[j] = z;
-                    yo[j] = gelu_f(z);
-                }
+            for (int j = 0; j < kNT; ++j) { z[j] = out[j] + bias[c0 + j]; y[j] = gelu_f(z[j]); }
+            *reinterpret_cast<float4*>(zo) = make_float4(z[0], z[1], z[2], z[3]);
+            *reinterpret_cast<float4*>(zo + 4) = make_float4(z[4], z[5], z[6], z[7]);
+            *reinterpret_cast<float4*>(yo) = make_float4(y[0], y[1], y[2], y[3]);
+            *reinterpret_cast<float4*>(yo + 4) = make_float4(y[4], y[5], y[6], y[7]);
         }
     }
 }
 
 // ============================================================================================================
 // pre backward: dzg = dg2l*gelu'(zg), dz3 = dgh*gelu'(z3);  dg = dz3 W3 + dzg W1;  dW3 = dz3^T g, dW1 = dzg^T g
+// (the activation derivative is element-wise, so it is applied while the A tile is staged: no row phase)
 // ============================================================================================================
 struct PreBwd {
     const float *dg2l, *dgh, *zg, *z3, *g, *W1, *W3;
@@ -228,23 +230,19 @@ struct PreBwd {
     int B, G, C;
 };
 
-__device__ __forceinline__ float4 mul_gelu_grad4(const float4 d, const float4 z) {
-    return make_float4(d.x * gelu_grad_f(z.x), d.y * gelu_grad_f(z.y), d.z * gelu_grad_f(z.z), d.w * gelu_grad_f(z.w));
-}
-
-__global__ void __launch_bounds__(kThreads) global_pre_bwd_kernel(PreBwd p) {
+__global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     extern __shared__ __align__(16) float sm[];
     const int G = p.G, C = p.C, KA = G + C, MT = row_tile_of(KA), lda = KA + 1;
     float* A_s = sm;                                   // [MT][lda] = [dz3 | dzg]
     float* Bt_s = A_s + (size_t)MT * lda;              // [KA][8]
-    float* red_s = Bt_s + (size_t)KA * kNT;            // [256*8]
+    float* red_s = Bt_s + (size_t)KA * kNT;            // [512*8]
     float* D_s = red_s + kThreads * kNT;               // [MT][8] slice of dz for the dW product
     // CTA i owns columns [8i, 8i+8) of dg (if < G) and rows [8i, 8i+8) of the stacked [dW3 ; dW1] matrix.
     const int n0 = blockIdx.x * kNT;                   // 0 .. G + C
     const bool has_dg = n0 < G;
     if (has_dg) {                                      // Bt = [W3[:, n0..] ; W1[:, n0..]]  (rows = contraction index)
-        load_bt_cols(Bt_s, p.W3, G, n0, min(kNT, G - n0), G);
-        load_bt_cols(Bt_s + (size_t)G * kNT, p.W1, G, n0, min(kNT, G - n0), C);
+        load_bt_cols(Bt_s, p.W3, G, n0, G);
+        load_bt_cols(Bt_s + (size_t)G * kNT, p.W1, G, n0, C);
     }
     const bool w_is_3 = n0 < G;
     const int wrow0 = w_is_3 ? n0 : n0 - G;
@@ -257,12 +255,8 @@ __global__ void __launch_bounds__(kThreads) global_pre_bwd_kernel(PreBwd p) {
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<2>(A_s, lda, MT, mt, G,
-                     [&](int r, int k, int i) { return ld4((i == 0 ? p.dgh : p.z3) + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[2], int, int) { return mul_gelu_grad4(v[0], v[1]); });
-        fill_tile<2>(A_s + G, lda, MT, mt, C,
-                     [&](int r, int k, int i) { return ld4((i == 0 ? p.dg2l : p.zg) + (size_t)(row0 + r) * C + k); },
-                     [&](float4 (&v)[2], int, int) { return mul_gelu_grad4(v[0], v[1]); });
+        fill_tile<2, false>(A_s, lda, MT, mt, G, p.dgh, p.z3, G, row0, MulGeluGrad4());
+        fill_tile<2, false>(A_s + G, lda, MT, mt, C, p.dg2l, p.zg, C, row0, MulGeluGrad4());
         __syncthreads();
         for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
             const int m = i / kNT, j = i - m * kNT;
@@ -271,149 +265,159 @@ __global__ void __launch_bounds__(kThreads) global_pre_bwd_kernel(PreBwd p) {
         __syncthreads();
         if (threadIdx.x < kNT)
             for (int m = 0; m < mt; ++m) colsum += D_s[m * kNT + threadIdx.x];
-        dw_accumulate<kQ>(accw, D_s, p.g, G, row0, mt, G);
+        dw_accumulate(accw, D_s, p.g, G, row0, mt, G);
         if (has_dg) {
             float out[kNT];
             cta_gemm8(A_s, lda, Bt_s, KA, MT, red_s, out);
             if (threadIdx.x < mt) {
                 float* o = p.dg + (size_t)(row0 + threadIdx.x) * G + n0;
-#pragma unroll
-                for (int j = 0; j < kNT; ++j)
-                    if (n0 + j < G) o[j] = out[j];
+                *reinterpret_cast<float4*>(o) = make_float4(out[0], out[1], out[2], out[3]);
+                *reinterpret_cast<float4*>(o + 4) = make_float4(out[4], out[5], out[6], out[7]);
             }
         }
     }
-    dw_store<kQ>(accw, w_is_3 ? p.dW3 : p.dW1, G, wrow0, kNT, G);
+    dw_store(accw, w_is_3 ? p.dW3 : p.dW1, G, wrow0, G);
     if (threadIdx.x < kNT) (w_is_3 ? p.db3 : p.db1)[wrow0 + threadIdx.x] = colsum;
 }
 
 // ============================================================================================================
-// post forward
+// post forward:  rows: g1 = LN(g + gh + coef*pool)  |  columns: z4 = g1 W4^T + b4  |  rows: g2 = LN(g1 + gelu(z4))
 // ============================================================================================================
 struct PostFwd {
     const float *g, *gh, *pool, *Wp, *gamma1, *beta1, *W4, *b4, *gamma2, *beta2;
     float *g1, *xhat1, *rstd1, *z4, *xhat2, *rstd2, *g2;
-    int* counter;
     int B, G, Kdim;
 };
 
-// LayerNorm of the rows of a shared tile, one warp per row, in place: a <- xhat*gamma + beta; optional global copies
-__device__ __forceinline__ void ln_rows_smem(float* A_s, int lda, int mt, int G, const float* __restrict__ gamma,
-                                             const float* __restrict__ beta, float* xhat_out, float* y_out, float* rstd_out,
-                                             int row0) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int r = warp; r < mt; r += kThreads / 32) {
-        float* a = A_s + (size_t)r * lda;
-        float s = 0.f;
-        for (int k = lane; k < G; k += 32) s += a[k];
-        const float mean = warp_sum(s) / (float)G;
-        float q = 0.f;
-        for (int k = lane; k < G; k += 32) { const float d = a[k] - mean; q += d * d; }
-        const float rstd = rsqrtf(warp_sum(q) / (float)G + kEps);
-        const size_t off = (size_t)(row0 + r) * G;
-        for (int k = lane; k < G; k += 32) {
-            const float xh = (a[k] - mean) * rstd;
-            const float y = xh * gamma[k] + beta[k];
-            a[k] = y;
-            if (xhat_out) { xhat_out[off + k] = xh; y_out[off + k] = y; }
-        }
-        if (rstd_out && lane == 0) rstd_out[row0 + r] = rstd;
+// LayerNorm of one row held as one value per (thread, i): v[i] is column threadIdx.x + i*512
+__device__ __forceinline__ void ln_row(float (&v)[kQ], int G, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       float* xhat_out, float* y_out, float* rstd_out, float* red) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kQ; ++i) s += v[i];
+    const float mean = block_sum(s, red) / (float)G;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < kQ; ++i) {
+        const int k = threadIdx.x + i * kThreads;
+        const float d = k < G ? v[i] - mean : 0.f;
+        q += d * d;
     }
+    const float rstd = rsqrtf(block_sum(q, red) / (float)G + kEps);
+#pragma unroll
+    for (int i = 0; i < kQ; ++i) {
+        const int k = threadIdx.x + i * kThreads;
+        if (k < G) {
+            const float xh = (v[i] - mean) * rstd;
+            xhat_out[k] = xh;
+            y_out[k] = xh * gamma[k] + beta[k];
+        }
+    }
+    if (threadIdx.x == 0) *rstd_out = rstd;
 }
 
-__global__ void __launch_bounds__(kThreads) global_post_fwd_kernel(PostFwd p) {
+__global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p) {
     extern __shared__ __align__(16) float sm[];
     __shared__ float red[32];
-    __shared__ int flag_s;
+    cg::grid_group grid = cg::this_grid();
     const int G = p.G, MT = row_tile_of(G), lda = G + 1;
     float* A_s = sm;                                   // [MT][lda]  g1 rows
     float* Bt_s = A_s + (size_t)MT * lda;              // [G][8]
-    float* red_s = Bt_s + (size_t)G * kNT;             // [256*8]
+    float* red_s = Bt_s + (size_t)G * kNT;             // [512*8]
     const int n0 = blockIdx.x * kNT;
+    load_bt_rows(Bt_s, p.W4, G, n0, G);
+    // ---- row phase: LayerNorm 1
     const float coef = coef_of(p.Wp, p.Kdim, red);
-    load_bt_rows(Bt_s, p.W4, G, n0, min(kNT, G - n0), G);
-    const bool writer = blockIdx.x == 0;
+    for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
+        const size_t off = (size_t)r * G;
+        float v[kQ];
+#pragma unroll
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            v[i] = k < G ? (p.g[off + k] + p.gh[off + k]) + coef * p.pool[off + k] : 0.f;
+        }
+        ln_row(v, G, p.gamma1, p.beta1, p.xhat1 + off, p.g1 + off, p.rstd1 + r, red);
+    }
+    grid.sync();
+    // ---- column phase: z4[:, n0..n0+7]
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        // LayerNorm 1 of every row of the tile, recomputed by every CTA (CTA 0 also publishes g1 / xhat1 / rstd1)
-        fill_tile<3>(A_s, lda, MT, mt, G,
-                     [&](int r, int k, int i) { return ld4((i == 0 ? p.g : (i == 1 ? p.gh : p.pool)) + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[3], int, int) {
-                         return make_float4(v[0].x + v[1].x + coef * v[2].x, v[0].y + v[1].y + coef * v[2].y,
-                                            v[0].z + v[1].z + coef * v[2].z, v[0].w + v[1].w + coef * v[2].w);
-                     });
-        __syncthreads();
-        ln_rows_smem(A_s, lda, mt, G, p.gamma1, p.beta1, writer ? p.xhat1 : nullptr, p.g1, writer ? p.rstd1 : nullptr, row0);
+        fill_tile<1, true>(A_s, lda, MT, mt, G, p.g1, nullptr, G, row0, Copy4());
         __syncthreads();
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);
         if (threadIdx.x < mt) {
             float* o = p.z4 + (size_t)(row0 + threadIdx.x) * G + n0;
-#pragma unroll
-            for (int j = 0; j < kNT; ++j)
-                if (n0 + j < G) o[j] = out[j] + p.b4[n0 + j];
+            const float4 b0 = ld4(p.b4 + n0), b1 = ld4(p.b4 + n0 + 4);
+            *reinterpret_cast<float4*>(o) = make_float4(out[0] + b0.x, out[1] + b0.y, out[2] + b0.z, out[3] + b0.w);
+            *reinterpret_cast<float4*>(o + 4) = make_float4(out[4] + b1.x, out[5] + b1.y, out[6] + b1.z, out[7] + b1.w);
         }
     }
-    // the last CTA to finish normalises g1 + gelu(z4) for all rows
-    if (!last_cta_done(p.counter, &flag_s)) return;
-    for (int row0 = 0; row0 < p.B; row0 += MT) {
-        const int mt = min(MT, p.B - row0);
-        __syncthreads();
-        fill_tile<2>(A_s, lda, MT, mt, G,
-                     [&](int r, int k, int i) { return ld4cg((i == 0 ? p.g1 : p.z4) + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[2], int, int) {
-                         return make_float4(v[0].x + gelu_f(v[1].x), v[0].y + gelu_f(v[1].y), v[0].z + gelu_f(v[1].z),
-                                            v[0].w + gelu_f(v[1].w));
-                     });
-        __syncthreads();
-        ln_rows_smem(A_s, lda, mt, G, p.gamma2, p.beta2, p.xhat2, p.g2, p.rstd2, row0);
+    grid.sync();
+    // ---- row phase: LayerNorm 2
+    for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
+        const size_t off = (size_t)r * G;
+        float v[kQ];
+#pragma unroll
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            v[i] = k < G ? __ldcg(p.g1 + off + k) + gelu_f(__ldcg(p.z4 + off + k)) : 0.f;
+        }
+        ln_row(v, G, p.gamma2, p.beta2, p.xhat2 + off, p.g2 + off, p.rstd2 + r, red);
     }
 }
 
 // ============================================================================================================
-// post backward (row tiles of 32: two shared arrays, the gradient rows and the matching xhat rows)
+// post backward:  rows: LN2 backward -> dx2, dz4 = dx2*gelu'(z4)
+//                 columns: dg1 = dx2 + dz4 W4 ; dW4 = dz4^T g1 ; db4, dgamma2, dbeta2
+//                 rows: LN1 backward -> dx1, dpool, dWp ;  columns (own 8): dgamma1, dbeta1
 // ============================================================================================================
 struct PostBwd {
     const float *dg2, *gamma2, *xhat2, *rstd2, *z4, *g1, *W4, *gamma1, *xhat1, *rstd1, *pool, *Wp;
-    float *dg1, *dx1, *dpool, *dWp, *dgamma1, *dbeta1, *dW4, *db4, *dgamma2, *dbeta2;
-    int* counter;
+    float *dg1, *dx2, *dz4, *dx1, *dpool, *dWp, *dgamma1, *dbeta1, *dW4, *db4, *dgamma2, *dbeta2;
     int B, G, Kdim;
 };
-constexpr int kMT2 = 32;
 
-// per-row means m1 = mean(d), m2 = mean(d * xh) over a shared tile (d already includes gamma when with_gamma == nullptr)
-__device__ __forceinline__ void row_means(const float* A_s, const float* X_s, int lda, int mt, int G, const float* __restrict__ gamma,
-                                          float* m_s) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int r = warp; r < mt; r += kThreads / 32) {
-        const float* a = A_s + (size_t)r * lda;
-        const float* x = X_s + (size_t)r * lda;
-        float s1 = 0.f, s2 = 0.f;
-        for (int k = lane; k < G; k += 32) {
-            const float d = gamma ? a[k] * gamma[k] : a[k];
-            s1 += d;
-            s2 += d * x[k];
-        }
-        s1 = warp_sum(s1); s2 = warp_sum(s2);
-        if (lane == 0) { m_s[2 * r] = s1 / (float)G; m_s[2 * r + 1] = s2 / (float)G; }
-    }
-}
-
-__global__ void __launch_bounds__(kThreads) global_post_bwd_kernel(PostBwd p) {
+__global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p) {
     extern __shared__ __align__(16) float sm[];
     __shared__ float red[32];
-    __shared__ int flag_s;
-    const int G = p.G, MT = kMT2, lda = G + 1;
-    float* A_s = sm;                                   // [32][lda]  d = dg2*gamma2, later dz4
-    float* X2_s = A_s + (size_t)MT * lda;              // [32][lda]  xhat rows
-    float* Bt_s = X2_s + (size_t)MT * lda;             // [G][8]     W4[:, n0..n0+7]
-    float* red_s = Bt_s + (size_t)G * kNT;             // [256*8]
-    float* D_s = red_s + kThreads * kNT;               // [32][8] dz4 slice
-    float* Xs_s = D_s + MT * kNT;                      // [32][8] dx2 slice (residual path)
-    float* m_s = Xs_s + MT * kNT;                      // [32][2]
+    cg::grid_group grid = cg::this_grid();
+    const int G = p.G, MT = row_tile_of(G), lda = G + 1;
+    float* A_s = sm;                                   // [MT][lda]  dz4 rows
+    float* Bt_s = A_s + (size_t)MT * lda;              // [G][8]     W4[:, n0..n0+7]
+    float* red_s = Bt_s + (size_t)G * kNT;             // [512*8]
+    float* D_s = red_s + kThreads * kNT;               // [MT][8] dz4 slice
     const int n0 = blockIdx.x * kNT;
-    load_bt_cols(Bt_s, p.W4, G, n0, min(kNT, G - n0), G);
+    load_bt_cols(Bt_s, p.W4, G, n0, G);
+    if (blockIdx.x == 0) for (int k = threadIdx.x; k < p.Kdim; k += kThreads) p.dWp[k] = 0.f;
+    // ---- row phase: LayerNorm-2 backward
+    for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
+        const size_t off = (size_t)r * G;
+        float d[kQ], xh[kQ];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            d[i] = k < G ? p.dg2[off + k] * p.gamma2[k] : 0.f;
+            xh[i] = k < G ? p.xhat2[off + k] : 0.f;
+            s1 += d[i];
+            s2 += d[i] * xh[i];
+        }
+        const float m1 = block_sum(s1, red) / (float)G, m2 = block_sum(s2, red) / (float)G;
+        const float rs = p.rstd2[r];
+#pragma unroll
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            if (k < G) {
+                const float dx2 = rs * (d[i] - m1 - xh[i] * m2);
+                p.dx2[off + k] = dx2;
+                p.dz4[off + k] = dx2 * gelu_grad_f(p.z4[off + k]);
+            }
+        }
+    }
+    grid.sync();
+    // ---- column phase
     float accw[kQ][kNT];
 #pragma unroll
     for (int q = 0; q < kQ; ++q)
@@ -423,41 +427,14 @@ __global__ void __launch_bounds__(kThreads) global_post_bwd_kernel(PostBwd p) {
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<1>(A_s, lda, MT, mt, G,
-                     [&](int r, int k, int) { return ld4(p.dg2 + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[1], int, int k) {
-                         const float4 gm = ld4(p.gamma2 + k);
-                         return make_float4(v[0].x * gm.x, v[0].y * gm.y, v[0].z * gm.z, v[0].w * gm.w);
-                     });
-        fill_tile<1>(X2_s, lda, MT, mt, G,
-                     [&](int r, int k, int) { return ld4(p.xhat2 + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[1], int, int) { return v[0]; });
-        __syncthreads();
-        row_means(A_s, X2_s, lda, mt, G, nullptr, m_s);
-        __syncthreads();
-        // dx2 = rstd2*(d - m1 - xhat2*m2); keep own columns of dx2; A <- dz4 = dx2 * gelu'(z4)
-        fill_tile<1>(A_s, lda, MT, mt, G,
-                     [&](int r, int k, int) { return ld4(p.z4 + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[1], int r, int k) {
-                         const float rs = p.rstd2[row0 + r], m1 = m_s[2 * r], m2 = m_s[2 * r + 1];
-                         const float* a = A_s + (size_t)r * lda + k;
-                         const float* x = X2_s + (size_t)r * lda + k;
-                         const float d0 = rs * (a[0] - m1 - x[0] * m2), d1 = rs * (a[1] - m1 - x[1] * m2);
-                         const float d2 = rs * (a[2] - m1 - x[2] * m2), d3 = rs * (a[3] - m1 - x[3] * m2);
-                         if (k >= n0 && k < n0 + kNT) {
-                             float* xs = Xs_s + r * kNT + (k - n0);
-                             xs[0] = d0; xs[1] = d1; xs[2] = d2; xs[3] = d3;
-                         }
-                         return make_float4(d0 * gelu_grad_f(v[0].x), d1 * gelu_grad_f(v[0].y), d2 * gelu_grad_f(v[0].z),
-                                            d3 * gelu_grad_f(v[0].w));
-                     });
+        fill_tile<1, true>(A_s, lda, MT, mt, G, p.dz4, nullptr, G, row0, Copy4());
         __syncthreads();
         for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
             const int m = i / kNT, j = i - m * kNT;
-            D_s[i] = (m < mt && n0 + j < G) ? A_s[(size_t)m * lda + n0 + j] : 0.f;
+            D_s[i] = A_s[(size_t)m * lda + n0 + j];
         }
         __syncthreads();
-        if (threadIdx.x < kNT && n0 + threadIdx.x < G) {
+        if (threadIdx.x < kNT) {
             const int c = n0 + threadIdx.x;
             for (int m = 0; m < mt; ++m) {
                 const size_t o = (size_t)(row0 + m) * G + c;
@@ -466,83 +443,72 @@ __global__ void __launch_bounds__(kThreads) global_post_bwd_kernel(PostBwd p) {
                 c_db2 += p.dg2[o];
             }
         }
-        dw_accumulate<kQ>(accw, D_s, p.g1, G, row0, mt, G);             // dW4[n0.., :] += dz4[:, n0..]^T g1
+        dw_accumulate(accw, D_s, p.g1, G, row0, mt, G);                 // dW4[n0.., :] += dz4[:, n0..]^T g1
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);                   // dz4 W4[:, n0..]
         if (threadIdx.x < mt) {
-            float* o = p.dg1 + (size_t)(row0 + threadIdx.x) * G + n0;
-#pragma unroll
-            for (int j = 0; j < kNT; ++j)
-                if (n0 + j < G) o[j] = out[j] + Xs_s[threadIdx.x * kNT + j];
+            const size_t o = (size_t)(row0 + threadIdx.x) * G + n0;
+            const float4 x0 = ld4cg(p.dx2 + o), x1 = ld4cg(p.dx2 + o + 4);
+            *reinterpret_cast<float4*>(p.dg1 + o) = make_float4(out[0] + x0.x, out[1] + x0.y, out[2] + x0.z, out[3] + x0.w);
+            *reinterpret_cast<float4*>(p.dg1 + o + 4) = make_float4(out[4] + x1.x, out[5] + x1.y, out[6] + x1.z, out[7] + x1.w);
         }
     }
-    dw_store<kQ>(accw, p.dW4, G, n0, min(kNT, G - n0), G);
-    if (threadIdx.x < kNT && n0 + threadIdx.x < G) {
+    dw_store(accw, p.dW4, G, n0, G);
+    if (threadIdx.x < kNT) {
         p.db4[n0 + threadIdx.x] = c_db4;
         p.dgamma2[n0 + threadIdx.x] = c_dg2;
         p.dbeta2[n0 + threadIdx.x] = c_db2;
     }
-    // the last CTA runs LayerNorm-1 backward over complete rows of dg1
-    if (!last_cta_done(p.counter, &flag_s)) return;
+    grid.sync();
+    // ---- row phase: LayerNorm-1 backward
     const float coef = coef_of(p.Wp, p.Kdim, red);
-    float cg[kQ], cb[kQ];                              // dgamma1 / dbeta1 of columns threadIdx.x + q*256
-#pragma unroll
-    for (int q = 0; q < kQ; ++q) { cg[q] = 0.f; cb[q] = 0.f; }
     float dcoef = 0.f;
-    for (int row0 = 0; row0 < p.B; row0 += MT) {
-        const int mt = min(MT, p.B - row0);
-        __syncthreads();
-        fill_tile<1>(A_s, lda, MT, mt, G, [&](int r, int k, int) { return ld4cg(p.dg1 + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[1], int, int) { return v[0]; });
-        fill_tile<1>(X2_s, lda, MT, mt, G, [&](int r, int k, int) { return ld4(p.xhat1 + (size_t)(row0 + r) * G + k); },
-                     [&](float4 (&v)[1], int, int) { return v[0]; });
-        __syncthreads();
-        row_means(A_s, X2_s, lda, mt, G, p.gamma1, m_s);
-        __syncthreads();
-        // column-wise: thread walks the tile's rows for its columns (shared memory, conflict-free)
+    for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
+        const size_t off = (size_t)r * G;
+        float d[kQ], xh[kQ];
+        float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-        for (int q = 0; q < kQ; ++q) {
-            const int k = threadIdx.x + q * kThreads;
-            if (k < G)
-                for (int r = 0; r < mt; ++r) {
-                    const float d = A_s[(size_t)r * lda + k];
-                    cg[q] += d * X2_s[(size_t)r * lda + k];
-                    cb[q] += d;
-                }
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            d[i] = k < G ? __ldcg(p.dg1 + off + k) * p.gamma1[k] : 0.f;
+            xh[i] = k < G ? p.xhat1[off + k] : 0.f;
+            s1 += d[i];
+            s2 += d[i] * xh[i];
         }
-        // element-wise: dx1, dpool, and the W_parameter coefficient
-        const int kv = G / 4, total = mt * kv;
-        for (int i = threadIdx.x; i < total; i += kThreads) {
-            const int r = i / kv, k = (i - r * kv) * 4;
-            const size_t o = (size_t)(row0 + r) * G + k;
-            const float4 pl = ld4(p.pool + o), gm = ld4(p.gamma1 + k);
-            const float rs = p.rstd1[row0 + r], m1 = m_s[2 * r], m2 = m_s[2 * r + 1];
-            const float* a = A_s + (size_t)r * lda + k;
-            const float* x = X2_s + (size_t)r * lda + k;
-            float4 dx;
-            dx.x = rs * (a[0] * gm.x - m1 - x[0] * m2); dx.y = rs * (a[1] * gm.y - m1 - x[1] * m2);
-            dx.z = rs * (a[2] * gm.z - m1 - x[2] * m2); dx.w = rs * (a[3] * gm.w - m1 - x[3] * m2);
-            *reinterpret_cast<float4*>(p.dx1 + o) = dx;
-            *reinterpret_cast<float4*>(p.dpool + o) = make_float4(coef * dx.x, coef * dx.y, coef * dx.z, coef * dx.w);
-            dcoef += dx.x * pl.x + dx.y * pl.y + dx.z * pl.z + dx.w * pl.w;
-        }
-    }
+        const float m1 = block_sum(s1, red) / (float)G, m2 = block_sum(s2, red) / (float)G;
+        const float rs = p.rstd1[r];
 #pragma unroll
-    for (int q = 0; q < kQ; ++q) {
-        const int k = threadIdx.x + q * kThreads;
-        if (k < G) { p.dgamma1[k] = cg[q]; p.dbeta1[k] = cb[q]; }
+        for (int i = 0; i < kQ; ++i) {
+            const int k = threadIdx.x + i * kThreads;
+            if (k < G) {
+                const float dx = rs * (d[i] - m1 - xh[i] * m2);
+                p.dx1[off + k] = dx;
+                p.dpool[off + k] = coef * dx;
+                dcoef += dx * p.pool[off + k];
+            }
+        }
     }
     const float tot = block_sum(dcoef, red) / (float)p.Kdim;
-    for (int k = threadIdx.x; k < p.Kdim; k += kThreads) p.dWp[k] = tot;
+    if (tot != 0.f)
+        for (int k = threadIdx.x; k < p.Kdim; k += kThreads) atomicAdd(&p.dWp[k], tot);
+    // ---- own columns: dgamma1 / dbeta1 (needs every row of dg1, complete since the barrier)
+    if (threadIdx.x < kNT) {
+        const int c = n0 + threadIdx.x;
+        float sg = 0.f, sb = 0.f;
+        for (int m = 0; m < p.B; ++m) {
+            const size_t o = (size_t)m * G + c;
+            const float dv = __ldcg(p.dg1 + o);
+            sg += dv * p.xhat1[o];
+            sb += dv;
+        }
+        p.dgamma1[c] = sg;
+        p.dbeta1[c] = sb;
+    }
 }
 
-size_t smem_bytes(int MT, int KA, bool with_slices) {
+size_t smem_bytes(int MT, int KA, bool with_slice) {
     size_t f = (size_t)MT * (KA + 1) + (size_t)KA * kNT + (size_t)kThreads * kNT;
-    if (with_slices) f += 2 * (size_t)MT * kNT;
-    return f * sizeof(float) + 64;
-}
-size_t smem_bytes_post_bwd(int G) {
-    const size_t f = 2 * (size_t)kMT2 * (G + 1) + (size_t)G * kNT + (size_t)kThreads * kNT + 2 * (size_t)kMT2 * kNT + 2 * kMT2;
+    if (with_slice) f += (size_t)MT * kNT;
     return f * sizeof(float) + 64;
 }
 
@@ -558,17 +524,16 @@ extern "C" {
 
 int pb_global_fused_ok(int B, int G, int C) {
     if (B < 1 || G < 8 || C < 8 || G % 8 || C % 8) return 0;
-    if (G > 1024 || G + C > 2048) return 0;                       // dW rows: up to kQ*256 columns per thread sweep
-    if (G % 4 || C % 4) return 0;
-    if (smem_bytes(host_row_tile(G + C), G + C, true) > 220 * 1024) return 0;
-    if (smem_bytes_post_bwd(G) > 220 * 1024) return 0;
+    if (G > kQ * kThreads) return 0;                              // row phases: kQ values per thread
+    if ((G + C) / kNT > 148) return 0;                            // cooperative kernels: one resident wave
+    if (smem_bytes(row_tile_of(G + C), G + C, true) > 220 * 1024) return 0;
     return 1;
 }
 
 int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const float* W3, const float* b3, float* zg, float* g2l,
                       float* z3, float* gh, int B, int G, int C, void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, C), PB_ERR_UNSUPPORTED, "global_pre_fwd: shape B=%d G=%d C=%d not covered", B, G, C);
-    const size_t smem = smem_bytes(host_row_tile(G), G, false);
+    const size_t smem = smem_bytes(row_tile_of(G), G, false);
     int rc = set_smem(global_pre_fwd_kernel, smem);
     if (rc) return rc;
     PreFwd p{g, W1, b1, W3, b3, zg, g2l, z3, gh, B, G, C};
@@ -581,7 +546,7 @@ int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, cons
                       const float* W3, float* dg, float* dW1, float* db1, float* dW3, float* db3, int B, int G, int C,
                       void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, C), PB_ERR_UNSUPPORTED, "global_pre_bwd: shape B=%d G=%d C=%d not covered", B, G, C);
-    const size_t smem = smem_bytes(host_row_tile(G + C), G + C, true);
+    const size_t smem = smem_bytes(row_tile_of(G + C), G + C, true);
     int rc = set_smem(global_pre_bwd_kernel, smem);
     if (rc) return rc;
     PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C};
@@ -592,32 +557,37 @@ int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, cons
 
 int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const float* Wp, int Kdim, const float* gamma1,
                        const float* beta1, const float* W4, const float* b4, const float* gamma2, const float* beta2, float* g1,
-                       float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2, float* g2, int* counter, int B, int G,
+                       float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2, float* g2, int B, int G,
                        void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, 8), PB_ERR_UNSUPPORTED, "global_post_fwd: shape B=%d G=%d not covered", B, G);
-    PB_REQUIRE(counter != nullptr && Kdim > 0, PB_ERR_SHAPE, "global_post_fwd: counter / Kdim missing");
-    const size_t smem = smem_bytes(host_row_tile(G), G, false);
+    PB_REQUIRE(Kdim > 0, PB_ERR_SHAPE, "global_post_fwd: Kdim missing");
+    const size_t smem = smem_bytes(row_tile_of(G), G, false);
     int rc = set_smem(global_post_fwd_kernel, smem);
     if (rc) return rc;
-    PostFwd p{g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, g1, xhat1, rstd1, z4, xhat2, rstd2, g2, counter, B, G, Kdim};
-    global_post_fwd_kernel<<<G / kNT, kThreads, smem, (cudaStream_t)stream>>>(p);
+    PostFwd p{g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, g1, xhat1, rstd1, z4, xhat2, rstd2, g2, B, G, Kdim};
+    void* args[] = {&p};
+    PB_CUDA(cudaLaunchCooperativeKernel((const void*)global_post_fwd_kernel, dim3(G / kNT), dim3(kThreads), args, smem,
+                                        (cudaStream_t)stream));
     pb_count_launch(1);
     return pb_check_launch("pb_global_post_fwd");
 }
 
 int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2, const float* rstd2, const float* z4,
                        const float* g1, const float* W4, const float* gamma1, const float* xhat1, const float* rstd1,
-                       const float* pool, const float* Wp, int Kdim, float* dg1_buf, float* dx1, float* dpool, float* dWp,
-                       float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2, float* dbeta2, int* counter, int B,
-                       int G, void* stream) {
+                       const float* pool, const float* Wp, int Kdim, float* scratch3, float* dx1, float* dpool, float* dWp,
+                       float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2, float* dbeta2, int B, int G,
+                       void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, 8), PB_ERR_UNSUPPORTED, "global_post_bwd: shape B=%d G=%d not covered", B, G);
-    PB_REQUIRE(counter != nullptr && Kdim > 0, PB_ERR_SHAPE, "global_post_bwd: bad arguments");
-    const size_t smem = smem_bytes_post_bwd(G);
+    PB_REQUIRE(Kdim > 0 && scratch3 != nullptr, PB_ERR_SHAPE, "global_post_bwd: bad arguments");
+    const size_t smem = smem_bytes(row_tile_of(G), G, true);
     int rc = set_smem(global_post_bwd_kernel, smem);
     if (rc) return rc;
+    const size_t n = (size_t)B * G;
     PostBwd p{dg2, gamma2, xhat2, rstd2, z4, g1, W4, gamma1, xhat1, rstd1, pool, Wp,
-              dg1_buf, dx1, dpool, dWp, dgamma1, dbeta1, dW4, db4, dgamma2, dbeta2, counter, B, G, Kdim};
-    global_post_bwd_kernel<<<G / kNT, kThreads, smem, (cudaStream_t)stream>>>(p);
+              scratch3, scratch3 + n, scratch3 + 2 * n, dx1, dpool, dWp, dgamma1, dbeta1, dW4, db4, dgamma2, dbeta2, B, G, Kdim};
+    void* args[] = {&p};
+    PB_CUDA(cudaLaunchCooperativeKernel((const void*)global_post_bwd_kernel, dim3(G / kNT), dim3(kThreads), args, smem,
+                                        (cudaStream_t)stream));
     pb_count_launch(1);
     return pb_check_launch("pb_global_post_bwd");
 }

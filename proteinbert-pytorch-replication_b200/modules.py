@@ -98,7 +98,7 @@ class ProteinBERTBlock(nn.Module):
         self.wide_conv_dilation = wide_conv_dilation
         self.precision = precision
         self.head_grads = True          # the reference's autograd also fills the (unregistered) heads' .grad
-        self.fuse_global = os.environ.get("PB_B200_FUSE_GLOBAL", "0") == "1"   # 4-launch global track (ops_global_fused.cu)
+        self.fuse_global = os.environ.get("PB_B200_FUSE_GLOBAL", "1") == "1"   # 4-launch global track (ops_global_fused.cu)
 
         self.global_attention_layer = GlobalAttention(num_heads=num_heads, local_dim=local_dim, global_dim=global_dim,
                                                       value_dim=int(global_dim / num_heads), key_dim=key_dim, device=device)

@@ -294,17 +294,6 @@ class GlobalPreFn(torch.autograd.Function):
         return dg, dW1, db1, dW3, db3
 
 
-_COUNTERS = {}
-
-
-def _counter(device):
-    c = _COUNTERS.get(device)
-    if c is None:
-        c = torch.zeros((16,), dtype=torch.int32, device=device)
-        _COUNTERS[device] = c
-    return c
-
-
 class GlobalPostFn(torch.autograd.Function):
     """g2 = LN(g1 + gelu(g1 W4^T + b4)), g1 = LN(g + gh + (sum(Wp)/K) pool) in one launch (modules.py:92,223-229)."""
 
@@ -318,7 +307,7 @@ class GlobalPostFn(torch.autograd.Function):
         rstd = torch.empty((2, B), dtype=torch.float32, device=dev)
         _call("pb_global_post_fwd", _p(g), _p(gh), _p(pool), _p(Wp), Wp.numel(), _p(gamma1), _p(beta1), _p(W4), _p(b4),
               _p(gamma2), _p(beta2), _p(buf[0]), _p(buf[1]), _p(rstd[0]), _p(buf[2]), _p(buf[3]), _p(rstd[1]), _p(buf[4]),
-              _p(_counter(dev)), B, G, _st())
+              B, G, _st())
         ctx.save_for_backward(pool, Wp, gamma1, W4, gamma2, buf, rstd)
         return buf[4]
 
@@ -328,14 +317,14 @@ class GlobalPostFn(torch.autograd.Function):
         B, G = pool.shape
         dev = pool.device
         dg2 = dg2.contiguous()
-        out = torch.empty((3, B, G), dtype=torch.float32, device=dev)      # dg1 scratch, dx1, dpool
+        out = torch.empty((5, B, G), dtype=torch.float32, device=dev)      # 3 x scratch, dx1, dpool
         dWp = torch.empty_like(Wp)
         vec = torch.empty((5, G), dtype=torch.float32, device=dev)         # dgamma1, dbeta1, db4, dgamma2, dbeta2
         dW4 = torch.empty_like(W4)
         _call("pb_global_post_bwd", _p(dg2), _p(gamma2), _p(buf[3]), _p(rstd[1]), _p(buf[2]), _p(buf[0]), _p(W4), _p(gamma1),
-              _p(buf[1]), _p(rstd[0]), _p(pool), _p(Wp), Wp.numel(), _p(out[0]), _p(out[1]), _p(out[2]), _p(dWp), _p(vec[0]),
-              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), _p(_counter(dev)), B, G, _st())
-        return out[1], out[1], out[2], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4]
+              _p(buf[1]), _p(rstd[0]), _p(pool), _p(Wp), Wp.numel(), _p(out[0]), _p(out[3]), _p(out[4]), _p(dWp), _p(vec[0]),
+              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), B, G, _st())
+        return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4]
 
 
 def global_fused_ok(B, G, C) -> bool:
