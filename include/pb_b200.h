@@ -188,9 +188,11 @@ int pb_local_linear_bwd(const void* du2_act, const void* z_act, const void* h_ac
 int pb_attn_pool_fwd(const void* h_act, const void* wvT_wt, float* pool, int B, int L, int C, int G, int dt,
                      void* stream);
 /* dzv = dpool[b,g]*gelu'(h.Wv) (scratch [B*L,G] act), dh_out = dh_in + dzv Wv^T, dWvT [G,C] (NULL = skip).
- * wv_wt = Wv_all [C, G] (K-major operand of the tensor-core dh GEMM); NULL selects the SIMT engine.          */
+ * wv_wt = Wv_all [C, G] (K-major operand of the tensor-core dh GEMM); NULL selects the SIMT engine.
+ * head_dv > 0: dWvT receives one contiguous [C, head_dv] gradient per head (the layout of each head's
+ * Wv_parameter, modules.py:36-39), stacked; head_dv = 0: the [G, C] matrix.                                  */
 int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const void* wv_wt, const float* dpool, const void* dh_in_act,
-                     void* dzv_act, void* dh_out_act, float* dWvT, int B, int L, int C, int G, int dt, void* ws,
+                     void* dzv_act, void* dh_out_act, float* dWvT, int head_dv, int B, int L, int C, int G, int dt, void* ws,
                      size_t ws_bytes, void* stream);
 
 /* ---- a15: token head, softmax over the BATCH axis (modules.py:277-284; nn.Softmax() on 3-D) ----- */

@@ -47,7 +47,7 @@ PROTOTYPES = {
     "pb_local_linear_fwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_attn_pool_fwd": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
-    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p],
+    "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_token_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_pretrain_loss": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],

@@ -1,6 +1,7 @@
 // Library plumbing: error string, device check, launch counter, parameter staging kernels.
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <atomic>
 #include "common.cuh"
 #include "../../include/pb_b200.h"
@@ -13,6 +14,17 @@ void pb_set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+static std::atomic<int> g_pdl{-1};
+bool pb_pdl_enabled() {
+    int v = g_pdl.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char* e = getenv("PB_B200_PDL");
+        v = (e == nullptr || e[0] != '0') ? 1 : 0;
+        g_pdl.store(v);
+    }
+    return v != 0;
 }
 
 void pb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }

@@ -143,3 +143,22 @@ __device__ __forceinline__ LnStat ln_stat(const double* stats, int b, double n, 
 }
 
 static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }
+
+// ---- programmatic dependent launch ----------------------------------------------------------------------
+// Kernels launched through pb_launch_pdl may be scheduled while the previous kernel in the stream drains;
+// they call pdl_wait() before touching global memory, which blocks until that kernel has completed and its
+// writes are visible.  This hides the launch latency between the ~200 short kernels of one step.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+bool pb_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t pb_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pb_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}

@@ -191,6 +191,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_fwd_kernel(PreFwd p) {
     float* A_s = sm;                                   // [MT][lda]
     float* Bt_s = A_s + (size_t)MT * lda;              // [K][8]
     float* red_s = Bt_s + (size_t)K * kNT;             // [512/MT][MT][8] = [512*8]
+    pdl_wait();
     const int n0 = blockIdx.x * kNT;                   // column in the concatenated [C + G] output
     const bool is_g2l = n0 < p.C;                      // slices never straddle (C % 8 == 0)
     const float* W = is_g2l ? p.W1 : p.W3;
@@ -238,6 +239,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     float* red_s = Bt_s + (size_t)KA * kNT;            // [512*8]
     float* D_s = red_s + kThreads * kNT;               // [MT][8] slice of dz for the dW product
     // CTA i owns columns [8i, 8i+8) of dg (if < G) and rows [8i, 8i+8) of the stacked [dW3 ; dW1] matrix.
+    pdl_wait();
     const int n0 = blockIdx.x * kNT;                   // 0 .. G + C
     const bool has_dg = n0 < G;
     if (has_dg) {                                      // Bt = [W3[:, n0..] ; W1[:, n0..]]  (rows = contraction index)
@@ -537,7 +539,7 @@ int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const fl
     int rc = set_smem(global_pre_fwd_kernel, smem);
     if (rc) return rc;
     PreFwd p{g, W1, b1, W3, b3, zg, g2l, z3, gh, B, G, C};
-    global_pre_fwd_kernel<<<(G + C) / kNT, kThreads, smem, (cudaStream_t)stream>>>(p);
+    PB_CUDA(pb_launch_pdl(global_pre_fwd_kernel, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
     pb_count_launch(1);
     return pb_check_launch("pb_global_pre_fwd");
 }
@@ -550,7 +552,7 @@ int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, cons
     int rc = set_smem(global_pre_bwd_kernel, smem);
     if (rc) return rc;
     PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C};
-    global_pre_bwd_kernel<<<(G + C) / kNT, kThreads, smem, (cudaStream_t)stream>>>(p);
+    PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
     pb_count_launch(1);
     return pb_check_launch("pb_global_pre_bwd");
 }

@@ -83,6 +83,13 @@ struct EpAtomic {
     float* out; long ld;
     __device__ void operator()(int m, int n, float acc, int, int) const { atomicAdd(&out[(size_t)m * ld + n], acc); }
 };
+// out is a stack of per-head [ntot, dv] matrices: row m = head*dv + j of the [G, C] product goes to out[head][n][j]
+struct EpAtomicHeads {
+    float* out; int dv, ntot;
+    __device__ void operator()(int m, int n, float acc, int, int) const {
+        atomicAdd(&out[(size_t)(m / dv) * ((size_t)ntot * dv) + (size_t)n * dv + (m % dv)], acc);
+    }
+};
 template <typename T>
 struct EpLocalLinear {
     const float* bias; const T* h; T* z; T* u2; int N;
@@ -318,6 +325,7 @@ template <typename T>
 __global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
                                        const float* __restrict__ gamma, double* __restrict__ sums, long long n, float eps) {
     __shared__ double red[32];
+    pdl_wait();
     const int b = blockIdx.y;
     const LnStat st = ln_stat(stats, b, (double)n, eps);
     const long long nv = n / 8;
@@ -346,6 +354,7 @@ __global__ void ln_bwd_apply_vec_kernel(const T* __restrict__ dy, const T* __res
                                         float* __restrict__ dgamma, float* __restrict__ dbeta, int B, long long n, float eps,
                                         int per_group, int use_atomics) {
     extern __shared__ float prm[];       // [per_group][4]: mean, rstd, m1, m2
+    pdl_wait();
     const int b0 = blockIdx.y * per_group;
     const int nb = min(per_group, B - b0);
     for (int k = threadIdx.x; k < nb; k += blockDim.x) {
@@ -392,6 +401,7 @@ __global__ void gelu_bwd_colsum_vec_kernel(const T* __restrict__ dy, const T* __
                                            T* __restrict__ dz0, T* __restrict__ dz1, float* __restrict__ dsample,
                                            float* __restrict__ db0, float* __restrict__ db1, int L, int C) {
     extern __shared__ float sm[];        // [3][C]
+    pdl_wait();
     const int b = blockIdx.y;
     const int vpr = C / 8;                        // vectors per row
     const int rows_pb = blockDim.x / vpr;         // rows handled concurrently
@@ -443,8 +453,8 @@ int launch_gelu_bwd_colsum(const void* dy, const void* z0, const void* z1, void*
                            float* db1, int B, int L, int C, cudaStream_t st) {
     if (C % 8 == 0 && C / 8 <= 256 && 256 % (C / 8) == 0) {
         dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
-        gelu_bwd_colsum_vec_kernel<T><<<grid, 256, 3 * C * sizeof(float), st>>>((const T*)dy, (const T*)z0, (const T*)z1, (T*)dz0,
-                                                                               (T*)dz1, dsample, db0, db1, L, C);
+        PB_CUDA(pb_launch_pdl(gelu_bwd_colsum_vec_kernel<T>, grid, dim3(256), 3 * C * sizeof(float), st, (const T*)dy, (const T*)z0,
+                              (const T*)z1, (T*)dz0, (T*)dz1, dsample, db0, db1, L, C));
     } else {
         dim3 grid(max(1, min(ceil_div(L, 64), 16)), B);
         gelu_bwd_colsum_kernel<T><<<grid, dim3(32, 8), 3 * C * sizeof(float), st>>>((const T*)dy, (const T*)z0, (const T*)z1, (T*)dz0,
@@ -503,9 +513,9 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
         dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
         dim3 g2((unsigned)ceil_div(nv, 256), groups);
         DISPATCH_DT(dt, {
-            ln_bwd_sums_vec_kernel<T><<<g1, 256, 0, st>>>((const T*)dy, (const T*)u, stats, gamma, sums, n, eps);
-            ln_bwd_apply_vec_kernel<T><<<g2, 256, 4 * per_group * sizeof(float), st>>>(
-                (const T*)dy, (const T*)u, stats, gamma, sums, (T*)du, dgamma, dbeta, B, n, eps, per_group, groups > 1 ? 1 : 0);
+            PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, stats, gamma, sums, n, eps));
+            PB_CUDA(pb_launch_pdl(ln_bwd_apply_vec_kernel<T>, g2, dim3(256), 4 * per_group * sizeof(float), st, (const T*)dy, (const T*)u,
+                                  stats, gamma, (const double*)sums, (T*)du, dgamma, dbeta, B, n, eps, per_group, groups > 1 ? 1 : 0));
         });
     } else {
         DISPATCH_DT(dt, (ln_bwd_pass1_kernel<T><<<ceil_div(n, 128), 128, 4 * B * sizeof(float), st>>>(
@@ -619,19 +629,22 @@ int pb_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, 
 }
 
 int pb_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
-                     float* dWvT, int B, int L, int C, int G, int dt, void* ws, size_t ws_bytes, void* stream) {
+                     float* dWvT, int head_dv, int B, int L, int C, int G, int dt, void* ws, size_t ws_bytes, void* stream) {
     PB_REQUIRE(B > 0 && L > 0 && C > 0 && G > 0, PB_ERR_SHAPE, "attn_pool_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
     if (dt == PB_BF16 && wv != nullptr && pb_tc_attn_ok(B, L, C, G))
-        return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, B, L, C, G, ws, ws_bytes, st);
+        return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, head_dv, B, L, C, G, ws, ws_bytes, st);
     if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
     DISPATCH_DT(dt, {
         gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
         gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);
         if (dWvT) {
             const int tiles = ceil_div(G, 128) * ceil_div(C, 128);
-            gemm_auto(ColMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)h, C}, EpAtomic{dWvT, C}, G, C, M, split_for(tiles, M), 1, st);
+            if (head_dv > 0)
+                gemm_auto(ColMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)h, C}, EpAtomicHeads{dWvT, head_dv, C}, G, C, M, split_for(tiles, M), 1, st);
+            else
+                gemm_auto(ColMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)h, C}, EpAtomic{dWvT, C}, G, C, M, split_for(tiles, M), 1, st);
         }
     });
     return pb_check_launch("pb_attn_pool_bwd");

@@ -22,6 +22,6 @@ int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const
                            int C, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st);
 int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv, void* dh_out,
-                        float* dWvT, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st);
+                        float* dWvT, int head_dv, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st);

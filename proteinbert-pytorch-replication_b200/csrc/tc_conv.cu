@@ -64,6 +64,7 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();          // everything above overlapped the previous kernel's tail; from here on we touch its outputs
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -202,7 +203,7 @@ int launch_conv(const void* a0, const void* a1, const void* w0, const void* w1, 
         PB_CUDA(cudaFuncSetAttribute(tc_conv_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
-    tc_conv_pair_kernel<kFwd><<<B * (L / kBM), kThreads, kSmemBytes, st>>>(mA0, mA1, mB0, mB1, ep, L, ksize, dil);
+    PB_CUDA(pb_launch_pdl(tc_conv_pair_kernel<kFwd>, dim3(B * (L / kBM)), dim3(kThreads), kSmemBytes, st, mA0, mA1, mB0, mB1, ep, L, ksize, dil));
     pb_count_launch(1);
     return pb_check_launch(kFwd ? "tc_conv_pair_fwd" : "tc_conv_pair_dgrad");
 }

@@ -78,6 +78,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -195,7 +196,13 @@ struct WgradParams {
     int L, dil[2], half, ntaps;                         // blockIdx.y = src * ntaps + t ; shift = (t - half) * dil[src]
     int chunks_total, chunks_per_split;                 // 64-row chunks over all samples
     float* ws;                                          // split-K partial tiles [split][y][tile][128][128], or NULL = atomics
+    int head_dv, ntot;                                  // > 0: out is a stack of per-head [ntot, head_dv] matrices (m = head*dv + j)
 };
+__device__ __forceinline__ size_t wgrad_out_index(const WgradParams& wp, int gm, int gn, int t) {
+    if (wp.head_dv > 0)
+        return (size_t)(gm / wp.head_dv) * ((size_t)wp.ntot * wp.head_dv) + (size_t)gn * wp.head_dv + (gm % wp.head_dv);
+    return (size_t)gm * wp.stride_m + (size_t)gn * wp.stride_n + (size_t)t * wp.stride_t;
+}
 
 __global__ void __launch_bounds__(kThreads, 2)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant__ CUtensorMap mapP1,
@@ -229,6 +236,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
     if (n_iter <= 0 && wp.ws != nullptr && warp >= 2) {
         // an empty split still owns a partial tile: write zeros so the reduction can read every slot
         float* dst = wp.ws + ((((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * kBM) * kBN;
@@ -289,7 +297,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant
                 } else {
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
-                        atomicAdd(outp + (size_t)m * wp.stride_m + (size_t)(n0 + ch * 32 + j) * wp.stride_n + (size_t)t * wp.stride_t, acc[j]);
+                        atomicAdd(outp + wgrad_out_index(wp, m, n0 + ch * 32 + j, t), acc[j]);
                 }
             }
             tc_fence_before();
@@ -304,6 +312,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant
 
 // out[src][m, n, t] = sum over splits of the partial tiles (plain stores: every output element is written once)
 __global__ void wgrad_reduce_kernel(WgradParams wp, int tiles_m, int tiles_n, int ny, int splits) {
+    pdl_wait();
     const long long total = (long long)ny * tiles_m * tiles_n * kBM * kBN;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int n = (int)(i % kBN);
@@ -314,7 +323,7 @@ __global__ void wgrad_reduce_kernel(WgradParams wp, int tiles_m, int tiles_n, in
         for (int k = 0; k < splits; ++k) s += wp.ws[(size_t)k * total + i];
         const int src = y / wp.ntaps, t = y % wp.ntaps;
         const int gm = (tile / tiles_n) * kBM + m, gn = (tile % tiles_n) * kBN + n;
-        wp.out[src][(size_t)gm * wp.stride_m + (size_t)gn * wp.stride_n + (size_t)t * wp.stride_t] = s;
+        wp.out[src][wgrad_out_index(wp, gm, gn, t)] = s;
     }
 }
 
@@ -342,7 +351,7 @@ int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, 
         PB_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
-    tc_gemm_kernel<EPI><<<dim3(M / kBM, N / kBN), kThreads, kSmemBytes, st>>>(mA, mB, ep, K);
+    PB_CUDA(pb_launch_pdl(tc_gemm_kernel<EPI>, dim3(M / kBM, N / kBN), dim3(kThreads), kSmemBytes, st, mA, mB, ep, K));
     pb_count_launch(1);
     return pb_check_launch(what);
 }
@@ -352,7 +361,7 @@ int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, 
 // without one they are accumulated with atomics into a zeroed `out`.
 int launch_wgrad(const void* P0, const void* P1, const void* Q, float* out0, float* out1, long stride_m, long stride_n,
                  long stride_t, int B, int L, int Mtot, int Ntot, int ntaps, int dil0, int dil1, void* ws, size_t ws_bytes,
-                 cudaStream_t st, const char* what) {
+                 cudaStream_t st, const char* what, int head_dv = 0) {
     CUtensorMap mP0, mP1, mQ;
     int rc;
     const int nsrc = P1 != nullptr ? 2 : 1;
@@ -367,6 +376,7 @@ int launch_wgrad(const void* P0, const void* P1, const void* Q, float* out0, flo
     WgradParams wp;
     wp.out[0] = out0; wp.out[1] = out1; wp.stride_m = stride_m; wp.stride_n = stride_n; wp.stride_t = stride_t;
     wp.L = L; wp.dil[0] = dil0; wp.dil[1] = dil1; wp.half = ntaps / 2; wp.ntaps = ntaps;
+    wp.head_dv = head_dv; wp.ntot = Ntot;
     wp.chunks_total = B * (L / 64);
     const int tiles_m = Mtot / kBM, tiles_n = Ntot / kBN, ny = nsrc * ntaps;
     const int tiles = tiles_m * tiles_n * ny;
@@ -382,11 +392,11 @@ int launch_wgrad(const void* P0, const void* P1, const void* Q, float* out0, flo
         PB_CUDA(cudaMemsetAsync(out0, 0, (size_t)Mtot * stride_m * sizeof(float), st));
         if (nsrc == 2) PB_CUDA(cudaMemsetAsync(out1, 0, (size_t)Mtot * stride_m * sizeof(float), st));
     }
-    tc_wgrad_kernel<<<dim3(tiles_m * tiles_n, ny, splits), kThreads, kSmemBytes, st>>>(mP0, mP1, mQ, wp, tiles_n);
+    PB_CUDA(pb_launch_pdl(tc_wgrad_kernel, dim3(tiles_m * tiles_n, ny, splits), dim3(kThreads), kSmemBytes, st, mP0, mP1, mQ, wp, tiles_n));
     pb_count_launch(1);
     if (wp.ws != nullptr) {
         const long long total = (long long)tiles * kBM * kBN;
-        wgrad_reduce_kernel<<<(int)min((long long)ceil_div(total, 256), 148LL * 8), 256, 0, st>>>(wp, tiles_m, tiles_n, ny, splits);
+        PB_CUDA(pb_launch_pdl(wgrad_reduce_kernel, dim3((unsigned)min((long long)ceil_div(total, 256), 148LL * 8)), dim3(256), 0, st, wp, tiles_m, tiles_n, ny, splits));
         pb_count_launch(1);
     }
     return pb_check_launch(what);
@@ -427,7 +437,7 @@ int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int 
 }
 
 int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float* dpool, const void* dh_in, void* dzv,
-                        void* dh_out, float* dWvT, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st) {
+                        void* dh_out, float* dWvT, int head_dv, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st) {
     GemmEpi e1{};
     e1.ldn = G; e1.L = L; e1.dpool = dpool; e1.out0 = (bf16*)dzv;
     int rc = launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
@@ -436,6 +446,6 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
     e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
     rc = launch_gemm<EPI_ADD_STORE>(dzv, wv, e2, B * L, C, G, st, "tc_attn_pool_bwd(dh)");
     if (rc) return rc;
-    if (dWvT) rc = launch_wgrad(dzv, nullptr, h, dWvT, nullptr, C, 1, 0, B, L, G, C, 1, 1, 1, ws, ws_bytes, st, "tc_attn_pool_bwd(dWv)");
+    if (dWvT) rc = launch_wgrad(dzv, nullptr, h, dWvT, nullptr, C, 1, 0, B, L, G, C, 1, 1, 1, ws, ws_bytes, st, "tc_attn_pool_bwd(dWv)", head_dv);
     return rc;
 }

@@ -44,6 +44,7 @@ namespace {
 // h = (u - mean) * rstd * gamma + beta, 8 bf16 per thread; grid = (chunks, B)
 __global__ void ln_apply_bf16_kernel(const bf16* __restrict__ u, const double* __restrict__ stats, const float* __restrict__ gamma,
                                      const float* __restrict__ beta, bf16* __restrict__ h, long long n, float eps) {
+    pdl_wait();
     const int b = blockIdx.y;
     const LnStat st = ln_stat(stats, b, (double)n, eps);
     const long long nv = n / 8;
@@ -69,7 +70,7 @@ int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const
                    float eps, cudaStream_t st) {
     const long long n = (long long)L * C;
     dim3 grid((unsigned)max(1, min(ceil_div(n / 8, 256), 16)), B);
-    ln_apply_bf16_kernel<<<grid, 256, 0, st>>>((const bf16*)u, stats, gamma, beta, (bf16*)h, n, eps);
+    PB_CUDA(pb_launch_pdl(ln_apply_bf16_kernel, grid, dim3(256), 0, st, (const bf16*)u, stats, gamma, beta, (bf16*)h, n, eps));
     pb_count_launch(1);
     return pb_check_launch("pb_ln_joint_apply(bf16)");
 }

@@ -399,8 +399,9 @@ class LocalTrackFn(torch.autograd.Function):
         # attention pooling
         dzv = torch.empty((B * L, G), dtype=adt, device=dev)
         dh2t = torch.empty_like(x)
-        dWvT = f32(G, C) if head_grads else None
-        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWvT), B, L, C, G, dt, *_wgrad_ws(dev), st)
+        Dv = G // n_heads
+        dWv = f32(n_heads, C, Dv) if head_grads else None          # one contiguous [C, Dv] gradient per head
+        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
         del dzv
         # LN2
         du2 = torch.empty_like(x)
@@ -422,8 +423,7 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_conv_pair_bwd", _p(du1), _p(zn), _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), _p(dx), _p(dWn),
                                   _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, *_wgrad_ws(dev), st)
         if head_grads:
-            Dv = G // n_heads
-            dheads = tuple(dWvT[h * Dv:(h + 1) * Dv].t() for h in range(n_heads))
+            dheads = tuple(dWv[h] for h in range(n_heads))
         else:
             dheads = (None,) * n_heads
         return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, None, None, None, None) + dheads
@@ -457,7 +457,7 @@ class AttnPoolFn(torch.autograd.Function):
         zero = torch.zeros_like(h)
         dh = torch.empty_like(h)
         dWvT = torch.empty((G, C), dtype=torch.float32, device=dev)
-        _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(wvw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), B, L, C, G,
+        _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(wvw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), 0, B, L, C, G,
                                      dt, *_wgrad_ws(dev), _st())
         return dh, dWvT
 

@@ -136,7 +136,7 @@ def test_attention_pool(pb):
         dh = torch.empty_like(h)
         dWvT = torch.empty(G, C, device="cuda")
         ops._call("pb_attn_pool_bwd", h.data_ptr(), wvTw.data_ptr(), wvw.data_ptr(), dpool.data_ptr(), dh_in.data_ptr(), dzv.data_ptr(),
-                  dh.data_ptr(), dWvT.data_ptr(), B, L, C, G, 1, *wsargs(pb), st)
+                  dh.data_ptr(), dWvT.data_ptr(), 0, B, L, C, G, 1, *wsargs(pb), st)
         return pool, dzv, dh, dWvT
 
     simt, tc = both_engines(pb, run)
