@@ -51,7 +51,8 @@ int pb_device_ok(int device);
 long long pb_launch_count(void);
 /* 1 (default): PB_BF16 contractions run on the tcgen05 tensor-core engine where the tiling covers the shape
  * (C = 128 for the convolutions, C, G multiples of 128, L a multiple of 128); 0: force the fp32-accumulating
- * SIMT engine (same bf16 operands; used by the tests to cross-check the two engines).  Returns the old value. */
+ * SIMT engine (same bf16 operands; used by the tests to cross-check the two engines); 4: tensor cores with the
+ * first-generation (128-position, one TMA load per tap) conv kernel instead of the halo kernel.  Returns the old value. */
 int pb_set_tensor_cores(int enabled);
 
 /* ---- parameter staging ----------------------------------------------------------------------- */

@@ -5,6 +5,7 @@
 #include "common.cuh"
 
 bool pb_tc_enabled();
+int pb_tc_mode();      // value given to pb_set_tensor_cores: 0 off, 1 default, 4 = force the first-generation conv kernel
 bool pb_tc_conv_ok(int B, int L, int C, int ksize, int dil);
 bool pb_tc_linear_ok(int B, int L, int C);
 bool pb_tc_attn_ok(int B, int L, int C, int G);
@@ -25,3 +26,10 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
                         float* dWvT, int head_dv, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st);
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st);
+
+bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil);
+int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
+                    void* zw, void* u, double* stats, int B, int L, int ksize, int dil, int bo_mode, cudaStream_t st);
+int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
+                      int L, int ksize, int dil, int bo_mode, cudaStream_t st);
+void* pb_debug_ptr();

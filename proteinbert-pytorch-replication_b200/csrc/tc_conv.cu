@@ -97,13 +97,11 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
                 const int conv = i / (ksize * kchunks);
                 const int first = (i % (ksize * kchunks)) == 0;
                 const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-                const uint32_t b_addr = a_addr + kBM * 64 * 2;
+                const uint64_t da0 = make_smem_desc_sw128(a_addr, 16, 1024);
+                const uint64_t db0 = make_smem_desc_sw128(a_addr + kBM * 64 * 2, 16, 1024);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-                    const uint64_t db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-                    umma_bf16(tmem_base + conv * kC, da, db, idesc, (first && k == 0) ? 0u : 1u);
-                }
+                for (int k = 0; k < 4; ++k)       // K step of 16 elements = +32 B = +2 in the descriptor's address field
+                    umma_bf16(tmem_base + conv * kC, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc, (first && k == 0) ? 0u : 1u);
                 umma_commit(&empty_bar[s]);          // frees the smem stage when these MMAs retire
             }
             umma_commit(tmem_full_bar);              // accumulators complete
@@ -216,6 +214,9 @@ bool pb_tc_conv_ok(int B, int L, int C, int ksize, int dil) {
 
 int pb_tc_conv_pair_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l,
                         void* zn, void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, cudaStream_t st) {
+    const int mode = pb_tc_mode();
+    if (mode != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil))       // 256-position halo kernel unless the first generation is forced
+        return pb_tc_conv2_fwd(x, wn, ww, bn, bw, g2l, zn, zw, u, stats, B, L, ksize, dil, 0, st);
     ConvEpiParams ep{};
     ep.x = (const bf16*)x; ep.bn = bn; ep.bw = bw; ep.g2l = g2l;
     ep.zn = (bf16*)zn; ep.zw = (bf16*)zw; ep.u = (bf16*)u; ep.stats = stats;
@@ -224,6 +225,9 @@ int pb_tc_conv_pair_fwd(const void* x, const void* wn, const void* ww, const flo
 
 int pb_tc_conv_pair_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx,
                           int B, int L, int C, int ksize, int dil, cudaStream_t st) {
+    const int mode = pb_tc_mode();
+    if (mode != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil))
+        return pb_tc_conv2_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, ksize, dil, 0, st);
     ConvEpiParams ep{};
     ep.du = (const bf16*)du; ep.dx = (bf16*)dx;
     return launch_conv<false>(dzn, dzw, wn_bwd, ww_bwd, ep, B, L, ksize, dil, st);

@@ -1,0 +1,337 @@
+// Conv pair, second-generation tcgen05 kernel: 256 sequence positions per CTA, input halo resident in shared memory.
+//
+// What changed against tc_conv.cu (which fetched one 128 x 64 activation tile per tap, 18 taps x 2 chunks per
+// tile, and was bound by L2 -> shared-memory traffic at ~1.15 MB per 128 positions):
+//   * the CTA loads the input rows it needs ONCE: positions [l0 - margin, l0 + 256 + margin) x 128 channels
+//     (74 KB for the dilated conv, margin = 4 * dilation) and every tap's A operand is the same tile read through
+//     a UMMA descriptor whose start address is moved down by (tap offset) rows of 128 bytes;
+//   * each 16 KB weight tile that arrives in the ring feeds 8 MMAs (two 128-position sub-tiles x 4 k-steps)
+//     instead of 4, so the weight stream per position is halved;
+//   * four accumulators (2 sub-tiles x 2 convolutions) fill the 512 TMEM columns; eight epilogue warps.
+// L2 -> smem traffic drops to ~0.65 MB per 256 positions (3.5x less per position).
+#include <stdlib.h>
+#include "tc_common.cuh"
+#include "tc_api.cuh"
+
+namespace {
+
+constexpr int kC = 128;
+constexpr int kRows = 256;                       // positions per CTA (two UMMA M = 128 sub-tiles)
+constexpr int kBTile = kC * 64 * 2;              // one weight tile [128 out-ch x 64 in-ch] bf16 = 16 KB
+constexpr int kThreads = 320;                    // warp 0 TMA, warp 1 MMA + TMEM, warps 2..9 epilogue
+
+struct Conv2Params {
+    const bf16* x; const float* bn; const float* bw; const float* g2l;
+    bf16* zn; bf16* zw; bf16* u; double* stats;
+    const bf16* du; bf16* dx;
+    int L, ksize, dil;
+    int hr[2];            // halo rows of input 0 / 1
+    int a_bytes[2];       // shared-memory bytes of one (input, channel chunk) halo tile, multiple of 1024
+    unsigned long long* dbg;   // optional cycle counters of CTA 0 (pb_debug_buffer)
+    int debug;            // experiment switches (PB_CONV2_DEBUG): 1 = align tap offsets to 8 rows (wrong results), 2 = skip epilogue math
+    int base_offset_mode; // 0 (measured on B200): the 128-byte swizzle is a function of the absolute shared-memory
+                          // address, so a descriptor that starts on any row of a TMA-written tile needs base_offset = 0;
+                          // 1 = (addr >> 7) & 7, kept only to document the convention that does NOT work
+};
+
+__device__ __forceinline__ uint64_t desc_sw128_bo(uint32_t saddr, uint32_t sbo_bytes, int mode) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;                                  // LBO (unused for swizzled K-major)
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;
+    if (mode) d |= (uint64_t)((saddr >> 7) & 0x7u) << 49;    // start row inside the 8-row swizzle atom
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+template <bool kFwd, int kStages>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constant__ CUtensorMap mapA0t,
+                const __grid_constant__ CUtensorMap mapA1m, const __grid_constant__ CUtensorMap mapA1t,
+                const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
+                const __grid_constant__ CUtensorMap mapS0, const __grid_constant__ CUtensorMap mapS1,
+                const __grid_constant__ CUtensorMap mapS2, Conv2Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // layout: two halo buffers (channel chunk 0 / 1, sized for the larger input) | weight ring | barriers.
+    // forward: both buffers hold x (wide margin) for the whole kernel.  dgrad: they hold dzn first; as soon as the
+    // narrow convolution has consumed chunk kc, the same buffer is refilled with dzw for the dilated one.
+    const int a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
+    uint8_t* ring = smem + 2 * a_buf;
+    uint64_t* full_bar = (uint64_t*)(ring + kStages * kBTile);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* a_full = empty_bar + kStages;          // [2 inputs][2 chunks]
+    uint64_t* a_free = a_full + 4;                   // [2 chunks]: narrow conv done with the buffer (dgrad)
+    uint64_t* tmem_full_bar = a_free + 2;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_per_sample = p.L / kRows;
+    const int b = blockIdx.x / tiles_per_sample;
+    const int l0 = (blockIdx.x % tiles_per_sample) * kRows;
+    const int half = p.ksize / 2;
+    const int n_iter = 2 * p.ksize * 2;              // (conv, tap, channel chunk)
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapA0m); tma_prefetch_desc(&mapA1m); tma_prefetch_desc(&mapB0); tma_prefetch_desc(&mapB1);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int i = 0; i < 4; ++i) mbar_init(&a_full[i], 1);
+        mbar_init(&a_free[0], 1); mbar_init(&a_free[1], 1);
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    // iteration i -> (conv, channel chunk, tap): chunk-major inside a convolution so that a halo buffer is released
+    // as early as possible
+    if (warp == 0) {
+        if (lane == 0) {
+            auto load_halo = [&](int in, int kc) {
+                const int margin = half * (in == 0 ? 1 : p.dil);
+                const int tail_rows = p.hr[in] - kRows;
+                uint64_t* bar = &a_full[in * 2 + kc];
+                uint8_t* dst = smem + kc * a_buf;
+                mbar_expect_tx(bar, p.hr[in] * 128);
+                tma_load_3d(dst, in == 0 ? &mapA0m : &mapA1m, bar, kc * 64, l0 - margin, b);
+                if (tail_rows > 0)
+                    tma_load_3d(dst + kRows * 128, in == 0 ? &mapA0t : &mapA1t, bar, kc * 64, l0 - margin + kRows, b);
+            };
+            const int in_first = kFwd ? 1 : 0;
+            load_halo(in_first, 0);
+            load_halo(in_first, 1);
+            for (int i = 0; i < n_iter; ++i) {
+                const int s = i % kStages;
+                const int conv = i / (p.ksize * 2), kc = (i / p.ksize) & 1, t = i % p.ksize;
+                if (!kFwd && conv == 1 && t == 0) {          // refill this chunk's buffer with the dilated conv's input
+                    mbar_wait(&a_free[kc], 0);
+                    load_halo(1, kc);
+                }
+                mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], kBTile);
+                tma_load_2d(ring + s * kBTile, conv == 0 ? &mapB0 : &mapB1, &full_bar[s], kc * 64, t * kC);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(128, kC, 0, 0);
+            long long t_wait_full = 0, t_wait_a = 0;
+            const long long t_begin = clock64();
+            for (int i = 0; i < n_iter; ++i) {
+                const int s = i % kStages;
+                const int conv = i / (p.ksize * 2), kc = (i / p.ksize) & 1, t = i % p.ksize;
+                const int in = kFwd ? 1 : conv;
+                const int d = conv == 0 ? 1 : p.dil;
+                // row of the halo tile at which this tap's window starts
+                int row_off = kFwd ? half * (p.dil - d) + t * d : (2 * half - t) * d;
+                if (p.debug & 1) row_off &= ~7;
+                long long c0 = clock64();
+                if (t == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * 2 + kc], 0);
+                long long c1 = clock64();
+                mbar_wait(&full_bar[s], (i / kStages) & 1);
+                long long c2 = clock64();
+                t_wait_a += c1 - c0; t_wait_full += c2 - c1;
+                tc_fence_after();
+                // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start address
+                // field (bits 0..13), so they are formed by adding constants -- the issuing thread is the bottleneck
+                const uint64_t da0 = desc_sw128_bo(smem_u32(smem + kc * a_buf) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
+                const uint64_t db0 = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
+                const uint32_t tm = tmem_base + conv * kC;
+                const uint32_t acc0 = (t == 0 && kc == 0) ? 0u : 1u;
+#pragma unroll
+                for (int tile = 0; tile < 2; ++tile) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16(tm + tile * 2 * kC, da0 + (uint64_t)(tile * 1024 + k * 2), db0 + (uint64_t)(k * 2), idesc,
+                                  k == 0 ? acc0 : 1u);
+                }
+                umma_commit(&empty_bar[s]);
+                if (!kFwd && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
+            }
+            umma_commit(tmem_full_bar);
+            if (p.dbg && blockIdx.x == 0) {
+                const long long t_issue_end = clock64();
+                mbar_wait(tmem_full_bar, 0);
+                const long long t_done = clock64();
+                p.dbg[0] = t_issue_end - t_begin; p.dbg[1] = t_wait_full; p.dbg[2] = t_wait_a; p.dbg[3] = t_done - t_begin;
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..9; sub-tile = (warp-2)/4, TMEM lane quarter = warp % 4 =====
+        const long long e0 = clock64();
+        mbar_wait(tmem_full_bar, 0);
+        const long long e1 = clock64();
+        tc_fence_after();
+        const int tile = (warp - 2) >> 2, q = warp & 3;
+        const int row = tile * 128 + q * 32 + lane;                     // position inside the CTA's 256
+        const size_t grow = ((size_t)b * p.L + l0 + row) * kC;
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + tile * 2 * kC;
+        // Output tiles leave through TMA: each warp stages its 32 x 32 bf16 sub-tile per tensor in shared memory
+        // (64-byte swizzle, conflict-free 16-byte stores), then one lane issues the bulk tensor store.  The staging
+        // area is the weight ring, idle now; two buffers per warp so a store can drain while the next chunk is computed.
+        uint8_t* stage = ring + (warp - 2) * (2 * 3 * 2048);
+        const int sw = (lane >> 1) & 3;                                 // 64B swizzle: 16-byte chunk ^= (row / 2) & 3
+        // x for the residual comes from the halo tile that fed the MMAs (forward only)
+        const int hrow = half * p.dil + row;
+        float s_sum = 0.f, s_sq = 0.f;
+#pragma unroll 1
+        for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+            float an[32], aw[32];
+            tmem_ld32(taddr + ch * 32, an);
+            tmem_ld32(taddr + kC + ch * 32, aw);
+            const int c0 = ch * 32;
+            uint8_t* sbuf = stage + (ch & 1) * (3 * 2048);
+            if (ch >= 2) {                                               // the buffer's previous store must have read it
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+            }
+            if (kFwd) {
+                uint4 xv[4];
+                const uint8_t* xrow = smem + (ch >> 1) * a_buf + (size_t)hrow * 128;
+#pragma unroll
+                for (int v = 0; v < 4; ++v) xv[v] = *reinterpret_cast<const uint4*>(xrow + ((((ch & 1) * 4 + v) ^ (hrow & 7)) * 16));
+                const bf16* xb = reinterpret_cast<const bf16*>(xv);
+                const float bnl = __ldg(p.bn + c0 + lane), bwl = __ldg(p.bw + c0 + lane), gl = __ldg(p.g2l + (size_t)b * kC + c0 + lane);
+                __align__(16) bf16 on[32], ow[32], ou[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const bf16 zn = __float2bfloat16_rn(an[j] + __shfl_sync(0xffffffffu, bnl, j));
+                    const bf16 zw = __float2bfloat16_rn(aw[j] + __shfl_sync(0xffffffffu, bwl, j));
+                    on[j] = zn; ow[j] = zw;
+                    float v = __bfloat162float(xb[j]) + gelu_fast(__bfloat162float(zn));
+                    v += gelu_fast(__bfloat162float(zw));
+                    v += __shfl_sync(0xffffffffu, gl, j);
+                    const bf16 ub = __float2bfloat16_rn(v);
+                    ou[j] = ub;
+                    const float ur = __bfloat162float(ub);
+                    s_sum += ur; s_sq += ur * ur;
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const int off = lane * 64 + ((v ^ sw) * 16);
+                    *reinterpret_cast<uint4*>(sbuf + off) = reinterpret_cast<const uint4*>(on)[v];
+                    *reinterpret_cast<uint4*>(sbuf + 2048 + off) = reinterpret_cast<const uint4*>(ow)[v];
+                    *reinterpret_cast<uint4*>(sbuf + 4096 + off) = reinterpret_cast<const uint4*>(ou)[v];
+                }
+            } else {
+                uint4 dv[4];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) dv[v] = *reinterpret_cast<const uint4*>(p.du + grow + c0 + v * 8);
+                const bf16* db_ = reinterpret_cast<const bf16*>(dv);
+                __align__(16) bf16 od[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__bfloat162float(db_[j]) + an[j] + aw[j]);
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                const int lrow = l0 + tile * 128 + q * 32;
+                tma_store_3d(&mapS0, sbuf, c0, lrow, b);
+                if (kFwd) {
+                    tma_store_3d(&mapS1, sbuf + 2048, c0, lrow, b);
+                    tma_store_3d(&mapS2, sbuf + 4096, c0, lrow, b);
+                }
+                tma_store_commit();
+            }
+        }
+        if (lane == 0) tma_store_wait<0>();
+        if (kFwd) {
+            const double ds = warp_sum_d((double)s_sum), dq = warp_sum_d((double)s_sq);
+            if (lane == 0) { atomicAdd(&p.stats[2 * b], ds); atomicAdd(&p.stats[2 * b + 1], dq); }
+        }
+        tc_fence_before();
+        if (p.dbg && blockIdx.x == 0 && threadIdx.x == 64) { p.dbg[4] = e1 - e0; p.dbg[5] = clock64() - e1; }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+int act_map(CUtensorMap* m, const void* base, int B, int L, int box_rows) {
+    const uint64_t dims[3] = {(uint64_t)kC, (uint64_t)L, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)kC * 2, (uint64_t)L * kC * 2};
+    const uint32_t box[3] = {64, (uint32_t)box_rows, 1};
+    return pb_make_tmap_bf16(m, base, 3, dims, strides, box);
+}
+int w_map(CUtensorMap* m, const void* base, int ksize) {
+    const uint64_t dims[2] = {(uint64_t)kC, (uint64_t)ksize * kC};
+    const uint64_t strides[1] = {(uint64_t)kC * 2};
+    const uint32_t box[2] = {64, (uint32_t)kC};
+    return pb_make_tmap_bf16(m, base, 2, dims, strides, box);
+}
+
+template <bool kFwd, int kStages>
+int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv2Params p, int B, int L, cudaStream_t st) {
+    const int half = p.ksize / 2;
+    { const char* e = getenv("PB_CONV2_DEBUG"); p.debug = e ? atoi(e) : 0; }
+    p.dbg = (unsigned long long*)pb_debug_ptr();
+    p.hr[0] = kRows + 2 * half;
+    p.hr[1] = kRows + 2 * half * p.dil;
+    for (int i = 0; i < 2; ++i) p.a_bytes[i] = (p.hr[i] * 128 + 1023) / 1024 * 1024;
+    CUtensorMap mA0m, mA0t, mA1m, mA1t, mB0, mB1, mS0, mS1, mS2;
+    int rc;
+    {   // store maps: 32 positions x 32 channels per box, 64-byte swizzle
+        const uint64_t dims[3] = {(uint64_t)kC, (uint64_t)L, (uint64_t)B};
+        const uint64_t strides[2] = {(uint64_t)kC * 2, (uint64_t)L * kC * 2};
+        const uint32_t box[3] = {32, 32, 1};
+        void* o0 = kFwd ? (void*)p.zn : (void*)p.dx;
+        void* o1 = kFwd ? (void*)p.zw : (void*)p.dx;
+        void* o2 = kFwd ? (void*)p.u : (void*)p.dx;
+        if ((rc = pb_make_tmap_bf16(&mS0, o0, 3, dims, strides, box, 64))) return rc;
+        if ((rc = pb_make_tmap_bf16(&mS1, o1, 3, dims, strides, box, 64))) return rc;
+        if ((rc = pb_make_tmap_bf16(&mS2, o2, 3, dims, strides, box, 64))) return rc;
+    }
+    if ((rc = act_map(&mA0m, a0, B, L, kRows))) return rc;
+    if ((rc = act_map(&mA0t, a0, B, L, p.hr[0] - kRows))) return rc;
+    if ((rc = act_map(&mA1m, a1, B, L, kRows))) return rc;
+    if ((rc = act_map(&mA1t, a1, B, L, p.hr[1] - kRows))) return rc;
+    if ((rc = w_map(&mB0, w0, p.ksize))) return rc;
+    if ((rc = w_map(&mB1, w1, p.ksize))) return rc;
+    const size_t a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
+    const size_t smem = 2 * a_buf + (size_t)kStages * kBTile + 1024 + 256;
+    PB_REQUIRE(smem <= 232448, PB_ERR_UNSUPPORTED, "conv2: %zu bytes of shared memory needed", smem);
+    PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PB_CUDA(pb_launch_pdl(tc_conv2_kernel<kFwd, kStages>, dim3(B * (L / kRows)), dim3(kThreads), smem, st, mA0m, mA0t, mA1m, mA1t,
+                          mB0, mB1, mS0, mS1, mS2, p));
+    pb_count_launch(1);
+    return pb_check_launch(kFwd ? "tc_conv2_fwd" : "tc_conv2_dgrad");
+}
+
+}  // namespace
+
+// halo kernel covers: C = 128, L a multiple of 256, kernel size 9 class shapes whose halos fit shared memory
+bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil) {
+    if (!(C == kC && L % kRows == 0 && (ksize & 1) && ksize >= 3 && dil >= 1 && B >= 1)) return false;
+    const int half = ksize / 2;
+    if ((2 * half) % 8 != 0 || (2 * half * dil) % 8 != 0) return false;     // halo tails are whole 8-row swizzle groups
+    const size_t a0 = (size_t)(kRows + 2 * half) * 128, a1 = (size_t)(kRows + 2 * half * dil) * 128;
+    const size_t am = a0 > a1 ? a0 : a1;
+    return 2 * am + 9 * kBTile + 2048 <= 232448 && 2 * half * dil <= 256;
+}
+
+int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
+                    void* zw, void* u, double* stats, int B, int L, int ksize, int dil, int bo_mode, cudaStream_t st) {
+    Conv2Params p{};
+    p.x = (const bf16*)x; p.bn = bn; p.bw = bw; p.g2l = g2l;
+    p.zn = (bf16*)zn; p.zw = (bf16*)zw; p.u = (bf16*)u; p.stats = stats;
+    p.L = L; p.ksize = ksize; p.dil = dil; p.base_offset_mode = bo_mode;
+    return launch2<true, 9>(x, x, wn, ww, p, B, L, st);
+}
+
+int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
+                      int L, int ksize, int dil, int bo_mode, cudaStream_t st) {
+    Conv2Params p{};
+    p.du = (const bf16*)du; p.dx = (bf16*)dx;
+    p.L = L; p.ksize = ksize; p.dil = dil; p.base_offset_mode = bo_mode;
+    return launch2<false, 9>(dzn, dzw, wn_bwd, ww_bwd, p, B, L, st);
+}

@@ -100,11 +100,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 mbar_wait(&full_bar[s], (i / kStages) & 1);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-                const uint32_t b_addr = a_addr + kBM * 64 * 2;
+                const uint64_t da0 = make_smem_desc_sw128(a_addr, 16, 1024);
+                const uint64_t db0 = make_smem_desc_sw128(a_addr + kBM * 64 * 2, 16, 1024);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 32, 16, 1024),
-                              make_smem_desc_sw128(b_addr + k * 32, 16, 1024), idesc, (i == 0 && k == 0) ? 0u : 1u);
+                    umma_bf16(tmem_base, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc, (i == 0 && k == 0) ? 0u : 1u);
                 umma_commit(&empty_bar[s]);
             }
             umma_commit(tmem_full_bar);
@@ -268,11 +268,11 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant
                     mbar_wait(&full_bar[s], (i / kStages) & 1);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-                    const uint32_t b_addr = a_addr + kBM * 64 * 2;
+                    const uint64_t da0 = make_smem_desc_sw128(a_addr, 8192, 1024);
+                    const uint64_t db0 = make_smem_desc_sw128(a_addr + kBM * 64 * 2, 8192, 1024);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)      // 16 contraction rows per MMA = 2048 B down the tile
-                        umma_bf16(tmem_base, make_smem_desc_sw128(a_addr + k * 2048, 8192, 1024),
-                                  make_smem_desc_sw128(b_addr + k * 2048, 8192, 1024), idesc, (i == 0 && k == 0) ? 0u : 1u);
+                    for (int k = 0; k < 4; ++k)      // 16 contraction rows per MMA = 2048 B down the tile = +128 in the address field
+                        umma_bf16(tmem_base, da0 + (uint64_t)(k * 128), db0 + (uint64_t)(k * 128), idesc, (i == 0 && k == 0) ? 0u : 1u);
                     umma_commit(&empty_bar[s]);
                 }
                 umma_commit(tmem_full_bar);

@@ -8,12 +8,17 @@
 
 static std::atomic<int> g_tc_enabled{1};
 
-bool pb_tc_enabled() { return g_tc_enabled.load(std::memory_order_relaxed) != 0; }
+static void* g_debug_ptr = nullptr;
+void* pb_debug_ptr() { return g_debug_ptr; }
+extern "C" void pb_debug_buffer(void* p) { g_debug_ptr = p; }
 
-extern "C" int pb_set_tensor_cores(int enabled) { return g_tc_enabled.exchange(enabled ? 1 : 0); }
+bool pb_tc_enabled() { return g_tc_enabled.load(std::memory_order_relaxed) != 0; }
+int pb_tc_mode() { return g_tc_enabled.load(std::memory_order_relaxed); }
+
+extern "C" int pb_set_tensor_cores(int enabled) { return g_tc_enabled.exchange(enabled < 0 ? 0 : enabled); }
 
 int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                      const uint32_t* box) {
+                      const uint32_t* box, int swizzle_bytes) {
     static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
     if (!encode) {
         void* fn = nullptr;
@@ -33,7 +38,9 @@ int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64
         gstr[i] = strides_bytes[i];
     }
     CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE),
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     PB_REQUIRE(r == CUDA_SUCCESS, PB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return PB_OK;

@@ -18,10 +18,10 @@ def pb():
     return proteinbert_b200
 
 
-def both_engines(pb, fn):
+def both_engines(pb, fn, modes=(0, 1)):
     lib = pb._lib.lib()
     outs = []
-    for enabled in (0, 1):
+    for enabled in modes:
         lib.pb_set_tensor_cores(enabled)
         try:
             outs.append([o.float().clone() for o in fn()])
@@ -155,3 +155,33 @@ def test_ln_apply_fast_path(pb):
               torch.cuda.current_stream().cuda_stream)
     ref = torch.nn.functional.layer_norm(u.double(), (L, C), gamma.double(), beta.double(), 1e-5)
     assert rel_fro(h, ref) < 3e-3
+
+
+@pytest.mark.parametrize("mode", [1, 4])
+def test_conv_pair_both_kernel_generations(pb, mode):
+    """The 256-position halo kernel (tc_conv2.cu, mode 1 = default) and the first-generation kernel (tc_conv.cu,
+    mode 4) against the SIMT engine."""
+    from proteinbert_b200 import ops
+    x = rnd(B, L, C, seed=1).cuda().bfloat16()
+    wn, ww = rnd(C, C, KS, scale=0.05, seed=2).cuda(), rnd(C, C, KS, scale=0.05, seed=3).cuda()
+    bn, bw, g2l = rnd(C, seed=4).cuda(), rnd(C, seed=5).cuda(), rnd(B, C, seed=6).cuda()
+    wn_f, wn_b = ops.conv_pack(wn, 1)
+    ww_f, ww_b = ops.conv_pack(ww, 1)
+    du = rnd(B, L, C, scale=0.1, seed=9).cuda().bfloat16()
+
+    def run():
+        st = torch.cuda.current_stream().cuda_stream
+        zn, zw, u = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+        stats = torch.zeros(B, 2, dtype=torch.float64, device="cuda")
+        ops._call("pb_conv_pair_fwd", x.data_ptr(), wn_f.data_ptr(), ww_f.data_ptr(), bn.data_ptr(), bw.data_ptr(), g2l.data_ptr(),
+                  zn.data_ptr(), zw.data_ptr(), u.data_ptr(), stats.data_ptr(), B, L, C, KS, DIL, 1, st)
+        dzn, dzw, dx = torch.empty_like(x), torch.empty_like(x), torch.empty_like(x)
+        dWn, dWw = torch.empty(C, C, KS, device="cuda"), torch.empty(C, C, KS, device="cuda")
+        dbn, dbw, dg2l = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(B, C, device="cuda")
+        ops._call("pb_conv_pair_bwd", du.data_ptr(), zn.data_ptr(), zw.data_ptr(), x.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(),
+                  dzn.data_ptr(), dzw.data_ptr(), dx.data_ptr(), dWn.data_ptr(), dWw.data_ptr(), dbn.data_ptr(), dbw.data_ptr(),
+                  dg2l.data_ptr(), B, L, C, KS, DIL, 1, *wsargs(pb), st)
+        return zn, zw, u, stats, dx
+
+    simt, tc = both_engines(pb, run, modes=(0, mode))
+    compare(["zn", "zw", "u", "stats", "dx"], simt, tc)
