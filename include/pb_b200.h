@@ -203,6 +203,17 @@ int pb_token_head_bwd(const float* dP, const float* p_local, const void* h_act, 
                       const double* grad_scale, void* dh_act, float* dWo, float* dbo, int B, int L, int C, int V,
                       int dt, void* stream);
 
+/* Tensor-core variant of the token head (PB_BF16 activations; C, L multiples of 128; V <= 32).  wo_pad / woT_pad are
+ * the output weight zero-padded to 128 vocabulary rows, [128, C] and its transpose [C, 128], type wt.  logits_ws
+ * [B*L, 32] float and dlogit_ws [B*L, 128] wt are scratch; dWo_pad [128, C] float receives dWo in its first V rows;
+ * dbo is ACCUMULATED (zero on entry); ws as pb_workspace_bytes("wgrad", 0, 0, 0). */
+int pb_token_head_tc_ok(int B, int L, int C, int V);
+int pb_token_head_fwd_tc(const void* h_act, const void* wo_pad, const float* bo, float* logits_ws, float* p_local, int B,
+                         int L, int C, int V, void* stream);
+int pb_token_head_bwd_tc(const float* dP, const float* p_local, const void* h_act, const void* woT_pad,
+                         const double* grad_scale, void* dlogit_ws, void* dh_act, float* dWo_pad, float* dbo, int B, int L,
+                         int C, int V, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- a17: the loss of utils.py:293-294 with CrossEntropyLoss/BCELoss(reduction='none') ----------
  * loss[0] = mean(CE(p_local over V, y_local) * w_local) + mean(BCE(p_global, y_global) * w_global)
  * (loss[1], loss[2] = the two terms), double.  When dP_local / dP_global are non-NULL they receive

@@ -50,6 +50,9 @@ PROTOTYPES = {
     "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_token_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
+    "pb_token_head_tc_ok": [_i, _i, _i, _i],
+    "pb_token_head_fwd_tc": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
+    "pb_token_head_bwd_tc": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_pretrain_loss": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_sigmoid_bwd": [_p, _p, _p, _p, _ll, _p],
     "pb_corrupt_pad": [_p] * 16 + [_i, _i, _i, _p],

@@ -2,6 +2,7 @@
 // Reference call sites: modules.py:249-253,277-293,300,304; utils.py:293-294; dummy_tests.py:132-133.
 #include "common.cuh"
 #include "../../include/pb_b200.h"
+#include "tc_api.cuh"
 
 namespace {
 
@@ -157,6 +158,64 @@ __global__ void token_head_bwd_kernel(const float* __restrict__ dP, const float*
     for (int i = threadIdx.x; i < V; i += blockDim.x) atomicAdd(&dbo[i], sb[i]);
 }
 
+// ---- token head, tensor-core path: the GEMMs run in tc_gemm.cu; these are the batch-axis softmax around them ----
+// logits32 [B*L, 32] fp32 (columns >= V unused) -> p_local [B, L, V]; one thread per (l, v), walking the batch
+__global__ void softmax_batch_kernel(const float* __restrict__ logits32, const float* __restrict__ bo, float* __restrict__ p_local,
+                                     int B, int L, int V) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L * 32) return;
+    const int l = i >> 5, v = i & 31;
+    if (v >= V) return;
+    const float bias = bo[v];
+    float mx = -INFINITY, s = 0.f;
+#pragma unroll 8
+    for (int b = 0; b < B; ++b) {                       // online max / sum
+        const float x = logits32[((size_t)b * L + l) * 32 + v] + bias;
+        const float m2 = fmaxf(mx, x);
+        s = s * expf(mx - m2) + expf(x - m2);
+        mx = m2;
+    }
+    const float inv = 1.0f / s;
+#pragma unroll 8
+    for (int b = 0; b < B; ++b) {
+        const float x = logits32[((size_t)b * L + l) * 32 + v] + bias;
+        p_local[((size_t)b * L + l) * V + v] = expf(x - mx) * inv;
+    }
+}
+
+// dlogit[b,l,v] = s * p * (dP - sum_b' p dP) as bf16 into a [B*L, 128] buffer (columns >= V zero); dbo[v] += sum
+__global__ void token_dlogit_kernel(const float* __restrict__ dP, const float* __restrict__ p_local, const double* __restrict__ gscale,
+                                    bf16* __restrict__ dlogit_pad, float* __restrict__ dbo, int B, int L, int V) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L * 32) return;
+    const int l = i >> 5, v = i & 31;
+    const float gs = gscale ? (float)(*gscale) : 1.0f;
+    float dot = 0.f;
+    if (v < V) {
+#pragma unroll 8
+        for (int b = 0; b < B; ++b) {
+            const size_t gi = ((size_t)b * L + l) * V + v;
+            dot += p_local[gi] * dP[gi];
+        }
+    }
+    float sb = 0.f;
+    const bf16 zero = __float2bfloat16_rn(0.f);
+#pragma unroll 4
+    for (int b = 0; b < B; ++b) {
+        float d = 0.f;
+        if (v < V) {
+            const size_t gi = ((size_t)b * L + l) * V + v;
+            d = gs * p_local[gi] * (dP[gi] - dot);
+        }
+        bf16* row = dlogit_pad + ((size_t)b * L + l) * 128;
+        const bf16 db_ = __float2bfloat16_rn(d);
+        row[v] = db_;
+        row[v + 32] = zero; row[v + 64] = zero; row[v + 96] = zero;
+        sb += __bfloat162float(db_);
+    }
+    if (v < V) atomicAdd(&dbo[v], sb);
+}
+
 // ---- loss ---------------------------------------------------------------------------------------
 // Token term: CE over the vocabulary axis of the PROBABILITIES (second softmax), times w_local, / (B*L).
 // Annotation term: BCE with logs clamped at -100, times w_global, / (B*A).  fp64 accumulation.
@@ -291,6 +350,35 @@ int pb_sigmoid_bwd(const float* dP, const float* p, const double* grad_scale, fl
     sigmoid_bwd_kernel<<<(int)min((long long)ceil_div(n, 256), 148LL * 8), 256, 0, (cudaStream_t)stream>>>(dP, p, grad_scale, dZ, n);
     pb_count_launch(1);
     return pb_check_launch("pb_sigmoid_bwd");
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int pb_token_head_tc_ok(int B, int L, int C, int V) { return pb_tc_token_ok(B, L, C, V) ? 1 : 0; }
+
+int pb_token_head_fwd_tc(const void* h, const void* wo_pad, const float* bo, float* logits_ws, float* p_local, int B, int L, int C,
+                         int V, void* stream) {
+    PB_REQUIRE(pb_tc_token_ok(B, L, C, V), PB_ERR_UNSUPPORTED, "token_head_fwd_tc: shape not covered (C %% 128, L %% 128, V <= 32)");
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = pb_tc_token_logits(h, wo_pad, logits_ws, B, L, C, st);
+    if (rc) return rc;
+    softmax_batch_kernel<<<ceil_div((long)L * 32, 128), 128, 0, st>>>(logits_ws, bo, p_local, B, L, V);
+    pb_count_launch(1);
+    return pb_check_launch("pb_token_head_fwd_tc");
+}
+
+int pb_token_head_bwd_tc(const float* dP, const float* p_local, const void* h, const void* woT_pad, const double* grad_scale,
+                         void* dlogit_ws, void* dh, float* dWo_pad, float* dbo, int B, int L, int C, int V, void* ws,
+                         size_t ws_bytes, void* stream) {
+    PB_REQUIRE(pb_tc_token_ok(B, L, C, V), PB_ERR_UNSUPPORTED, "token_head_bwd_tc: shape not covered");
+    cudaStream_t st = (cudaStream_t)stream;
+    token_dlogit_kernel<<<ceil_div((long)L * 32, 128), 128, 0, st>>>(dP, p_local, grad_scale, (bf16*)dlogit_ws, dbo, B, L, V);
+    pb_count_launch(1);
+    int rc = pb_check_launch("pb_token_head_bwd_tc(dlogit)");
+    if (rc) return rc;
+    return pb_tc_token_bwd(dlogit_ws, woT_pad, h, dh, dWo_pad, B, L, C, ws, ws_bytes, st);
 }
 
 }  // extern "C"

@@ -33,3 +33,7 @@ int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* 
 int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
                       int L, int ksize, int dil, int bo_mode, cudaStream_t st);
 void* pb_debug_ptr();
+bool pb_tc_token_ok(int B, int L, int C, int V);
+int pb_tc_token_logits(const void* h, const void* wo_pad, float* logits32, int B, int L, int C, cudaStream_t st);
+int pb_tc_token_bwd(const void* dlogit_pad, const void* woT_pad, const void* h, void* dh, float* dWo_pad, int B, int L, int C,
+                    void* ws, size_t ws_bytes, cudaStream_t st);

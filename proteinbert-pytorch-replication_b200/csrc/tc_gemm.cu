@@ -21,7 +21,7 @@ constexpr int kStageBytes = (kBM + kBN) * 64 * 2;          // 32 KB
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + 4 * kBN * 4;
 constexpr int kThreads = 192;
 
-enum { EPI_LINEAR_FWD = 0, EPI_POOL_FWD = 1, EPI_POOL_DZ = 2, EPI_ADD_STORE = 3 };
+enum { EPI_LINEAR_FWD = 0, EPI_POOL_FWD = 1, EPI_POOL_DZ = 2, EPI_ADD_STORE = 3, EPI_STORE_F32_32 = 4, EPI_STORE = 5 };
 
 struct GemmEpi {
     int ldn;                       // row pitch (elements) of the [M, ldn] tensors touched by the epilogue
@@ -33,6 +33,7 @@ struct GemmEpi {
     double* stats;                 // [B, 2]
     float* pool;                   // [B, ldn]
     const float* dpool;            // [B, ldn]
+    float* f32out;                 // EPI_STORE_F32_32: [M, 32] fp32 (first 32 columns of the tile)
 };
 
 // transpose-reduce: on return lane i holds the sum over the warp's 32 lanes of v[i]
@@ -156,6 +157,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
                     *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(od)[v];
+            } else if (EPI == EPI_STORE_F32_32) {
+                if (ch == 0 && n0 == 0) {
+                    float* o = ep.f32out + (size_t)row * 32;
+#pragma unroll
+                    for (int v = 0; v < 8; ++v)
+                        reinterpret_cast<float4*>(o)[v] = make_float4(acc[4 * v], acc[4 * v + 1], acc[4 * v + 2], acc[4 * v + 3]);
+                }
+            } else if (EPI == EPI_STORE) {
+                __align__(16) bf16 oo[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) oo[j] = __float2bfloat16_rn(acc[j]);
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oo)[v];
             } else {
                 uint4 bv[4];
 #pragma unroll
@@ -448,4 +463,23 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
     if (rc) return rc;
     if (dWvT) rc = launch_wgrad(dzv, nullptr, h, dWvT, nullptr, C, 1, 0, B, L, G, C, 1, 1, 1, ws, ws_bytes, st, "tc_attn_pool_bwd(dWv)", head_dv);
     return rc;
+}
+
+// ---- token head on tensor cores (modules.py:277-284): logits = h Wo^T with Wo zero-padded to 128 rows ----------
+bool pb_tc_token_ok(int B, int L, int C, int V) { return pb_tc_enabled() && C % 128 == 0 && L % 128 == 0 && V <= 32 && B >= 1; }
+
+int pb_tc_token_logits(const void* h, const void* wo_pad, float* logits32, int B, int L, int C, cudaStream_t st) {
+    GemmEpi ep{};
+    ep.ldn = 128; ep.L = L; ep.f32out = logits32;
+    return launch_gemm<EPI_STORE_F32_32>(h, wo_pad, ep, B * L, 128, C, st, "tc_token_logits");
+}
+
+int pb_tc_token_bwd(const void* dlogit_pad, const void* woT_pad, const void* h, void* dh, float* dWo_pad, int B, int L, int C,
+                    void* ws, size_t ws_bytes, cudaStream_t st) {
+    // dh = dlogit Wo (K = 128 padded vocabulary)  ;  dWo_pad[v, c] = sum_rows dlogit[row, v] h[row, c]
+    GemmEpi ep{};
+    ep.ldn = C; ep.L = L; ep.out0 = (bf16*)dh;
+    int rc = launch_gemm<EPI_STORE>(dlogit_pad, woT_pad, ep, B * L, C, 128, st, "tc_token_bwd(dh)");
+    if (rc) return rc;
+    return launch_wgrad(dlogit_pad, nullptr, h, dWo_pad, nullptr, C, 1, 0, B, L, 128, C, 1, 1, 1, ws, ws_bytes, st, "tc_token_bwd(dWo)");
 }

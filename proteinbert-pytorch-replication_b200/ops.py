@@ -463,7 +463,8 @@ class AttnPoolFn(torch.autograd.Function):
 
 
 class TokenHeadFn(torch.autograd.Function):
-    """softmax over the batch axis of Linear(C->V)(h)  (modules.py:277-284,304)."""
+    """softmax over the batch axis of Linear(C->V)(h)  (modules.py:277-284,304).  bf16 activations with
+    tensor-core-friendly shapes take the tcgen05 GEMM path; everything else the one-CTA-per-position kernel."""
 
     @staticmethod
     def forward(ctx, h, Wo, bo):
@@ -472,23 +473,46 @@ class TokenHeadFn(torch.autograd.Function):
         dt = dt_of(h)
         B, L, C = h.shape
         V = Wo.shape[0]
-        p = torch.empty((B, L, V), dtype=torch.float32, device=h.device)
-        _call("pb_token_head_fwd", _p(h), _p(Wo.contiguous()), _p(bo), _p(p), B, L, C, V, dt, _st())
-        ctx.save_for_backward(h, Wo, p)
+        dev = h.device
+        p = torch.empty((B, L, V), dtype=torch.float32, device=dev)
+        tc = dt == BF16 and bool(lib().pb_token_head_tc_ok(B, L, C, V))
+        ctx.tc = tc
+        if tc:
+            # Wo zero-padded to 128 vocabulary rows, and its transpose: the K-major operands of the two GEMMs
+            pad = torch.zeros((2, 128, C), dtype=torch.bfloat16, device=dev) if C == 128 else None
+            wo_pad = pad[0] if pad is not None else torch.zeros((128, C), dtype=torch.bfloat16, device=dev)
+            woT_pad = pad[1] if pad is not None else torch.zeros((C, 128), dtype=torch.bfloat16, device=dev)
+            wo_pad[:V].copy_(Wo)
+            woT_pad[:, :V].copy_(Wo.t())
+            logits = torch.empty((B * L, 32), dtype=torch.float32, device=dev)
+            _call("pb_token_head_fwd_tc", _p(h), _p(wo_pad), _p(bo), _p(logits), _p(p), B, L, C, V, _st())
+            ctx.save_for_backward(h, Wo, p, woT_pad)
+        else:
+            _call("pb_token_head_fwd", _p(h), _p(Wo.contiguous()), _p(bo), _p(p), B, L, C, V, dt, _st())
+            ctx.save_for_backward(h, Wo, p)
         return p
 
     @staticmethod
     def backward(ctx, dP):
-        h, Wo, p = ctx.saved_tensors
+        h, Wo, p = ctx.saved_tensors[:3]
         dt = dt_of(h)
         B, L, C = h.shape
         V = Wo.shape[0]
+        dev = h.device
         dP = dP.contiguous().float()
         dh = torch.empty_like(h)
+        if ctx.tc:
+            woT_pad = ctx.saved_tensors[3]
+            dlogit = torch.empty((B * L, 128), dtype=torch.bfloat16, device=dev)
+            dWo_pad = torch.empty((128, C), dtype=torch.float32, device=dev)
+            dbo = torch.zeros((V,), dtype=torch.float32, device=dev)
+            _call("pb_token_head_bwd_tc", _p(dP), _p(p), _p(h), _p(woT_pad), None, _p(dlogit), _p(dh), _p(dWo_pad), _p(dbo),
+                  B, L, C, V, *_wgrad_ws(dev), _st())
+            return dh, dWo_pad[:V], dbo
         dWo = torch.empty_like(Wo)
-        dbo = torch.empty((V,), dtype=torch.float32, device=h.device)
+        dbo = torch.empty((V,), dtype=torch.float32, device=dev)
         _call("pb_token_head_bwd", _p(dP), _p(p), _p(h), _p(Wo.contiguous()), None, _p(dh), _p(dWo), _p(dbo), B, L, C, V,
-                                      dt, _st())
+              dt, _st())
         return dh, dWo, dbo
 
 

@@ -185,3 +185,26 @@ def test_conv_pair_both_kernel_generations(pb, mode):
 
     simt, tc = both_engines(pb, run, modes=(0, mode))
     compare(["zn", "zw", "u", "stats", "dx"], simt, tc)
+
+
+def test_token_head_tensor_core_path(pb):
+    """bf16 token head through the tcgen05 GEMMs + batch softmax kernels vs an fp64 torch evaluation."""
+    from proteinbert_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    Bt, Lt, V = 6, 128, 26
+    assert pb._lib.lib().pb_token_head_tc_ok(Bt, Lt, C, V)
+    h = torch.randn(Bt, Lt, C, generator=g).bfloat16()
+    Wo, bo = (torch.randn(V, C, generator=g) * 0.3), torch.randn(V, generator=g)
+    hd, Wd, bd = h.cuda().requires_grad_(), Wo.cuda().requires_grad_(), bo.cuda().requires_grad_()
+    p = ops.TokenHeadFn.apply(hd, Wd, bd)
+    assert torch.allclose(p.sum(0), torch.ones(Lt, V, device="cuda"), atol=1e-5)
+    hr = h.double().requires_grad_()
+    Wr, br = Wo.bfloat16().double().requires_grad_(), bo.double().requires_grad_()
+    pr = torch.softmax(hr @ Wr.t() + br, dim=0)
+    assert rel_fro(p, pr) < 1e-3
+    dP = torch.randn(Bt, Lt, V, generator=g)
+    p.backward(dP.cuda())
+    pr.backward(dP.double())
+    assert rel_fro(hd.grad, hr.grad) < 1e-2
+    assert rel_fro(Wd.grad, Wr.grad) < 1e-2
+    assert float(bd.grad.abs().max()) < 1e-3 * float(Wd.grad.abs().max())     # mathematically zero
