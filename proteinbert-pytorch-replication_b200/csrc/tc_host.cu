@@ -48,24 +48,37 @@ int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64
 
 namespace {
 
-// h = (u - mean) * rstd * gamma + beta, 8 bf16 per thread; grid = (chunks, B)
+// h = (u - mean) * rstd * gamma + beta, 8 bf16 per thread.  grid = (ceil(nv/256), sample groups): a thread owns one
+// 8-wide (l,c) vector and walks its group's samples, so the [L,C] affine (8 bytes per element against 4 bytes of
+// activation traffic) is read once per group instead of once per sample.
 __global__ void ln_apply_bf16_kernel(const bf16* __restrict__ u, const double* __restrict__ stats, const float* __restrict__ gamma,
-                                     const float* __restrict__ beta, bf16* __restrict__ h, long long n, float eps) {
+                                     const float* __restrict__ beta, bf16* __restrict__ h, long long n, float eps, int B,
+                                     int per_group) {
+    extern __shared__ float prm[];            // [per_group][2] mean, rstd
     pdl_wait();
-    const int b = blockIdx.y;
-    const LnStat st = ln_stat(stats, b, (double)n, eps);
-    const long long nv = n / 8;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
-        const uint4 uv = *reinterpret_cast<const uint4*>(u + (size_t)b * n + i * 8);
-        const float4 g0 = *reinterpret_cast<const float4*>(gamma + i * 8), g1 = *reinterpret_cast<const float4*>(gamma + i * 8 + 4);
-        const float4 b0 = *reinterpret_cast<const float4*>(beta + i * 8), b1 = *reinterpret_cast<const float4*>(beta + i * 8 + 4);
+    const int b0 = blockIdx.y * per_group;
+    const int nb = min(per_group, B - b0);
+    for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+        const LnStat st = ln_stat(stats, b0 + k, (double)n, eps);
+        prm[2 * k] = st.mean; prm[2 * k + 1] = st.rstd;
+    }
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n / 8) return;
+    const float4 g0 = *reinterpret_cast<const float4*>(gamma + i * 8), g1 = *reinterpret_cast<const float4*>(gamma + i * 8 + 4);
+    const float4 c0 = *reinterpret_cast<const float4*>(beta + i * 8), c1 = *reinterpret_cast<const float4*>(beta + i * 8 + 4);
+    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float bb[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll 4
+    for (int k = 0; k < nb; ++k) {
+        const size_t off = (size_t)(b0 + k) * n + i * 8;
+        const uint4 uv = *reinterpret_cast<const uint4*>(u + off);
         const bf16* ub = reinterpret_cast<const bf16*>(&uv);
-        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        const float mean = prm[2 * k], rstd = prm[2 * k + 1];
         __align__(16) bf16 o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16_rn((__bfloat162float(ub[j]) - st.mean) * st.rstd * gg[j] + bb[j]);
-        *reinterpret_cast<uint4*>(h + (size_t)b * n + i * 8) = *reinterpret_cast<const uint4*>(o);
+        for (int j = 0; j < 8; ++j) o[j] = __float2bfloat16_rn((__bfloat162float(ub[j]) - mean) * rstd * gg[j] + bb[j]);
+        *reinterpret_cast<uint4*>(h + off) = *reinterpret_cast<const uint4*>(o);
     }
 }
 
@@ -75,9 +88,16 @@ bool pb_tc_ln_apply_ok(int L, int C) { return ((long long)L * C) % 8 == 0; }
 
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st) {
-    const long long n = (long long)L * C;
-    dim3 grid((unsigned)max(1, min(ceil_div(n / 8, 256), 16)), B);
-    PB_CUDA(pb_launch_pdl(ln_apply_bf16_kernel, grid, dim3(256), 0, st, (const bf16*)u, stats, gamma, beta, (bf16*)h, n, eps));
+    const long long n = (long long)L * C, nv = n / 8;
+    // enough sample groups for ~150k threads in flight, at most 16 samples per thread
+    int groups = (int)((151552 + nv - 1) / nv);
+    if (groups > B) groups = B;
+    if (groups < (B + 15) / 16) groups = (B + 15) / 16;
+    const int per_group = (B + groups - 1) / groups;
+    groups = (B + per_group - 1) / per_group;
+    dim3 grid((unsigned)ceil_div(nv, 256), groups);
+    PB_CUDA(pb_launch_pdl(ln_apply_bf16_kernel, grid, dim3(256), 2 * per_group * sizeof(float), st, (const bf16*)u, stats, gamma, beta,
+                          (bf16*)h, n, eps, B, per_group));
     pb_count_launch(1);
     return pb_check_launch("pb_ln_joint_apply(bf16)");
 }
