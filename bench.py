@@ -261,8 +261,13 @@ def main():
     peaks = load_peaks()
     peak_tf = peaks["bf16_tflops_sustained"]
     achieved_tf = conv_flops / (conv_ms_mean * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_conv_traffic.json")
+    if os.path.exists(tpath) and B == 64:          # dram bytes per launch from the committed ncu --set full capture
+        t = json.load(open(tpath))
+        traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     roofline = {"kernel": "conv_pair_fwd", "bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": achieved_tf / peak_tf, "traffic": None, "peak_source": f"{peaks['_source']} bf16_tflops_sustained",
+                "frac": achieved_tf / peak_tf, "traffic": traffic, "peak_source": f"{peaks['_source']} bf16_tflops_sustained",
                 "us_per_launch": conv_ms_mean * 1e3, "launches_timed": len(conv_ms)}
 
     # ---- e2e: public API from pinned host buffers, H2D of inputs + D2H of the loss inside the timed region ----
