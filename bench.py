@@ -171,7 +171,9 @@ def main():
     dev = torch.device("cuda", local_rank)
     pb._lib.check(pb._lib.lib().pb_device_ok(local_rank), "pb_device_ok")
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        _opts = dist.ProcessGroupNCCL.Options()
+        _opts.is_high_priority_stream = True      # the all-reduce has to get SMs while backward kernels are queued
+        dist.init_process_group("nccl", device_id=dev, pg_options=_opts)
 
     torch.manual_seed(0)
     model = pb.ProteinBERT(device=dev, precision=args.precision, **CFG)

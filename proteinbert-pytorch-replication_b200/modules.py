@@ -216,7 +216,10 @@ class ProteinBERT(nn.Module):
         g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU)                    # :301
         blocks = list(self.proteinBERT_blocks)
         ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
-        for blk in blocks:
+        cut = getattr(self, "_boundary_at", None)        # training.GraphedPretrainStep: where backward is split in two
+        for i, blk in enumerate(blocks):
+            if cut is not None and i == cut:
+                self._boundary = (h, g)
             blk._prestaged = dt
             h, g = blk.forward_channels_last(h, g)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]

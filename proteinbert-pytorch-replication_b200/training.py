@@ -72,9 +72,10 @@ class FlatGradBucket:
         ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 1, 1.0,
                   torch.cuda.current_stream().cuda_stream)
 
-    def all_reduce(self):
+    def all_reduce(self, async_op: bool = False):
         if self.world > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+            return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+        return None
 
     def scatter(self):
         ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 0, 1.0 / self.world,
@@ -88,36 +89,89 @@ class GraphedPretrainStep:
     needs to run them, so the public fast path is: copy the batch into static device buffers (one async H2D per
     tensor, from pinned memory if the caller provides it), replay the graph, read the loss.  Gradients are
     written to the parameters' static ``.grad`` tensors, ready for ``optimizer.step()``.  Shapes are fixed at
-    construction.  Under torch.distributed (world > 1) the captured region ends with a gather of all 133
-    gradients into one flat bucket; each call then all-reduces the bucket (NCCL, outside the graph) and scatters
-    it back scaled by 1/world, so every rank ends the step with the averaged gradients.
+    construction.  Under torch.distributed (world > 1) backward is captured as TWO graphs split at the middle block:
+    after the first (forward, loss, heads and upper blocks) its gradients are gathered into a flat bucket (one
+    kernel) and all-reduced asynchronously by NCCL while the second graph (lower blocks, embedding, annotation
+    input layer) replays; the second bucket follows, then one scatter kernel per bucket applies 1/world
+    (``overlap=False``: one graph, one bucket reduced after it).
 
         step = GraphedPretrainStep(model, X, Y, W)      # example batch fixes shapes / dtypes
         loss = step(X, Y, W)                            # host or device tensors
     """
 
-    def __init__(self, model, X, Y, W, warmup: int = 3):
+    def __init__(self, model, X, Y, W, warmup: int = 3, overlap: bool = True, force_split: bool = False):
         dev = next(model.parameters()).device
         self.model = model
         self.device = dev
         self.static = [t.to(dev).clone() for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])]
         sx, sy, sw = self._dicts()
+        distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        nblk = len(model.proteinBERT_blocks)
+        self.split = ((distributed and overlap) or force_split) and nblk >= 2
+        self.bucket = self.bucket_a = self.bucket_b = None
+        self.graph_b = None
+        cut = nblk // 2
+
+        # ---- two-stage backward (data-parallel): stage A = forward + loss + backward down to the input of block
+        # `cut`; stage B = the rest.  The gradients of stage A are all-reduced while stage B runs.
+        upper = [p for n, p in model.named_parameters()
+                 if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut)]
+        upper_ids = {id(p) for p in upper}
+        lower = [p for p in model.parameters() if id(p) not in upper_ids]
+        upper_heads = [h.Wv_parameter for blk in list(model.proteinBERT_blocks)[cut:]
+                       for h in blk.global_attention_layer.global_attention_heads if blk.head_grads]
+
+        def stage_a():
+            for p in model.parameters():
+                p.grad = None
+            model._boundary_at = cut
+            try:
+                p_local, p_global = model(sx)
+            finally:
+                model._boundary_at = None
+            loss = pretraining_loss(p_local, p_global, sy, sw)
+            hb, gb = model._boundary
+            model._boundary = None
+            grads = torch.autograd.grad(loss, upper + upper_heads + [hb, gb], retain_graph=True)
+            for p, g in zip(upper + upper_heads, grads):
+                p.grad = g
+            return loss.detach(), hb, gb, grads[-2], grads[-1]
+
+        def stage_b(hb, gb, dhb, dgb):
+            torch.autograd.backward([hb, gb], [dhb, dgb])
+
+        def full_step():
+            if self.split:
+                out = stage_a()
+                stage_b(*out[1:])
+                return out[0]
+            return pretraining_step(model, sx, sy, sw)
+
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             for _ in range(warmup):
-                pretraining_step(model, sx, sy, sw)
+                full_step()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         for p in model.parameters():
             p.grad = None
         self.graph = torch.cuda.CUDAGraph()
-        self.bucket = None
-        distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        with torch.cuda.graph(self.graph):
-            self.loss = pretraining_step(model, sx, sy, sw)
-        if distributed:            # the captured backward fixed the gradient addresses: build the flat bucket over them
-            self.bucket = FlatGradBucket(model.parameters())
+        if self.split:
+            with torch.cuda.graph(self.graph):
+                out = stage_a()
+            self.loss = out[0]
+            self.graph_b = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_b, pool=self.graph.pool()):
+                stage_b(*out[1:])
+            del out
+            self.bucket_a = FlatGradBucket(upper)
+            self.bucket_b = FlatGradBucket(lower)
+        else:
+            with torch.cuda.graph(self.graph):
+                self.loss = pretraining_step(model, sx, sy, sw)
+            if distributed:        # the captured backward fixed the gradient addresses: build the flat bucket over them
+                self.bucket = FlatGradBucket(model.parameters())
 
     def _dicts(self):
         s = self.static
@@ -129,7 +183,17 @@ class GraphedPretrainStep:
             if t is not dst:
                 dst.copy_(t, non_blocking=True)
         self.graph.replay()
-        if self.bucket is not None:
+        if self.split:
+            self.bucket_a.gather()
+            work = self.bucket_a.all_reduce(async_op=True)       # NCCL on its own stream ...
+            self.graph_b.replay()                                # ... while the second half of backward runs
+            self.bucket_b.gather()
+            self.bucket_b.all_reduce()
+            if work is not None:
+                work.wait()
+            self.bucket_a.scatter()
+            self.bucket_b.scatter()
+        elif self.bucket is not None:
             self.bucket.gather()
             self.bucket.all_reduce()
             self.bucket.scatter()
