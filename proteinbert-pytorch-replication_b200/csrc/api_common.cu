@@ -131,7 +131,7 @@ int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_fla
 int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream) {
     if (n <= 0) return PB_OK;
     PB_REQUIRE(jobs_dev != nullptr, PB_ERR_SHAPE, "stage_weights: null job table");
-    dim3 grid(32, n);
+    dim3 grid(96, n);
     if (dt == PB_F32) stage_weights_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);
     else if (dt == PB_BF16) stage_weights_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);
     else { pb_set_error("stage_weights: unknown dtype code %d", dt); return PB_ERR_UNSUPPORTED; }

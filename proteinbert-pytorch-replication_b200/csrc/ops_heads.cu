@@ -49,6 +49,33 @@ __global__ void embedding_bwd_kernel(const int64_t* __restrict__ tok, const T* _
     }
 }
 
+// Warp-privatised variant (no atomics in the hot loop): every warp owns a full [V, C] accumulator in shared memory
+// and walks its own rows; a row's token id is warp-uniform and the lanes split the channels, so each lane updates
+// addresses nobody else touches.  The eight per-warp tables are summed once at the end.
+template <typename T>
+__global__ void embedding_bwd_warp_kernel(const int64_t* __restrict__ tok, const T* __restrict__ dout, float* __restrict__ dtable,
+                                          long long n_tok, int C, int V) {
+    extern __shared__ float acc[];           // [warps][V*C]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    const int VC = V * C;
+    for (int i = threadIdx.x; i < nwarp * VC; i += blockDim.x) acc[i] = 0.f;
+    __syncthreads();
+    float* mine = acc + (size_t)warp * VC;
+    const long long gw = (long long)blockIdx.x * nwarp + warp, nw = (long long)gridDim.x * nwarp;
+    for (long long r = gw; r < n_tok; r += nw) {
+        const int64_t t = tok[r];
+        if (t < 0 || t >= V) continue;
+        float* row = mine + (int)t * C;
+        for (int c = lane; c < C; c += 32) row[c] += ldf(dout, (size_t)r * C + c);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < VC; i += blockDim.x) {
+        float v = 0.f;
+        for (int w = 0; w < nwarp; ++w) v += acc[(size_t)w * VC + i];
+        if (v != 0.f) atomicAdd(&dtable[i], v);
+    }
+}
+
 // ---- token head ---------------------------------------------------------------------------------
 // One CTA per sequence position l (grid-stride).  The softmax runs over the BATCH axis, so the CTA needs
 // all B rows of its position: smem holds h[:, l, :] as float [B][C+1], Wo [V][C+1], logits/probs [B][V].
@@ -292,9 +319,15 @@ int pb_embedding_bwd(const int64_t* tok, const void* dout, float* dtable, long l
     cudaStream_t st = (cudaStream_t)stream;
     PB_CUDA(cudaMemsetAsync(dtable, 0, smem, st));
     const int grid = (int)min((long long)ceil_div(n_tok, 64), 148LL * 2);
+    const size_t smem_w = smem * 8;          // one table per warp
     DISPATCH_DT(dt, {
-        if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        embedding_bwd_kernel<T><<<grid, 256, smem, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
+        if (smem_w <= 200 * 1024) {
+            if (smem_w > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_warp_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w));
+            embedding_bwd_warp_kernel<T><<<min(grid, 148), 256, smem_w, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
+        } else {
+            if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            embedding_bwd_kernel<T><<<grid, 256, smem, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
+        }
     });
     pb_count_launch(1);
     return pb_check_launch("pb_embedding_bwd");

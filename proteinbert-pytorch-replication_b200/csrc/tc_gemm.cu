@@ -34,6 +34,7 @@ struct GemmEpi {
     float* pool;                   // [B, ldn]
     const float* dpool;            // [B, ldn]
     float* f32out;                 // EPI_STORE_F32_32: [M, 32] fp32 (first 32 columns of the tile)
+    int base_in_smem;              // LINEAR_FWD with K == N == 128: the residual h tile is the A operand still in the ring
 };
 
 // transpose-reduce: on return lane i holds the sum over the warp's 32 lanes of v[i]
@@ -55,7 +56,8 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
 
 template <int EPI>
 __global__ void __launch_bounds__(kThreads, 2)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmEpi ep, int K) {
+tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+               const __grid_constant__ CUtensorMap mapS0, const __grid_constant__ CUtensorMap mapS1, GemmEpi ep, int K) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
@@ -118,21 +120,39 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         const int b = m0 / ep.L;                         // tiles never straddle samples (L % 128 == 0)
         const size_t grow = (size_t)row * ep.ldn + n0;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+        // bf16 outputs leave through TMA: each warp stages its 32 x 32 sub-tile (64-byte swizzle) in the last ring
+        // stage, idle by now, and one lane issues the tensor store; two buffers so a store drains behind the math
+        constexpr bool kTmaOut = EPI == EPI_LINEAR_FWD || EPI == EPI_POOL_DZ || EPI == EPI_STORE || EPI == EPI_ADD_STORE;
+        uint8_t* stage = smem + 2 * kStageBytes + (warp - 2) * 8192;
+        const int sw = (lane >> 1) & 3;
+        const int trow = q * 32 + lane;                              // row inside the tile
         float s_sum = 0.f, s_sq = 0.f;
 #pragma unroll 1
         for (int ch = 0; ch < kBN / 32; ++ch) {
             float acc[32];
             tmem_ld32(taddr + ch * 32, acc);
             const int c0 = ch * 32;
+            uint8_t* sbuf = stage + (ch & 1) * 4096;
+            if (kTmaOut && ch >= 2) {
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+            }
             if (EPI == EPI_LINEAR_FWD) {
                 uint4 hv[4];
+                if (ep.base_in_smem) {
+                    const uint8_t* hrow = smem + (ch >> 1) * kStageBytes + (size_t)trow * 128;
 #pragma unroll
-                for (int v = 0; v < 4; ++v) hv[v] = *reinterpret_cast<const uint4*>(ep.base + grow + c0 + v * 8);
+                    for (int v = 0; v < 4; ++v) hv[v] = *reinterpret_cast<const uint4*>(hrow + ((((ch & 1) * 4 + v) ^ (trow & 7)) * 16));
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) hv[v] = *reinterpret_cast<const uint4*>(ep.base + grow + c0 + v * 8);
+                }
                 const bf16* hb = reinterpret_cast<const bf16*>(hv);
+                const float bl = __ldg(ep.bias + n0 + c0 + lane);
                 __align__(16) bf16 oz[32], ou[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const bf16 z = __float2bfloat16_rn(acc[j] + __ldg(ep.bias + n0 + c0 + j));
+                    const bf16 z = __float2bfloat16_rn(acc[j] + __shfl_sync(0xffffffffu, bl, j));
                     oz[j] = z;
                     const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_fast(__bfloat162float(z)));
                     ou[j] = ub;
@@ -141,8 +161,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
 #pragma unroll
                 for (int v = 0; v < 4; ++v) {
-                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oz)[v];
-                    *reinterpret_cast<uint4*>(ep.out1 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(ou)[v];
+                    const int off = lane * 64 + ((v ^ sw) * 16);
+                    *reinterpret_cast<uint4*>(sbuf + off) = reinterpret_cast<const uint4*>(oz)[v];
+                    *reinterpret_cast<uint4*>(sbuf + 2048 + off) = reinterpret_cast<const uint4*>(ou)[v];
                 }
             } else if (EPI == EPI_POOL_FWD) {
 #pragma unroll
@@ -150,13 +171,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 const float cs = warp_transpose_sum(acc, lane);
                 colsum[q * kBN + c0 + lane] = cs;
             } else if (EPI == EPI_POOL_DZ) {
+                const float dl = __ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + lane);
                 __align__(16) bf16 od[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j)
-                    od[j] = __float2bfloat16_rn(__ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + j) * gelu_grad_fast(acc[j]));
+                    od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * gelu_grad_fast(acc[j]));
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
-                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(od)[v];
+                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
             } else if (EPI == EPI_STORE_F32_32) {
                 if (ch == 0 && n0 == 0) {
                     float* o = ep.f32out + (size_t)row * 32;
@@ -170,7 +192,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) oo[j] = __float2bfloat16_rn(acc[j]);
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
-                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oo)[v];
+                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(oo)[v];
             } else {
                 uint4 bv[4];
 #pragma unroll
@@ -181,9 +203,19 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) oo[j] = __float2bfloat16_rn(__bfloat162float(bb[j]) + acc[j]);
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
-                    *reinterpret_cast<uint4*>(ep.out0 + grow + c0 + v * 8) = reinterpret_cast<const uint4*>(oo)[v];
+                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(oo)[v];
+            }
+            if (kTmaOut) {
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&mapS0, sbuf, n0 + c0, m0 + q * 32);
+                    if (EPI == EPI_LINEAR_FWD) tma_store_2d(&mapS1, sbuf + 2048, n0 + c0, m0 + q * 32);
+                    tma_store_commit();
+                }
             }
         }
+        if (kTmaOut && lane == 0) tma_store_wait<0>();
         if (EPI == EPI_LINEAR_FWD) {
             const double ds = warp_sum_d((double)s_sum), dq = warp_sum_d((double)s_sq);
             if (lane == 0) { atomicAdd(&ep.stats[2 * b], ds); atomicAdd(&ep.stats[2 * b + 1], dq); }
@@ -357,16 +389,25 @@ int make_act_map(CUtensorMap* m, const void* base, int B, int L, int C, int box_
 
 template <int EPI>
 int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, int K, cudaStream_t st, const char* what) {
-    CUtensorMap mA, mB;
+    CUtensorMap mA, mB, mS0, mS1;
     int rc;
     if ((rc = make_mat_map(&mA, A, M, K, kBM))) return rc;
     if ((rc = make_mat_map(&mB, Bm, N, K, kBN))) return rc;
+    {   // output maps for the TMA-store epilogue: 32 x 32 boxes of the [M, ldn] bf16 outputs, 64-byte swizzle
+        const uint64_t dims[2] = {(uint64_t)ep.ldn, (uint64_t)M};
+        const uint64_t strides[1] = {(uint64_t)ep.ldn * 2};
+        const uint32_t box[2] = {32, 32};
+        const void* o0 = ep.out0 ? (const void*)ep.out0 : A;
+        const void* o1 = ep.out1 ? (const void*)ep.out1 : o0;
+        if ((rc = pb_make_tmap_bf16(&mS0, o0, 2, dims, strides, box, 64))) return rc;
+        if ((rc = pb_make_tmap_bf16(&mS1, o1, 2, dims, strides, box, 64))) return rc;
+    }
     static bool attr_set = false;
     if (!attr_set) {
         PB_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
-    PB_CUDA(pb_launch_pdl(tc_gemm_kernel<EPI>, dim3(M / kBM, N / kBN), dim3(kThreads), kSmemBytes, st, mA, mB, ep, K));
+    PB_CUDA(pb_launch_pdl(tc_gemm_kernel<EPI>, dim3(M / kBM, N / kBN), dim3(kThreads), kSmemBytes, st, mA, mB, mS0, mS1, ep, K));
     pb_count_launch(1);
     return pb_check_launch(what);
 }
@@ -432,6 +473,7 @@ int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void
                            int C, cudaStream_t st) {
     GemmEpi ep{};
     ep.ldn = C; ep.L = L; ep.bias = bias; ep.base = (const bf16*)h; ep.out0 = (bf16*)z; ep.out1 = (bf16*)u2; ep.stats = stats2;
+    ep.base_in_smem = (C == 128) ? 1 : 0;
     return launch_gemm<EPI_LINEAR_FWD>(h, W, ep, B * L, C, C, st, "tc_local_linear_fwd");
 }
 

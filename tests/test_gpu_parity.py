@@ -62,7 +62,9 @@ def check_fp32(grads, ref_grads, what=""):
     gmax = max(float(v.abs().max()) for v in ref_grads.values())
     for k, ref in ref_grads.items():
         assert grads[k] is not None, k
-        floor = 1e-6 * gmax * np.sqrt(ref.numel()) if any(s in k for s in MATH_ZERO) else 0.0
+        # W_parameter's gradient is a cancelling sum ~1e-4 of the largest gradient: fp32 atomics reorder it run to run,
+        # so it gets the same absolute allowance as the mathematically-zero tensors on top of its relative bound
+        floor = 1e-6 * gmax * np.sqrt(ref.numel()) if any(s in k for s in MATH_ZERO) or k.endswith("W_parameter") else 0.0
         rtol = 2e-3 if k.endswith("W_parameter") else 1e-4
         assert_close_rel(grads[k], ref, rtol, floor=floor, what=f"{what}{k}")
 
