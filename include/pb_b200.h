@@ -170,6 +170,16 @@ int pb_ln_joint_apply(const void* u_act, const double* stats, const float* gamma
  * ACCUMULATED into: zero on entry. */
 int pb_ln_joint_bwd(const void* dy_act, const void* u_act, const double* stats, const float* gamma, void* du_act,
                     float* dgamma, float* dbeta, double* sums, int B, int L, int C, float eps, int dt, void* stream);
+/* The same LayerNorm backward fused with the GELU backward(s) that consume du in the block (modules.py:207-217 run in
+ * reverse): additionally dz0 = du*gelu'(z0), db0[c] += sum dz0 and, when z1 is given, dz1/db1 likewise (z1, dz1, db1 all
+ * NULL otherwise); dsample[b,c] += sum_l du when not NULL (the gradient of the broadcast global->local term).  db0, db1,
+ * dsample, sums, dgamma, dbeta are ACCUMULATED into: zero on entry.  Needs (C/8) to divide 32 (pb_ln_joint_bwd_gelu_ok);
+ * callers then pass z = NULL to pb_local_linear_bwd / zn = NULL to pb_conv_pair_bwd, which take dz as already computed. */
+int pb_ln_joint_bwd_gelu_ok(int B, int L, int C);
+int pb_ln_joint_bwd_gelu(const void* dy_act, const void* u_act, const double* stats, const float* gamma, const void* z0_act,
+                         const void* z1_act, void* du_act, void* dz0_act, void* dz1_act, float* dgamma, float* dbeta,
+                         float* dsample, float* db0, float* db1, double* sums, int B, int L, int C, float eps, int dt,
+                         void* stream);
 
 /* ---- a9: local Linear(C->C)+GELU + residual (modules.py:153-160,214-216) ------------------------
  * z = h W^T + b, u2 = h + gelu(z), stats2[b] += (sum, sumsq) of u2.  W is [C,C] of type wt.        */

@@ -44,6 +44,8 @@ PROTOTYPES = {
     "pb_ln_joint_stats": [_p, _p, _i, _i, _i, _i, _p],
     "pb_ln_joint_apply": [_p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
     "pb_ln_joint_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _f, _i, _p],
+    "pb_ln_joint_bwd_gelu_ok": [_i, _i, _i],
+    "pb_ln_joint_bwd_gelu": [_p] * 15 + [_i, _i, _i, _f, _i, _p],
     "pb_local_linear_fwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_attn_pool_fwd": [_p, _p, _p, _i, _i, _i, _i, _i, _p],

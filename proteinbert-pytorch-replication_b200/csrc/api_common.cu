@@ -178,7 +178,7 @@ size_t pb_workspace_bytes(const char* op, int M, int N, int K) {
     if (!strcmp(op, "linear_fwd")) return (size_t)32 * M * N * sizeof(float);
     if (!strcmp(op, "linear_bwd")) return (size_t)32 * M * K * sizeof(float);
     // split-K partial tiles of the tensor-core weight-gradient GEMMs: at most 148 tiles of 128 x 128 floats
-    if (!strcmp(op, "wgrad")) return (size_t)148 * 128 * 128 * sizeof(float);
+    if (!strcmp(op, "wgrad")) return (size_t)148 * 3 * 128 * 128 * sizeof(float);     // three partial tiles per CTA (tc_wgrad_conv.cu)
     return 0;
 }
 

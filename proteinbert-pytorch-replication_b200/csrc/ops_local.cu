@@ -297,6 +297,11 @@ template <> struct V8<float> {
         *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
     }
     static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_f(z); }
+    struct Raw { float4 a, b; };
+    static __device__ __forceinline__ Raw ld_raw(const float* p) { return Raw{*reinterpret_cast<const float4*>(p), *reinterpret_cast<const float4*>(p + 4)}; }
+    static __device__ __forceinline__ void unpack(const Raw& r, float (&v)[8]) {
+        v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+    }
 };
 template <> struct V8<bf16> {
     static __device__ __forceinline__ void ld(const bf16* p, float (&v)[8]) {
@@ -317,6 +322,13 @@ template <> struct V8<bf16> {
         *reinterpret_cast<uint4*>(p) = r;
     }
     static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_fast(z); }
+    typedef uint4 Raw;
+    static __device__ __forceinline__ Raw ld_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
+    static __device__ __forceinline__ void unpack(const Raw& r, float (&v)[8]) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+    }
 };
 __device__ __forceinline__ void ldf8(const float* p, float (&v)[8]) { V8<float>::ld(p, v); }
 
@@ -462,6 +474,128 @@ __global__ void gelu_bwd_colsum_vec_kernel(const T* __restrict__ dy, const T* __
     }
 }
 
+// LayerNorm input gradient and the GELU gradients that follow it, in one pass over the activations:
+//   du = rstd*(dy*gamma - m1 - xhat*m2)   dz0 = du*gelu'(z0)   [dz1 = du*gelu'(z1)]
+// plus dgamma/dbeta (per (l,c), over the batch), db0/db1 (per channel, over batch and positions) and, if asked,
+// dsample[b,c] = sum_l du.  Same thread layout as ln_bwd_apply_vec_kernel: a thread owns one 8-wide (l,c) vector and
+// walks its group's samples, so the (l,c) and per-channel sums stay in registers; per-sample sums go through one
+// shared-memory slot per warp and sample.  Requires (C/8) to divide 32.
+template <typename T, bool TWO>
+__global__ void __launch_bounds__(256)
+ln_bwd_apply_gelu_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
+                         const float* __restrict__ gamma, const double* __restrict__ sums, const T* __restrict__ z0,
+                         const T* __restrict__ z1, T* __restrict__ du, T* __restrict__ dz0, T* __restrict__ dz1,
+                         float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dsample,
+                         float* __restrict__ db0, float* __restrict__ db1, int B, int C, long long n, float eps, int per_group) {
+    extern __shared__ float sh[];        // [per_group][4] LN parameters | [8 warps][per_group + 2][C] partial column sums
+    float* prm = sh;
+    float* part = sh + 4 * per_group;
+    pdl_wait();
+    const int b0 = blockIdx.y * per_group;
+    const int nb = min(per_group, B - b0);
+    for (int k = threadIdx.x; k < nb; k += blockDim.x) {
+        const LnStat st = ln_stat(stats, b0 + k, (double)n, eps);
+        prm[4 * k] = st.mean; prm[4 * k + 1] = st.rstd;
+        prm[4 * k + 2] = (float)(sums[2 * (b0 + k)] / (double)n);
+        prm[4 * k + 3] = (float)(sums[2 * (b0 + k) + 1] / (double)n);
+    }
+    __syncthreads();
+    const int vpr = C / 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slots = per_group + 2;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = i < n / 8;
+    const int tv = (int)(i % vpr);
+    float* wpart = part + (size_t)warp * slots * C;
+    float g[8], ag[8], ab[8], c0[8], c1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { g[j] = 0.f; ag[j] = 0.f; ab[j] = 0.f; c0[j] = 0.f; c1[j] = 0.f; }
+    if (valid) ldf8(gamma + i * 8, g);
+    // the next sample's operands are requested before this sample's arithmetic: twice the bytes in flight per thread
+    typename V8<T>::Raw rd, rx, ra, rb;
+    if (valid && nb > 0) {
+        const size_t off = (size_t)b0 * n + i * 8;
+        rd = V8<T>::ld_raw(dy + off); rx = V8<T>::ld_raw(u + off); ra = V8<T>::ld_raw(z0 + off);
+        if (TWO) rb = V8<T>::ld_raw(z1 + off);
+    }
+    for (int k = 0; k < nb; ++k) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = 0.f;
+        if (valid) {
+            const size_t off = (size_t)(b0 + k) * n + i * 8;
+            float d[8], x[8], za[8], zb[8], e[8];
+            V8<T>::unpack(rd, d); V8<T>::unpack(rx, x); V8<T>::unpack(ra, za);
+            if (TWO) V8<T>::unpack(rb, zb);
+            if (k + 1 < nb) {
+                rd = V8<T>::ld_raw(dy + off + n); rx = V8<T>::ld_raw(u + off + n); ra = V8<T>::ld_raw(z0 + off + n);
+                if (TWO) rb = V8<T>::ld_raw(z1 + off + n);
+            }
+            const float mean = prm[4 * k], rstd = prm[4 * k + 1], m1 = prm[4 * k + 2], m2 = prm[4 * k + 3];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float xh = (x[j] - mean) * rstd;
+                o[j] = rstd * (d[j] * g[j] - m1 - xh * m2);
+                ag[j] += d[j] * xh;
+                ab[j] += d[j];
+            }
+            V8<T>::st(du + off, o);                  // o now holds the stored (rounded) values
+#pragma unroll
+            for (int j = 0; j < 8; ++j) e[j] = o[j] * V8<T>::gelu_grad(za[j]);
+            V8<T>::st(dz0 + off, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) c0[j] += e[j];
+            if (TWO) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) e[j] = o[j] * V8<T>::gelu_grad(zb[j]);
+                V8<T>::st(dz1 + off, e);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) c1[j] += e[j];
+            }
+        }
+        if (dsample != nullptr) {        // fold the rows this warp holds, one slot per warp and sample
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                for (int s = 16; s >= vpr; s >>= 1) o[j] += __shfl_xor_sync(0xffffffffu, o[j], s);
+            if (lane < vpr) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) wpart[(size_t)(2 + k) * C + tv * 8 + j] = o[j];
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        for (int s = 16; s >= vpr; s >>= 1) {
+            c0[j] += __shfl_xor_sync(0xffffffffu, c0[j], s);
+            if (TWO) c1[j] += __shfl_xor_sync(0xffffffffu, c1[j], s);
+        }
+    if (lane < vpr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            wpart[tv * 8 + j] = c0[j];
+            wpart[C + tv * 8 + j] = c1[j];
+        }
+    }
+    if (valid) {
+        atomicAdd(reinterpret_cast<float4*>(dgamma + i * 8), make_float4(ag[0], ag[1], ag[2], ag[3]));
+        atomicAdd(reinterpret_cast<float4*>(dgamma + i * 8 + 4), make_float4(ag[4], ag[5], ag[6], ag[7]));
+        atomicAdd(reinterpret_cast<float4*>(dbeta + i * 8), make_float4(ab[0], ab[1], ab[2], ab[3]));
+        atomicAdd(reinterpret_cast<float4*>(dbeta + i * 8 + 4), make_float4(ab[4], ab[5], ab[6], ab[7]));
+    }
+    __syncthreads();
+    // across the 8 warps: slot 0 -> db0, slot 1 -> db1, slot 2+k -> dsample[b0+k]
+    const int first = 0, last = dsample != nullptr ? 2 + nb : 2;
+    for (int e = threadIdx.x; e < (last - first) * C; e += blockDim.x) {
+        const int slot = e / C, c = e % C;
+        if (slot == 1 && !TWO) continue;
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += part[((size_t)w * slots + slot) * C + c];
+        float* dst = slot == 0 ? db0 + c : slot == 1 ? db1 + c : dsample + (size_t)(b0 + slot - 2) * C + c;
+        atomicAdd(dst, s);
+    }
+}
+
 template <typename T>
 int launch_gelu_bwd_colsum(const void* dy, const void* z0, const void* z1, void* dz0, void* dz1, float* dsample, float* db0,
                            float* db1, int B, int L, int C, cudaStream_t st) {
@@ -541,6 +675,47 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
     return pb_check_launch("pb_ln_joint_bwd");
 }
 
+int pb_ln_joint_bwd_gelu_ok(int B, int L, int C) {
+    const int vpr = C / 8;
+    return B > 0 && L > 0 && C > 0 && C % 8 == 0 && vpr <= 32 && 32 % vpr == 0 && B <= 4096;
+}
+
+int pb_ln_joint_bwd_gelu(const void* dy, const void* u, const double* stats, const float* gamma, const void* z0, const void* z1,
+                         void* du, void* dz0, void* dz1, float* dgamma, float* dbeta, float* dsample, float* db0, float* db1,
+                         double* sums, int B, int L, int C, float eps, int dt, void* stream) {
+    PB_REQUIRE(pb_ln_joint_bwd_gelu_ok(B, L, C), PB_ERR_SHAPE, "ln_joint_bwd_gelu: unsupported shape B=%d L=%d C=%d (see pb_ln_joint_bwd_gelu_ok)", B, L, C);
+    PB_REQUIRE(z0 != nullptr && dz0 != nullptr && db0 != nullptr, PB_ERR_SHAPE, "ln_joint_bwd_gelu: z0, dz0 and db0 are required");
+    PB_REQUIRE((z1 == nullptr) == (dz1 == nullptr) && (z1 == nullptr) == (db1 == nullptr), PB_ERR_SHAPE,
+               "ln_joint_bwd_gelu: z1, dz1 and db1 go together");
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long n = (long long)L * C;
+    const long long nv = n / 8;
+    int groups = (int)((75776 + nv - 1) / nv);
+    if (groups > B) groups = B;
+    if (groups < 1) groups = 1;
+    int per_group = (B + groups - 1) / groups;
+    const int cap = max(1, (12288 - 16 * C) / (8 * C + 4));      // keeps the partial-sum slots inside 48 KB of shared memory
+    if (per_group > cap) per_group = cap;
+    groups = (B + per_group - 1) / per_group;
+    const size_t smem = (size_t)(4 * per_group + 8 * (per_group + 2) * C) * sizeof(float);
+    dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
+    dim3 g2((unsigned)ceil_div(nv, 256), groups);
+    DISPATCH_DT(dt, {
+        PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, stats, gamma, sums, n, eps));
+        if (z1 != nullptr) {
+            PB_CUDA(pb_launch_pdl(ln_bwd_apply_gelu_kernel<T, true>, g2, dim3(256), smem, st, (const T*)dy, (const T*)u, stats, gamma,
+                                  (const double*)sums, (const T*)z0, (const T*)z1, (T*)du, (T*)dz0, (T*)dz1, dgamma, dbeta, dsample, db0,
+                                  db1, B, C, n, eps, per_group));
+        } else {
+            PB_CUDA(pb_launch_pdl(ln_bwd_apply_gelu_kernel<T, false>, g2, dim3(256), smem, st, (const T*)dy, (const T*)u, stats, gamma,
+                                  (const double*)sums, (const T*)z0, (const T*)z1, (T*)du, (T*)dz0, (T*)dz1, dgamma, dbeta, dsample, db0,
+                                  db1, B, C, n, eps, per_group));
+        }
+    });
+    pb_count_launch(2);
+    return pb_check_launch("pb_ln_joint_bwd_gelu");
+}
+
 int pb_conv_pair_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l,
                      void* zn, void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, int dt,
                      void* stream) {
@@ -573,7 +748,7 @@ int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void*
         PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
     }
     DISPATCH_DT(dt, {
-        launch_gelu_bwd_colsum<T>(du, zn, zw, dzn, dzw, dg2l, dbn, dbw, B, L, C, st);
+        if (zn != nullptr) launch_gelu_bwd_colsum<T>(du, zn, zw, dzn, dzw, dg2l, dbn, dbw, B, L, C, st);
         if (tc) {
             int rc = pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st);
             if (rc) return rc;
@@ -619,7 +794,7 @@ int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const voi
     const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
     if (!tc) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     DISPATCH_DT(dt, {
-        launch_gelu_bwd_colsum<T>(du2, z, nullptr, dz, nullptr, nullptr, db, nullptr, B, L, C, st);
+        if (z != nullptr) launch_gelu_bwd_colsum<T>(du2, z, nullptr, dz, nullptr, nullptr, db, nullptr, B, L, C, st);
         if (tc) {
             int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, ws, ws_bytes, st);
             if (rc) return rc;

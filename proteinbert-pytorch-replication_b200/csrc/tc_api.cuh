@@ -17,6 +17,9 @@ int pb_tc_conv_pair_dgrad(const void* du, const void* dzn, const void* dzw, cons
                           int B, int L, int C, int ksize, int dil, cudaStream_t st);
 int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int C, int ksize,
                      int dil, void* ws, size_t ws_bytes, cudaStream_t st);
+bool pb_tc_conv_wgrad3_ok(int B, int L, int C, int ksize, int dil, size_t ws_bytes);
+int pb_tc_conv_wgrad3(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int ksize, int dil,
+                      void* ws, cudaStream_t st);
 int pb_tc_local_linear_fwd(const void* h, const void* W, const float* bias, void* z, void* u2, double* stats2, int B, int L,
                            int C, cudaStream_t st);
 int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const void* Wt, void* dh, float* dW, int B, int L,

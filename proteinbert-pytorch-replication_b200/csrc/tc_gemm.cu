@@ -357,20 +357,43 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_constant
     }
 }
 
-// out[src][m, n, t] = sum over splits of the partial tiles (plain stores: every output element is written once)
-__global__ void wgrad_reduce_kernel(WgradParams wp, int tiles_m, int tiles_n, int ny, int splits) {
+// out[src][m, n, t] = sum over splits of the partial tiles (plain stores: every output element is written once).
+// block = 16 float4 lanes x 16 split lanes over 64 consecutive partial-tile elements: the loads of one output are
+// spread over 16 threads, so a 148-way split costs ~10 dependent loads instead of 148.
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(WgradParams wp, int tiles_m, int tiles_n, int ny, int splits) {
+    __shared__ float4 part[16][16];
     pdl_wait();
     const long long total = (long long)ny * tiles_m * tiles_n * kBM * kBN;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const long long base = (long long)blockIdx.x * 64;                 // total is a multiple of 64
+    const float4* src = reinterpret_cast<const float4*>(wp.ws + base) + tx;
+    const long long stride4 = total / 4;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+    int k = ty;
+    for (; k + 16 < splits; k += 32) {
+        const float4 v0 = src[(long long)k * stride4], v1 = src[(long long)(k + 16) * stride4];
+        a.x += v0.x; a.y += v0.y; a.z += v0.z; a.w += v0.w;
+        b.x += v1.x; b.y += v1.y; b.z += v1.z; b.w += v1.w;
+    }
+    if (k < splits) {
+        const float4 v0 = src[(long long)k * stride4];
+        a.x += v0.x; a.y += v0.y; a.z += v0.z; a.w += v0.w;
+    }
+    part[ty][tx] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        const float* pf = reinterpret_cast<const float*>(&part[0][0]);
+        float s = 0.f;
+#pragma unroll
+        for (int y = 0; y < 16; ++y) s += pf[y * 64 + threadIdx.x];
+        const long long i = base + threadIdx.x;
         const int n = (int)(i % kBN);
         const int m = (int)((i / kBN) % kBM);
         const int tile = (int)((i / (kBM * kBN)) % (tiles_m * tiles_n));
         const int y = (int)(i / ((long long)kBM * kBN * tiles_m * tiles_n));
-        float s = 0.f;
-        for (int k = 0; k < splits; ++k) s += wp.ws[(size_t)k * total + i];
-        const int src = y / wp.ntaps, t = y % wp.ntaps;
+        const int srcI = y / wp.ntaps, t = y % wp.ntaps;
         const int gm = (tile / tiles_n) * kBM + m, gn = (tile % tiles_n) * kBN + n;
-        wp.out[src][wgrad_out_index(wp, gm, gn, t)] = s;
+        wp.out[srcI][wgrad_out_index(wp, gm, gn, t)] = s;
     }
 }
 
@@ -452,7 +475,7 @@ int launch_wgrad(const void* P0, const void* P1, const void* Q, float* out0, flo
     pb_count_launch(1);
     if (wp.ws != nullptr) {
         const long long total = (long long)tiles * kBM * kBN;
-        PB_CUDA(pb_launch_pdl(wgrad_reduce_kernel, dim3((unsigned)min((long long)ceil_div(total, 256), 148LL * 8)), dim3(256), 0, st, wp, tiles_m, tiles_n, ny, splits));
+        PB_CUDA(pb_launch_pdl(wgrad_reduce_kernel, dim3((unsigned)(total / 64)), dim3(256), 0, st, wp, tiles_m, tiles_n, ny, splits));
         pb_count_launch(1);
     }
     return pb_check_launch(what);
@@ -466,6 +489,8 @@ bool pb_tc_attn_ok(int B, int L, int C, int G) { return pb_tc_enabled() && C % 1
 int pb_tc_conv_wgrad(const void* dzn, const void* dzw, const void* x, float* dWn, float* dWw, int B, int L, int C, int ksize,
                      int dil, void* ws, size_t ws_bytes, cudaStream_t st) {
     // dW[co, ci, t] = sum_{b,l} dz[b,l,co] x[b,l+(t-half)*d,ci]; both convolutions (2 x ksize taps) in one launch
+    if (pb_tc_mode() != 4 && pb_tc_conv_wgrad3_ok(B, L, C, ksize, dil, ws ? ws_bytes : 0))      // three taps per CTA off one halo tile
+        return pb_tc_conv_wgrad3(dzn, dzw, x, dWn, dWw, B, L, ksize, dil, ws, st);
     return launch_wgrad(dzn, dzw, x, dWn, dWw, (long)C * ksize, ksize, 1, B, L, C, C, ksize, 1, dil, ws, ws_bytes, st, "tc_conv_wgrad");
 }
 

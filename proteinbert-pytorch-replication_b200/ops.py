@@ -403,25 +403,40 @@ class LocalTrackFn(torch.autograd.Function):
         dWv = f32(n_heads, C, Dv) if head_grads else None          # one contiguous [C, Dv] gradient per head
         _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
         del dzv
-        # LN2
+        fused = bool(L_.pb_ln_joint_bwd_gelu_ok(B, L, C))
+        # LN2 (+ the linear layer's GELU gradient when the fused kernel takes the shape)
         du2 = torch.empty_like(x)
-        _call("pb_ln_joint_bwd", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(du2), _p(dln2w), _p(dln2b), _p(sums_all[0]), B, L, C,
-                                 LN_EPS, dt, st)
-        # local linear
-        dz2 = dh2t                      # reuse as scratch
-        dh1 = torch.empty_like(x)
         dW2 = f32(C, C)
-        _call("pb_local_linear_bwd", _p(du2), _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2), B, L, C, dt, *_wgrad_ws(dev), st)
-        # LN1
+        if fused:
+            dz2 = torch.empty_like(x)
+            _call("pb_ln_joint_bwd_gelu", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(z2), None, _p(du2), _p(dz2), None,
+                                          _p(dln2w), _p(dln2b), None, _p(db2), None, _p(sums_all[0]), B, L, C, LN_EPS, dt, st)
+            dh1 = dh2t                  # dh2t is dead once LN2's backward has read it
+        else:
+            _call("pb_ln_joint_bwd", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(du2), _p(dln2w), _p(dln2b), _p(sums_all[0]), B, L, C,
+                                     LN_EPS, dt, st)
+            dz2 = dh2t                  # reuse as scratch
+            dh1 = torch.empty_like(x)
+        # local linear
+        _call("pb_local_linear_bwd", _p(du2), None if fused else _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2),
+                                     B, L, C, dt, *_wgrad_ws(dev), st)
+        # LN1 (+ both convolutions' GELU gradients and the per-sample sums behind dg2l)
         du1 = du2                       # du2 is dead after the linear backward
-        _call("pb_ln_joint_bwd", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(du1), _p(dln1w), _p(dln1b), _p(sums_all[1]), B, L, C,
-                                 LN_EPS, dt, st)
+        dzn = dz2                       # so is dz2
+        if fused:
+            dzw = torch.empty_like(x)
+            _call("pb_ln_joint_bwd_gelu", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(zn), _p(zw), _p(du1), _p(dzn), _p(dzw),
+                                          _p(dln1w), _p(dln1b), _p(dg2l), _p(dbn), _p(dbw), _p(sums_all[1]), B, L, C, LN_EPS, dt, st)
+        else:
+            _call("pb_ln_joint_bwd", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(du1), _p(dln1w), _p(dln1b), _p(sums_all[1]), B, L, C,
+                                     LN_EPS, dt, st)
+            dzw = dh1                   # dead by now
         # conv pair
-        dzn, dzw = dz2, dh1             # both dead by now
         dx = torch.empty_like(x)
         dWn, dWw = f32(C, C, ksize), f32(C, C, ksize)
-        _call("pb_conv_pair_bwd", _p(du1), _p(zn), _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), _p(dx), _p(dWn),
-                                  _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, *_wgrad_ws(dev), st)
+        _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
+                                  _p(dzw), _p(dx), _p(dWn), _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt,
+                                  *_wgrad_ws(dev), st)
         if head_grads:
             dheads = tuple(dWv[h] for h in range(n_heads))
         else:

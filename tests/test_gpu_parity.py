@@ -242,6 +242,49 @@ def test_conv_pair_against_torch_conv1d(pb):
         assert_close_rel(stats[:, 1], (ru * ru).sum((1, 2)), 1e-5)
 
 
+@pytest.mark.parametrize("dtype,two,shape", [("fp32", True, (5, 96, 32)), ("fp32", False, (3, 40, 64)),
+                                            ("bf16", True, (19, 256, 128)), ("bf16", False, (6, 128, 256))])
+def test_fused_layernorm_gelu_backward(pb, dtype, two, shape):
+    """pb_ln_joint_bwd_gelu against torch autograd (double) of u -> LayerNorm((L,C)) with z -> gelu side branches
+    (modules.py:207-217 in reverse): du, dz, dgamma/dbeta, channel sums and the per-sample sums."""
+    from proteinbert_b200 import ops
+    B, L, C = shape
+    assert pb._lib.lib().pb_ln_joint_bwd_gelu_ok(B, L, C)
+    g = torch.Generator().manual_seed(B * 1000 + L)
+    act = torch.float32 if dtype == "fp32" else torch.bfloat16
+    dt = 0 if dtype == "fp32" else 1
+    u, dy, z0, z1 = (torch.randn(B, L, C, generator=g).cuda().to(act) for _ in range(4))
+    gamma = (1 + 0.2 * torch.randn(L, C, generator=g)).cuda()
+    stats = torch.stack([u.double().sum((1, 2)), (u.double() ** 2).sum((1, 2))], 1).contiguous()
+    du, dz0, dz1 = torch.empty_like(u), torch.empty_like(u), torch.empty_like(u)
+    dgamma, dbeta = torch.zeros(L, C, device="cuda"), torch.zeros(L, C, device="cuda")
+    dsample, db0, db1 = torch.zeros(B, C, device="cuda"), torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+    sums = torch.zeros(B, 2, dtype=torch.float64, device="cuda")
+    ops._call("pb_ln_joint_bwd_gelu", dy.data_ptr(), u.data_ptr(), stats.data_ptr(), gamma.data_ptr(), z0.data_ptr(),
+              z1.data_ptr() if two else None, du.data_ptr(), dz0.data_ptr(), dz1.data_ptr() if two else None, dgamma.data_ptr(),
+              dbeta.data_ptr(), dsample.data_ptr(), db0.data_ptr(), db1.data_ptr() if two else None, sums.data_ptr(), B, L, C,
+              1e-5, dt, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ud = u.double().requires_grad_(True)
+    gd = gamma.double().requires_grad_(True)
+    bd = torch.zeros(L, C, dtype=torch.float64, device="cuda", requires_grad=True)
+    y = torch.nn.functional.layer_norm(ud, (L, C), gd, bd, 1e-5)
+    y.backward(dy.double())
+    du_ref = ud.grad
+    tol = 1e-5 if dtype == "fp32" else 4e-3
+    assert_close_rel(du, du_ref, tol, what="du")
+    assert_close_rel(dgamma, gd.grad, tol, what="dgamma")
+    assert_close_rel(dbeta, bd.grad, tol, what="dbeta")
+    # the GELU branches act on the STORED du (rounded to the activation type), as the unfused kernels do
+    dus = du.double()
+    for z, dz, db in ((z0, dz0, db0), (z1, dz1, db1)) if two else ((z0, dz0, db0),):
+        zd = z.double().requires_grad_(True)
+        torch.nn.functional.gelu(zd).backward(dus)
+        assert_close_rel(dz, zd.grad, tol, what="dz")
+        assert_close_rel(db, dz.double().sum((0, 1)), 1e-5 if dtype == "fp32" else 1e-4, floor=1e-4, what="db")
+    assert_close_rel(dsample, dus.sum(1), 1e-5 if dtype == "fp32" else 1e-4, floor=1e-4, what="dsample")
+
+
 def test_token_head_batch_axis_softmax(pb):
     g = torch.Generator().manual_seed(2)
     B, L, C, V = 5, 33, 48, 26
