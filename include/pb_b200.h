@@ -113,6 +113,19 @@ int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float*
                   float* dW, float* db, int M, int N, int K, int act, int accumulate_dx, void* ws,
                   size_t ws_bytes, void* stream);
 
+/* The same two operations on the tcgen05 tensor cores, for the layers whose weight matrix dwarfs the batch (the
+ * annotation layers, modules.py:248-251 and 290-297: M = batch rows <= 128).  Same arguments and results; operands are
+ * read as fp32, rounded to bf16 on the way into shared memory and accumulated in fp32 (the arithmetic of
+ * precision = "bf16"; the fp32 entry points above keep full fp32).  ws is required: pb_linear_tc_workspace(M, N, K)
+ * bytes cover both directions.  pb_linear_tc_ok says whether the shape is taken.                                       */
+int pb_linear_tc_ok(int M, int N, int K);
+size_t pb_linear_tc_workspace(int M, int N, int K);
+int pb_linear_fwd_tc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
+                     int act, void* ws, size_t ws_bytes, void* stream);
+int pb_linear_bwd_tc(const float* dY, const float* ZY, const float* X, const float* W, float* dZ_buf, float* dX,
+                     float* dW, float* db, int M, int N, int K, int act, int accumulate_dx, void* ws,
+                     size_t ws_bytes, void* stream);
+
 /* y = LayerNorm_G(a + b + coef*c), coef = sum(w_param)/Kdim  (modules.py:183-186,196-199,223-229 and the
  * head mix of :87-92 under the reference's softmax axis).  b, c may be NULL.  Saves xhat and rstd. */
 int pb_res_ln_rows_fwd(const float* a, const float* b, const float* c, const float* w_param, int Kdim,

@@ -32,6 +32,10 @@ PROTOTYPES = {
     "pb_linear_fwd": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_linear_fwd_noalloc": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p],
+    "pb_linear_tc_ok": [_i, _i, _i],
+    "pb_linear_tc_workspace": [_i, _i, _i],
+    "pb_linear_fwd_tc": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
+    "pb_linear_bwd_tc": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_res_ln_rows_fwd": [_p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_res_ln_rows_bwd": [_p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_global_fused_ok": [_i, _i, _i],
@@ -60,7 +64,7 @@ PROTOTYPES = {
     "pb_corrupt_pad": [_p] * 16 + [_i, _i, _i, _p],
     "pb_workspace_bytes": [C.c_char_p, _i, _i, _i],
 }
-_RESTYPES = {"pb_last_error": C.c_char_p, "pb_launch_count": _ll, "pb_workspace_bytes": _sz}
+_RESTYPES = {"pb_last_error": C.c_char_p, "pb_launch_count": _ll, "pb_workspace_bytes": _sz, "pb_linear_tc_workspace": _sz}
 
 _lib = None
 

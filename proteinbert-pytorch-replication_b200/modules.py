@@ -213,7 +213,8 @@ class ProteinBERT(nn.Module):
         x_local, x_global = x["local"], x["global"]
         h = ops.EmbeddingFn.apply(x_local, self.local_embedding.weight, dt)                     # modules.py:300
         gin = self.global_linear_layer[0]
-        g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU)                    # :301
+        tc = dt == ops.BF16           # annotation layers: tensor cores in bf16 precision, fp32 SIMT otherwise
+        g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU, tc)                # :301
         blocks = list(self.proteinBERT_blocks)
         ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
         cut = getattr(self, "_boundary_at", None)        # training.GraphedPretrainStep: where backward is split in two
@@ -224,5 +225,5 @@ class ProteinBERT(nn.Module):
             h, g = blk.forward_channels_last(h, g)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
         p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284
-        p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID)                           # :286-293
+        p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID, tc)                       # :286-293
         return p_local, p_global

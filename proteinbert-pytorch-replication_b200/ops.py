@@ -187,10 +187,11 @@ class EmbeddingFn(torch.autograd.Function):
 
 
 class LinearActFn(torch.autograd.Function):
-    """act(X W^T + b) on the global track, float32 (modules.py:166-199,255-262,286-293)."""
+    """act(X W^T + b) on the global track, float32 tensors (modules.py:166-199,255-262,286-293).  tc=True takes the
+    tcgen05 path (bf16 operands, fp32 accumulation) when the shape allows: the annotation layers in bf16 precision."""
 
     @staticmethod
-    def forward(ctx, x, W, b, act):
+    def forward(ctx, x, W, b, act, tc=False):
         _need_cuda(x, W, b)
         x = x.contiguous().float()
         W = W.contiguous()
@@ -198,10 +199,16 @@ class LinearActFn(torch.autograd.Function):
         N = W.shape[0]
         y = torch.empty((M, N), dtype=torch.float32, device=x.device)
         z = torch.empty_like(y) if act == ACT_GELU else None
-        nbytes = lib().pb_workspace_bytes(b"linear_fwd", M, N, K)
-        ws = _workspace(nbytes, x.device)
-        _call("pb_linear_fwd", _p(x), _p(W), _p(b), _p(z), _p(y), M, N, K, act, _p(ws), ws.numel(), _st())
+        tc = bool(tc) and bool(lib().pb_linear_tc_ok(M, N, K))
+        if tc:
+            ws = _workspace(lib().pb_linear_tc_workspace(M, N, K), x.device)
+            _call("pb_linear_fwd_tc", _p(x), _p(W), _p(b), _p(z), _p(y), M, N, K, act, _p(ws), ws.numel(), _st())
+        else:
+            nbytes = lib().pb_workspace_bytes(b"linear_fwd", M, N, K)
+            ws = _workspace(nbytes, x.device)
+            _call("pb_linear_fwd", _p(x), _p(W), _p(b), _p(z), _p(y), M, N, K, act, _p(ws), ws.numel(), _st())
         ctx.act = act
+        ctx.tc = tc
         ctx.needs = (ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         ctx.save_for_backward(x, W, z if act == ACT_GELU else (y if act == ACT_SIGMOID else None))
         return y
@@ -217,11 +224,16 @@ class LinearActFn(torch.autograd.Function):
         dx = torch.empty((M, K), dtype=torch.float32, device=dy.device) if need_dx else None
         dW = torch.empty((N, K), dtype=torch.float32, device=dy.device) if need_dw else None
         db = torch.empty((N,), dtype=torch.float32, device=dy.device)
-        nbytes = lib().pb_workspace_bytes(b"linear_bwd", M, N, K)
-        ws = _workspace(nbytes, dy.device)
-        _call("pb_linear_bwd", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
-                                  _p(ws), ws.numel(), _st())
-        return dx, dW, db, None
+        if ctx.tc:
+            ws = _workspace(lib().pb_linear_tc_workspace(M, N, K), dy.device)
+            _call("pb_linear_bwd_tc", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
+                                         _p(ws), ws.numel(), _st())
+        else:
+            nbytes = lib().pb_workspace_bytes(b"linear_bwd", M, N, K)
+            ws = _workspace(nbytes, dy.device)
+            _call("pb_linear_bwd", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
+                                      _p(ws), ws.numel(), _st())
+        return dx, dW, db, None, None
 
 
 class ResLnRowsFn(torch.autograd.Function):
@@ -559,8 +571,8 @@ class PretrainLossFn(torch.autograd.Function):
         return dPl * s, dPg * s, None, None, None, None
 
 
-def linear_act(x, W, b, act):
-    return LinearActFn.apply(x, W, b, act)
+def linear_act(x, W, b, act, tc=False):
+    return LinearActFn.apply(x, W, b, act, tc)
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",

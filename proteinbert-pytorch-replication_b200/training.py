@@ -19,11 +19,23 @@ def pretraining_loss(p_local, p_global, Y: Dict[str, torch.Tensor], W: Dict[str,
     return ops.PretrainLossFn.apply(p_local, p_global, Y["local"], Y["global"], W["local"], W["global"])
 
 
+def _clear_grads(model):
+    """``optimizer.zero_grad(set_to_none=True)`` of utils.py:295, extended to the attention-head tensors: the reference
+    keeps them in plain Python lists (modules.py:78-81), so no optimizer ever zeroes or reads their ``.grad`` and it
+    would grow by one step's gradient per step; here ``.grad`` always holds the last step's gradient (and the step
+    saves four accumulate launches per block)."""
+    for p in model.parameters():
+        p.grad = None
+    heads = getattr(model, "head_tensors", None)
+    if heads is not None:
+        for t in heads().values():
+            t.grad = None
+
+
 def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None) -> torch.Tensor:
     """forward + loss + backward (utils.py:291-299 without the optimizer).  Gradients are left in ``.grad``
     (averaged over ranks when a reducer is given).  Returns the detached loss."""
-    for p in model.parameters():
-        p.grad = None
+    _clear_grads(model)
     p_local, p_global = model(X)
     loss = pretraining_loss(p_local, p_global, Y, W)
     if reducer is not None:
@@ -122,8 +134,7 @@ class GraphedPretrainStep:
                        for h in blk.global_attention_layer.global_attention_heads if blk.head_grads]
 
         def stage_a():
-            for p in model.parameters():
-                p.grad = None
+            _clear_grads(model)
             model._boundary_at = cut
             try:
                 p_local, p_global = model(sx)
@@ -154,8 +165,7 @@ class GraphedPretrainStep:
                 full_step()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
-        for p in model.parameters():
-            p.grad = None
+        _clear_grads(model)
         self.graph = torch.cuda.CUDAGraph()
         if self.split:
             with torch.cuda.graph(self.graph):

@@ -208,3 +208,51 @@ def test_token_head_tensor_core_path(pb):
     assert rel_fro(hd.grad, hr.grad) < 1e-2
     assert rel_fro(Wd.grad, Wr.grad) < 1e-2
     assert float(bd.grad.abs().max()) < 1e-3 * float(Wd.grad.abs().max())     # mathematically zero
+
+
+@pytest.mark.parametrize("M,N,K,act", [(64, 512, 8943, 1), (64, 8943, 512, 2), (5, 301, 64, 0), (100, 130, 70, 1), (128, 64, 200, 0)])
+def test_annotation_layers_on_tensor_cores(pb, M, N, K, act):
+    """pb_linear_fwd_tc / pb_linear_bwd_tc (tc_skinny.cu) against torch on the bf16-rounded operands (what the kernel
+    multiplies) and against the fp32 entry points: odd leading dimensions, ragged tiles, every operand arrangement."""
+    from proteinbert_b200 import ops
+    lib = pb._lib.lib()
+    assert lib.pb_linear_tc_ok(M, N, K)
+    x = rnd(M, K, seed=1).cuda()
+    if K > 1000:
+        x = (x > 0.5).float()                      # annotations are 0/1
+    W, b = rnd(N, K, scale=K ** -0.5, seed=2).cuda(), rnd(N, scale=0.1, seed=3).cuda()
+    dy = rnd(M, N, scale=0.1, seed=4).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    ws = torch.empty(lib.pb_linear_tc_workspace(M, N, K), dtype=torch.uint8, device="cuda")
+    z, y = torch.empty(M, N, device="cuda"), torch.empty(M, N, device="cuda")
+    ops._call("pb_linear_fwd_tc", x.data_ptr(), W.data_ptr(), b.data_ptr(), z.data_ptr(), y.data_ptr(), M, N, K, act, ws.data_ptr(),
+              ws.numel(), st)
+    xr, Wr = x.bfloat16().double(), W.bfloat16().double()
+    z_ref = xr @ Wr.t() + b.double()
+    y_ref = {0: z_ref, 1: torch.nn.functional.gelu(z_ref), 2: torch.sigmoid(z_ref)}[act]
+    assert rel_fro(z, z_ref) < 5e-5
+    assert rel_fro(y, y_ref) < 5e-5
+    assert rel_fro(z, x.double() @ W.double().t() + b.double()) < 1e-2          # vs the unrounded product
+    zy = z if act == 1 else y
+    dz, dx, dW, db = torch.empty(M, N, device="cuda"), torch.empty(M, K, device="cuda"), torch.empty(N, K, device="cuda"), torch.empty(N, device="cuda")
+    ops._call("pb_linear_bwd_tc", dy.data_ptr(), zy.data_ptr() if act else None, x.data_ptr(), W.data_ptr(), dz.data_ptr(), dx.data_ptr(),
+              dW.data_ptr(), db.data_ptr(), M, N, K, act, 0, ws.data_ptr(), ws.numel(), st)
+    torch.cuda.synchronize()
+    zd = z.double()
+    dact = {0: torch.ones_like(zd), 1: None, 2: y.double() * (1 - y.double())}[act]
+    if act == 1:
+        zz = zd.clone().requires_grad_(True)
+        torch.nn.functional.gelu(zz).backward(torch.ones_like(zz))
+        dact = zz.grad
+    dz_ref = dy.double() * dact
+    assert rel_fro(dz, dz_ref) < 1e-5
+    assert rel_fro(db, dz_ref.sum(0)) < 1e-5
+    dzr = dz.bfloat16().double()
+    assert rel_fro(dx, dzr @ Wr) < 5e-5
+    assert rel_fro(dW, dzr.t() @ xr) < 5e-5
+    assert rel_fro(dW, dz_ref.t() @ x.double()) < 1e-2
+    # accumulate_dx adds into dX
+    dx2 = dx.clone()
+    ops._call("pb_linear_bwd_tc", dy.data_ptr(), zy.data_ptr() if act else None, x.data_ptr(), W.data_ptr(), dz.data_ptr(), dx2.data_ptr(),
+              None, db.data_ptr(), M, N, K, act, 1, ws.data_ptr(), ws.numel(), st)
+    assert rel_fro(dx2, 2 * dx.double()) < 1e-5
