@@ -54,10 +54,19 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
     return v[0];
 }
 
+// The two pooling GEMMs (K = C = 128: two 64-wide chunks) are bound by their GELU epilogues, i.e. by how many
+// epilogue warps an SM holds: they take a two-stage ring so that three CTAs fit per SM.
+template <int EPI> struct GemmCfg {
+    static constexpr int kStagesE = (EPI == EPI_POOL_FWD || EPI == EPI_POOL_DZ) ? 2 : 3;
+    static constexpr int kCtas = (EPI == EPI_POOL_FWD || EPI == EPI_POOL_DZ) ? 3 : 2;
+    static constexpr int kSmem = kStagesE * kStageBytes + 1024 + 256 + 4 * kBN * 4;
+};
+
 template <int EPI>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, GemmCfg<EPI>::kCtas)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                const __grid_constant__ CUtensorMap mapS0, const __grid_constant__ CUtensorMap mapS1, GemmEpi ep, int K) {
+    constexpr int kStages = GemmCfg<EPI>::kStagesE;          // shadows the file-level ring depth
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
@@ -123,7 +132,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // bf16 outputs leave through TMA: each warp stages its 32 x 32 sub-tile (64-byte swizzle) in the last ring
         // stage, idle by now, and one lane issues the tensor store; two buffers so a store drains behind the math
         constexpr bool kTmaOut = EPI == EPI_LINEAR_FWD || EPI == EPI_POOL_DZ || EPI == EPI_STORE || EPI == EPI_ADD_STORE;
-        uint8_t* stage = smem + 2 * kStageBytes + (warp - 2) * 8192;
+        uint8_t* stage = smem + (kStages - 1) * kStageBytes + (warp - 2) * 8192;
         const int sw = (lane >> 1) & 3;
         const int trow = q * 32 + lane;                              // row inside the tile
         float s_sum = 0.f, s_sq = 0.f;
@@ -427,10 +436,10 @@ int launch_gemm(const void* A, const void* Bm, const GemmEpi& ep, int M, int N, 
     }
     static bool attr_set = false;
     if (!attr_set) {
-        PB_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        PB_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<EPI>::kSmem));
         attr_set = true;
     }
-    PB_CUDA(pb_launch_pdl(tc_gemm_kernel<EPI>, dim3(M / kBM, N / kBN), dim3(kThreads), kSmemBytes, st, mA, mB, mS0, mS1, ep, K));
+    PB_CUDA(pb_launch_pdl(tc_gemm_kernel<EPI>, dim3(M / kBM, N / kBN), dim3(kThreads), GemmCfg<EPI>::kSmem, st, mA, mB, mS0, mS1, ep, K));
     pb_count_launch(1);
     return pb_check_launch(what);
 }
