@@ -145,19 +145,22 @@ int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, c
 int pb_global_fused_ok(int B, int G, int C);
 int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const float* W3, const float* b3, float* zg,
                       float* g2l, float* z3, float* gh, int B, int G, int C, void* stream);
+/* dgh_is_dz3 = 1: the dgh argument already holds dgh * gelu'(z3) (the dz3 output of pb_global_post_bwd), which saves
+ * every CTA the B x G GELU derivatives. */
 int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, const float* z3, const float* g,
                       const float* W1, const float* W3, float* dg, float* dW1, float* db1, float* dW3, float* db3,
-                      int B, int G, int C, void* stream);
+                      int B, int G, int C, int dgh_is_dz3, void* stream);
 int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const float* Wp, int Kdim,
                        const float* gamma1, const float* beta1, const float* W4, const float* b4, const float* gamma2,
                        const float* beta2, float* g1, float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2,
                        float* g2, int B, int G, void* stream);
-/* scratch3 [3,B,G] is scratch; dx1 = d loss/d g (residual path) = d loss/d gh. */
+/* scratch3 [3,B,G] is scratch; dx1 = d loss/d g (residual path) = d loss/d gh.  z3 / dz3 (both or neither): when given,
+ * dz3 = dx1 * gelu'(z3) is written as well, for pb_global_pre_bwd(dgh = dz3, dgh_is_dz3 = 1). */
 int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2, const float* rstd2, const float* z4,
                        const float* g1, const float* W4, const float* gamma1, const float* xhat1, const float* rstd1,
                        const float* pool, const float* Wp, int Kdim, float* scratch3, float* dx1, float* dpool,
                        float* dWp, float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2,
-                       float* dbeta2, int B, int G, void* stream);
+                       float* dbeta2, const float* z3, float* dz3, int B, int G, void* stream);
 
 /* ---- a5/a6/a7: narrow + dilated Conv1d, GELU, 4-way add with the global broadcast ---------------
  * zn = conv(x, Wn, d=1)+bn, zw = conv(x, Ww, d=dil)+bw, u = x + gelu(zn) + gelu(zw) + g2l[b,:]

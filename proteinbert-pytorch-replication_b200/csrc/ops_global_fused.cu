@@ -20,12 +20,22 @@
 
 namespace cg = cooperative_groups;
 
+void* pb_debug_ptr();          // tc_host.cu: optional device buffer for phase timestamps (scripts/global_phase_probe.py)
+
 namespace {
 
 constexpr int kNT = 8;            // output columns per CTA
 constexpr int kThreads = 512;
 constexpr float kEps = 1e-5f;
 constexpr int kQ = 2;             // row phases / dW row sweep: up to kQ * 512 = 1024 columns
+
+__device__ __forceinline__ void stamp(unsigned long long* dbg, int slot) {
+    if (dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        dbg[slot] = t;
+    }
+}
 
 __host__ __device__ __forceinline__ int row_tile_of(int K) { return K <= 704 ? 64 : (K <= 1472 ? 32 : 16); }
 
@@ -122,25 +132,27 @@ __device__ __forceinline__ void fill_tile(float* A_s, int lda, int MT, int mt, i
 }
 
 // dW rows of this CTA's slice: acc[q][j] += sum_m D_s[m*8 + j] * X[(row0+m)*ldx + kcol], kcol = tid + q*512.
-// Rows are taken eight at a time with all global loads issued before the FMAs.
-__device__ __forceinline__ void dw_accumulate(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
-                                              int row0, int mt, int Kout) {
-    for (int m0 = 0; m0 < mt; m0 += 8) {
-        float x[8][kQ];
+// Rows are taken R at a time with all global loads issued before the FMAs: the sweep is a chain of mt / R round trips
+// to L2, so R is as large as the registers allow without spilling (16 rows when one column per thread covers Kout, else 8).
+template <int Q, int R>
+__device__ __forceinline__ void dw_accumulate_q(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
+                                                int row0, int mt, int Kout) {
+    for (int m0 = 0; m0 < mt; m0 += R) {
+        float x[R][Q];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < R; ++i)
 #pragma unroll
-            for (int q = 0; q < kQ; ++q) {
+            for (int q = 0; q < Q; ++q) {
                 const int kc = threadIdx.x + q * kThreads;
                 x[i][q] = (m0 + i < mt && kc < Kout) ? __ldg(X + (size_t)(row0 + m0 + i) * ldx + kc) : 0.f;
             }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < R; ++i) {
             if (m0 + i < mt) {
                 const float4 d0 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT);
                 const float4 d1 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT + 4);
 #pragma unroll
-                for (int q = 0; q < kQ; ++q) {
+                for (int q = 0; q < Q; ++q) {
                     const float xv = x[i][q];
                     acc[q][0] = fmaf(d0.x, xv, acc[q][0]); acc[q][1] = fmaf(d0.y, xv, acc[q][1]);
                     acc[q][2] = fmaf(d0.z, xv, acc[q][2]); acc[q][3] = fmaf(d0.w, xv, acc[q][3]);
@@ -150,6 +162,11 @@ __device__ __forceinline__ void dw_accumulate(float (&acc)[kQ][kNT], const float
             }
         }
     }
+}
+__device__ __forceinline__ void dw_accumulate(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
+                                              int row0, int mt, int Kout) {
+    if (Kout <= kThreads) dw_accumulate_q<1, 16>(acc, D_s, X, ldx, row0, mt, Kout);
+    else dw_accumulate_q<kQ, 8>(acc, D_s, X, ldx, row0, mt, Kout);
 }
 __device__ __forceinline__ void dw_store(const float (&acc)[kQ][kNT], float* __restrict__ dW, int ldw, int n0, int Kout) {
 #pragma unroll
@@ -229,8 +246,11 @@ struct PreBwd {
     const float *dg2l, *dgh, *zg, *z3, *g, *W1, *W3;
     float *dg, *dW1, *db1, *dW3, *db3;
     int B, G, C;
+    int dgh_is_dz3;                // dgh already holds dgh * gelu'(z3) (written by the post backward kernel)
+    unsigned long long* dbg;
 };
 
+template <bool kDz3Ready>
 __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     extern __shared__ __align__(16) float sm[];
     const int G = p.G, C = p.C, KA = G + C, MT = row_tile_of(KA), lda = KA + 1;
@@ -242,10 +262,12 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     pdl_wait();
     const int n0 = blockIdx.x * kNT;                   // 0 .. G + C
     const bool has_dg = n0 < G;
+    stamp(p.dbg, 16);
     if (has_dg) {                                      // Bt = [W3[:, n0..] ; W1[:, n0..]]  (rows = contraction index)
         load_bt_cols(Bt_s, p.W3, G, n0, G);
         load_bt_cols(Bt_s + (size_t)G * kNT, p.W1, G, n0, C);
     }
+    stamp(p.dbg, 22);
     const bool w_is_3 = n0 < G;
     const int wrow0 = w_is_3 ? n0 : n0 - G;
     float accw[kQ][kNT];
@@ -257,17 +279,26 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<2, false>(A_s, lda, MT, mt, G, p.dgh, p.z3, G, row0, MulGeluGrad4());
+        if (kDz3Ready) fill_tile<1, false>(A_s, lda, MT, mt, G, p.dgh, nullptr, G, row0, Copy4());
+        else fill_tile<2, false>(A_s, lda, MT, mt, G, p.dgh, p.z3, G, row0, MulGeluGrad4());
+        stamp(p.dbg, 23);
         fill_tile<2, false>(A_s + G, lda, MT, mt, C, p.dg2l, p.zg, C, row0, MulGeluGrad4());
         __syncthreads();
+        stamp(p.dbg, 17);
         for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
             const int m = i / kNT, j = i - m * kNT;
             D_s[i] = A_s[(size_t)m * lda + n0 + j];    // n0 + j < KA always ((G + C) % 8 == 0)
         }
         __syncthreads();
-        if (threadIdx.x < kNT)
-            for (int m = 0; m < mt; ++m) colsum += D_s[m * kNT + threadIdx.x];
+        if (threadIdx.x < 32) {
+            float a = 0.f;
+            for (int m = threadIdx.x >> 3; m < mt; m += 4) a += D_s[m * kNT + (threadIdx.x & 7)];
+            a += __shfl_xor_sync(0xffffffffu, a, 8); a += __shfl_xor_sync(0xffffffffu, a, 16);
+            colsum += a;                               // read by threads < 8 only
+        }
+        stamp(p.dbg, 18);
         dw_accumulate(accw, D_s, p.g, G, row0, mt, G);
+        stamp(p.dbg, 19);
         if (has_dg) {
             float out[kNT];
             cta_gemm8(A_s, lda, Bt_s, KA, MT, red_s, out);
@@ -278,8 +309,10 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
             }
         }
     }
+    stamp(p.dbg, 20);
     dw_store(accw, w_is_3 ? p.dW3 : p.dW1, G, wrow0, G);
     if (threadIdx.x < kNT) (w_is_3 ? p.db3 : p.db1)[wrow0 + threadIdx.x] = colsum;
+    stamp(p.dbg, 21);
 }
 
 // ============================================================================================================
@@ -377,8 +410,11 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
 // ============================================================================================================
 struct PostBwd {
     const float *dg2, *gamma2, *xhat2, *rstd2, *z4, *g1, *W4, *gamma1, *xhat1, *rstd1, *pool, *Wp;
+    const float* z3;               // optional: pre-activation of gh, to emit dz3 = dx1 * gelu'(z3) for the pre backward kernel
+    float* dz3;
     float *dg1, *dx2, *dz4, *dx1, *dpool, *dWp, *dgamma1, *dbeta1, *dW4, *db4, *dgamma2, *dbeta2;
     int B, G, Kdim;
+    unsigned long long* dbg;
 };
 
 __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p) {
@@ -391,6 +427,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
     float* red_s = Bt_s + (size_t)G * kNT;             // [512*8]
     float* D_s = red_s + kThreads * kNT;               // [MT][8] dz4 slice
     const int n0 = blockIdx.x * kNT;
+    stamp(p.dbg, 32);
     load_bt_cols(Bt_s, p.W4, G, n0, G);
     if (blockIdx.x == 0) for (int k = threadIdx.x; k < p.Kdim; k += kThreads) p.dWp[k] = 0.f;
     // ---- row phase: LayerNorm-2 backward
@@ -418,7 +455,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             }
         }
     }
+    stamp(p.dbg, 33);
     grid.sync();
+    stamp(p.dbg, 34);
     // ---- column phase
     float accw[kQ][kNT];
 #pragma unroll
@@ -431,23 +470,34 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
         __syncthreads();
         fill_tile<1, true>(A_s, lda, MT, mt, G, p.dz4, nullptr, G, row0, Copy4());
         __syncthreads();
+        stamp(p.dbg, 35);
         for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
             const int m = i / kNT, j = i - m * kNT;
             D_s[i] = A_s[(size_t)m * lda + n0 + j];
         }
         __syncthreads();
-        if (threadIdx.x < kNT) {
-            const int c = n0 + threadIdx.x;
-            for (int m = 0; m < mt; ++m) {
+        if (threadIdx.x < 32) {          // one warp: 8 columns x 4 row lanes, folded with two shuffles
+            const int j = threadIdx.x & 7, c = n0 + j;
+            float a = 0.f, b = 0.f, e = 0.f;
+#pragma unroll 4
+            for (int m = threadIdx.x >> 3; m < mt; m += 4) {
                 const size_t o = (size_t)(row0 + m) * G + c;
-                c_db4 += D_s[m * kNT + threadIdx.x];
-                c_dg2 += p.dg2[o] * p.xhat2[o];
-                c_db2 += p.dg2[o];
+                const float dv = p.dg2[o];
+                a += D_s[m * kNT + j];
+                b += dv * p.xhat2[o];
+                e += dv;
             }
+            a += __shfl_xor_sync(0xffffffffu, a, 8); a += __shfl_xor_sync(0xffffffffu, a, 16);
+            b += __shfl_xor_sync(0xffffffffu, b, 8); b += __shfl_xor_sync(0xffffffffu, b, 16);
+            e += __shfl_xor_sync(0xffffffffu, e, 8); e += __shfl_xor_sync(0xffffffffu, e, 16);
+            c_db4 += a; c_dg2 += b; c_db2 += e;       // read by threads < 8 only
         }
+        stamp(p.dbg, 36);
         dw_accumulate(accw, D_s, p.g1, G, row0, mt, G);                 // dW4[n0.., :] += dz4[:, n0..]^T g1
+        stamp(p.dbg, 37);
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);                   // dz4 W4[:, n0..]
+        stamp(p.dbg, 38);
         if (threadIdx.x < mt) {
             const size_t o = (size_t)(row0 + threadIdx.x) * G + n0;
             const float4 x0 = ld4cg(p.dx2 + o), x1 = ld4cg(p.dx2 + o + 4);
@@ -461,7 +511,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
         p.dgamma2[n0 + threadIdx.x] = c_dg2;
         p.dbeta2[n0 + threadIdx.x] = c_db2;
     }
+    stamp(p.dbg, 39);
     grid.sync();
+    stamp(p.dbg, 40);
     // ---- row phase: LayerNorm-1 backward
     const float coef = coef_of(p.Wp, p.Kdim, red);
     float dcoef = 0.f;
@@ -485,6 +537,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             if (k < G) {
                 const float dx = rs * (d[i] - m1 - xh[i] * m2);
                 p.dx1[off + k] = dx;
+                if (p.dz3 != nullptr) p.dz3[off + k] = dx * gelu_grad_f(p.z3[off + k]);
                 p.dpool[off + k] = coef * dx;
                 dcoef += dx * p.pool[off + k];
             }
@@ -493,19 +546,26 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
     const float tot = block_sum(dcoef, red) / (float)p.Kdim;
     if (tot != 0.f)
         for (int k = threadIdx.x; k < p.Kdim; k += kThreads) atomicAdd(&p.dWp[k], tot);
+    stamp(p.dbg, 41);
     // ---- own columns: dgamma1 / dbeta1 (needs every row of dg1, complete since the barrier)
-    if (threadIdx.x < kNT) {
-        const int c = n0 + threadIdx.x;
+    if (threadIdx.x < 32) {
+        const int c = n0 + (threadIdx.x & 7);
         float sg = 0.f, sb = 0.f;
-        for (int m = 0; m < p.B; ++m) {
+#pragma unroll 4
+        for (int m = threadIdx.x >> 3; m < p.B; m += 4) {
             const size_t o = (size_t)m * G + c;
             const float dv = __ldcg(p.dg1 + o);
             sg += dv * p.xhat1[o];
             sb += dv;
         }
-        p.dgamma1[c] = sg;
-        p.dbeta1[c] = sb;
+        sg += __shfl_xor_sync(0xffffffffu, sg, 8); sg += __shfl_xor_sync(0xffffffffu, sg, 16);
+        sb += __shfl_xor_sync(0xffffffffu, sb, 8); sb += __shfl_xor_sync(0xffffffffu, sb, 16);
+        if (threadIdx.x < kNT) {
+            p.dgamma1[c] = sg;
+            p.dbeta1[c] = sb;
+        }
     }
+    stamp(p.dbg, 42);
 }
 
 size_t smem_bytes(int MT, int KA, bool with_slice) {
@@ -546,13 +606,14 @@ int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const fl
 
 int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, const float* z3, const float* g, const float* W1,
                       const float* W3, float* dg, float* dW1, float* db1, float* dW3, float* db3, int B, int G, int C,
-                      void* stream) {
+                      int dgh_is_dz3, void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, C), PB_ERR_UNSUPPORTED, "global_pre_bwd: shape B=%d G=%d C=%d not covered", B, G, C);
     const size_t smem = smem_bytes(row_tile_of(G + C), G + C, true);
-    int rc = set_smem(global_pre_bwd_kernel, smem);
+    int rc = dgh_is_dz3 ? set_smem(global_pre_bwd_kernel<true>, smem) : set_smem(global_pre_bwd_kernel<false>, smem);
     if (rc) return rc;
-    PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C};
-    PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
+    PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C, dgh_is_dz3, (unsigned long long*)pb_debug_ptr()};
+    if (dgh_is_dz3) PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel<true>, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
+    else PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel<false>, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
     pb_count_launch(1);
     return pb_check_launch("pb_global_pre_bwd");
 }
@@ -577,16 +638,17 @@ int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const
 int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2, const float* rstd2, const float* z4,
                        const float* g1, const float* W4, const float* gamma1, const float* xhat1, const float* rstd1,
                        const float* pool, const float* Wp, int Kdim, float* scratch3, float* dx1, float* dpool, float* dWp,
-                       float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2, float* dbeta2, int B, int G,
-                       void* stream) {
+                       float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2, float* dbeta2, const float* z3,
+                       float* dz3, int B, int G, void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, 8), PB_ERR_UNSUPPORTED, "global_post_bwd: shape B=%d G=%d not covered", B, G);
     PB_REQUIRE(Kdim > 0 && scratch3 != nullptr, PB_ERR_SHAPE, "global_post_bwd: bad arguments");
     const size_t smem = smem_bytes(row_tile_of(G), G, true);
     int rc = set_smem(global_post_bwd_kernel, smem);
     if (rc) return rc;
     const size_t n = (size_t)B * G;
-    PostBwd p{dg2, gamma2, xhat2, rstd2, z4, g1, W4, gamma1, xhat1, rstd1, pool, Wp,
-              scratch3, scratch3 + n, scratch3 + 2 * n, dx1, dpool, dWp, dgamma1, dbeta1, dW4, db4, dgamma2, dbeta2, B, G, Kdim};
+    PB_REQUIRE((z3 == nullptr) == (dz3 == nullptr), PB_ERR_SHAPE, "global_post_bwd: z3 and dz3 go together");
+    PostBwd p{dg2, gamma2, xhat2, rstd2, z4, g1, W4, gamma1, xhat1, rstd1, pool, Wp, z3, dz3,
+              scratch3, scratch3 + n, scratch3 + 2 * n, dx1, dpool, dWp, dgamma1, dbeta1, dW4, db4, dgamma2, dbeta2, B, G, Kdim, (unsigned long long*)pb_debug_ptr()};
     void* args[] = {&p};
     PB_CUDA(cudaLaunchCooperativeKernel((const void*)global_post_bwd_kernel, dim3(G / kNT), dim3(kThreads), args, smem,
                                         (cudaStream_t)stream));

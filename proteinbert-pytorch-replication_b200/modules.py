@@ -135,7 +135,8 @@ class ProteinBERTBlock(nn.Module):
         gl1, gl2 = self.global_linear_layer_1[0], self.global_linear_layer_2[0]
         fused = self.fuse_global and ops.global_fused_ok(g.shape[0], g.shape[1], g2l_lin.weight.shape[0])
         if fused:       # both linears that read the block's input g in one launch
-            g2l, gh = ops.GlobalPreFn.apply(g, g2l_lin.weight, g2l_lin.bias, gl1.weight, gl1.bias)   # :208, :221
+            link = ops.GlobalLink()
+            g2l, gh = ops.GlobalPreFn.apply(g, g2l_lin.weight, g2l_lin.bias, gl1.weight, gl1.bias, link)   # :208, :221
         else:
             g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                    # modules.py:208
         h, pool = ops.LocalTrackFn.apply(                                                      # :205-219
@@ -146,7 +147,7 @@ class ProteinBERTBlock(nn.Module):
             *[hd.Wv_parameter for hd in att.global_attention_heads])
         if fused:       # LN(g + gh + att), Linear+GELU, LN in one launch                       # :223-229
             g2 = ops.GlobalPostFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias,
-                                        gl2.weight, gl2.bias, self.global_norm_2.weight, self.global_norm_2.bias)
+                                        gl2.weight, gl2.bias, self.global_norm_2.weight, self.global_norm_2.bias, link)
             return h, g2
         gh = ops.linear_act(g, gl1.weight, gl1.bias, ACT_GELU)                                  # :221
         g1 = ops.ResLnRowsFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224

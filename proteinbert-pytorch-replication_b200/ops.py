@@ -273,11 +273,22 @@ class ResLnRowsFn(torch.autograd.Function):
         return dx, (dx if has_b else None), dc, dwp, dgamma, dbeta
 
 
+class GlobalLink:
+    """Side channel between the two fused global-track functions of one block.  GlobalPostFn.backward produces
+    dgh (= dx1) and, because it holds every row anyway, also dgh * gelu'(z3); GlobalPreFn.backward takes that product
+    from here instead of recomputing the B x G derivatives in each of its CTAs.  Used only when the tensor autograd
+    hands to GlobalPreFn.backward is the very tensor GlobalPostFn.backward returned (no other consumer of gh)."""
+    __slots__ = ("z3", "dz3", "dgh_ptr")
+
+    def __init__(self):
+        self.z3 = self.dz3 = self.dgh_ptr = None
+
+
 class GlobalPreFn(torch.autograd.Function):
     """(g2l, gh) = (gelu(g W1^T + b1), gelu(g W3^T + b3)) in one launch (modules.py:208,221)."""
 
     @staticmethod
-    def forward(ctx, g, W1, b1, W3, b3):
+    def forward(ctx, g, W1, b1, W3, b3, link=None):
         _need_cuda(g, W1, W3)
         g = g.contiguous()
         B, G = g.shape
@@ -288,6 +299,9 @@ class GlobalPreFn(torch.autograd.Function):
         _call("pb_global_pre_fwd", _p(g), _p(W1), _p(b1), _p(W3), _p(b3), _p(zg[0]), _p(zg[1]), _p(z3[0]), _p(z3[1]),
               B, G, C, _st())
         ctx.save_for_backward(g, W1, W3, zg, z3)
+        ctx.link = link
+        if link is not None:
+            link.z3 = z3[0]
         return zg[1], z3[1]
 
     @staticmethod
@@ -298,19 +312,25 @@ class GlobalPreFn(torch.autograd.Function):
         dev = g.device
         dg2l = torch.zeros((B, C), dtype=torch.float32, device=dev) if dg2l is None else dg2l.contiguous()
         dgh = torch.zeros((B, G), dtype=torch.float32, device=dev) if dgh is None else dgh.contiguous()
+        link = ctx.link
+        ready = 0
+        if link is not None and link.dz3 is not None and link.dgh_ptr == dgh.data_ptr():
+            dgh, ready = link.dz3, 1
+        if link is not None:
+            link.z3 = link.dz3 = link.dgh_ptr = None
         dg = torch.empty_like(g)
         dW1, db1 = torch.empty_like(W1), torch.empty((C,), dtype=torch.float32, device=dev)
         dW3, db3 = torch.empty_like(W3), torch.empty((G,), dtype=torch.float32, device=dev)
         _call("pb_global_pre_bwd", _p(dg2l), _p(dgh), _p(zg[0]), _p(z3[0]), _p(g), _p(W1), _p(W3), _p(dg), _p(dW1), _p(db1),
-              _p(dW3), _p(db3), B, G, C, _st())
-        return dg, dW1, db1, dW3, db3
+              _p(dW3), _p(db3), B, G, C, ready, _st())
+        return dg, dW1, db1, dW3, db3, None
 
 
 class GlobalPostFn(torch.autograd.Function):
     """g2 = LN(g1 + gelu(g1 W4^T + b4)), g1 = LN(g + gh + (sum(Wp)/K) pool) in one launch (modules.py:92,223-229)."""
 
     @staticmethod
-    def forward(ctx, g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2):
+    def forward(ctx, g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, link=None):
         _need_cuda(g, gh, pool, W4)
         g, gh, pool = g.contiguous(), gh.contiguous(), pool.contiguous()
         B, G = g.shape
@@ -321,6 +341,7 @@ class GlobalPostFn(torch.autograd.Function):
               _p(gamma2), _p(beta2), _p(buf[0]), _p(buf[1]), _p(rstd[0]), _p(buf[2]), _p(buf[3]), _p(rstd[1]), _p(buf[4]),
               B, G, _st())
         ctx.save_for_backward(pool, Wp, gamma1, W4, gamma2, buf, rstd)
+        ctx.link = link
         return buf[4]
 
     @staticmethod
@@ -329,14 +350,19 @@ class GlobalPostFn(torch.autograd.Function):
         B, G = pool.shape
         dev = pool.device
         dg2 = dg2.contiguous()
-        out = torch.empty((5, B, G), dtype=torch.float32, device=dev)      # 3 x scratch, dx1, dpool
+        link = ctx.link
+        z3 = link.z3 if link is not None else None
+        out = torch.empty((6 if z3 is not None else 5, B, G), dtype=torch.float32, device=dev)   # 3 x scratch, dx1, dpool[, dz3]
         dWp = torch.empty_like(Wp)
         vec = torch.empty((5, G), dtype=torch.float32, device=dev)         # dgamma1, dbeta1, db4, dgamma2, dbeta2
         dW4 = torch.empty_like(W4)
+        dz3 = out[5] if z3 is not None else None
         _call("pb_global_post_bwd", _p(dg2), _p(gamma2), _p(buf[3]), _p(rstd[1]), _p(buf[2]), _p(buf[0]), _p(W4), _p(gamma1),
               _p(buf[1]), _p(rstd[0]), _p(pool), _p(Wp), Wp.numel(), _p(out[0]), _p(out[3]), _p(out[4]), _p(dWp), _p(vec[0]),
-              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), B, G, _st())
-        return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4]
+              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), _p(z3), _p(dz3), B, G, _st())
+        if dz3 is not None:
+            link.dz3, link.dgh_ptr = dz3, out[3].data_ptr()
+        return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4], None
 
 
 def global_fused_ok(B, G, C) -> bool:
@@ -576,4 +602,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
