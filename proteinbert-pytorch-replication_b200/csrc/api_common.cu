@@ -67,6 +67,9 @@ __global__ void conv_pack_kernel(const float* __restrict__ w, T* __restrict__ fw
     }
 }
 
+__device__ __forceinline__ void st2(float* p, size_t i, float a, float b) { *reinterpret_cast<float2*>(p + i) = make_float2(a, b); }
+__device__ __forceinline__ void st2(bf16* p, size_t i, float a, float b) { *reinterpret_cast<__nv_bfloat162*>(p + i) = __floats2bfloat162_rn(a, b); }
+
 // One launch stages every weight of the local track: blockIdx.y walks a device table of jobs.
 //   kind 0: src [d0, d1] row-major -> dst0[r*ld0 + c] (copy/cast) and dst1[c*ld1 + r] (transposed copy/cast)
 //   kind 1: src [Co=d0, Ci=d1, k=d2] -> dst0 [k][Co][Ci], dst1 [k][Ci][Co]
@@ -86,13 +89,30 @@ __global__ void stage_weights_kernel(const pb_stage_desc* __restrict__ jobs) {
     } else {
         const int C0 = j.d0, C1 = j.d1, k = j.d2;
         const long long n = (long long)C0 * C1 * k;
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-            const int t = (int)(i % k);
-            const int ci = (int)((i / k) % C1);
-            const int co = (int)(i / ((long long)k * C1));
-            const float v = j.src[i];
-            if (d0) stf(d0, ((size_t)t * C0 + co) * C1 + ci, v);
-            if (d1) stf(d1, ((size_t)t * C1 + ci) * C0 + co, v);
+        if (((C0 | C1) & 1) == 0) {
+            // gather form: threads walk the OUTPUT in pairs (coalesced 4/8-byte stores); the strided reads stay in L1/L2
+            for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n / 2; i += (long long)gridDim.x * blockDim.x) {
+                const long long o = 2 * i;
+                if (d0) {
+                    const int ci = (int)(o % C1), co = (int)((o / C1) % C0), t = (int)(o / ((long long)C1 * C0));
+                    const float* sp = j.src + ((size_t)co * C1 + ci) * k + t;
+                    st2(d0, (size_t)o, __ldg(sp), __ldg(sp + k));
+                }
+                if (d1) {
+                    const int co = (int)(o % C0), ci = (int)((o / C0) % C1), t = (int)(o / ((long long)C1 * C0));
+                    const float* sp = j.src + ((size_t)co * C1 + ci) * k + t;
+                    st2(d1, (size_t)o, __ldg(sp), __ldg(sp + (size_t)C1 * k));
+                }
+            }
+        } else {
+            for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+                const int t = (int)(i % k);
+                const int ci = (int)((i / k) % C1);
+                const int co = (int)(i / ((long long)k * C1));
+                const float v = j.src[i];
+                if (d0) stf(d0, ((size_t)t * C0 + co) * C1 + ci, v);
+                if (d1) stf(d1, ((size_t)t * C1 + ci) * C0 + co, v);
+            }
         }
     }
 }

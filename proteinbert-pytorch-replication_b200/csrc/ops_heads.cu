@@ -25,6 +25,27 @@ __global__ void embedding_fwd_kernel(const int64_t* __restrict__ tok, const floa
         stf(out, (size_t)i, (t >= 0 && t < V) ? table[(size_t)t * C + c] : 0.f);
     }
 }
+// C % 8 == 0: one thread per 8 channels of a row, 16-byte stores
+__global__ void embedding_fwd_vec_kernel(const int64_t* __restrict__ tok, const float* __restrict__ table, bf16* __restrict__ out,
+                                         long long n_tok, int C, int V) {
+    const int vpr = C / 8;
+    const long long total = n_tok * vpr;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long r = i / vpr;
+        const int c = (int)(i - r * vpr) * 8;
+        const int64_t t = tok[r];
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+        if (t >= 0 && t < V) {
+            a = __ldg(reinterpret_cast<const float4*>(table + (size_t)t * C + c));
+            b = __ldg(reinterpret_cast<const float4*>(table + (size_t)t * C + c + 4));
+        }
+        uint4 o;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+        h[0] = __floats2bfloat162_rn(a.x, a.y); h[1] = __floats2bfloat162_rn(a.z, a.w);
+        h[2] = __floats2bfloat162_rn(b.x, b.y); h[3] = __floats2bfloat162_rn(b.z, b.w);
+        *reinterpret_cast<uint4*>(out + (size_t)r * C + c) = o;
+    }
+}
 
 // shared-memory privatised scatter-add: each CTA owns a [V, C] float accumulator for its slice of rows
 template <typename T>
@@ -62,11 +83,25 @@ __global__ void embedding_bwd_warp_kernel(const int64_t* __restrict__ tok, const
     __syncthreads();
     float* mine = acc + (size_t)warp * VC;
     const long long gw = (long long)blockIdx.x * nwarp + warp, nw = (long long)gridDim.x * nwarp;
-    for (long long r = gw; r < n_tok; r += nw) {
-        const int64_t t = tok[r];
-        if (t < 0 || t >= V) continue;
-        float* row = mine + (int)t * C;
-        for (int c = lane; c < C; c += 32) row[c] += ldf(dout, (size_t)r * C + c);
+    // eight rows per trip: the token ids, then all their gradient values, are requested before anything is added, so a
+    // warp's walk is a few round trips to memory instead of two per row
+    constexpr int R = 8;
+    for (long long r = gw; r < n_tok; r += R * nw) {
+        int t[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const long long rr = r + j * nw;
+            const int64_t tt = rr < n_tok ? tok[rr] : -1;
+            t[j] = (tt >= 0 && tt < V) ? (int)tt : -1;
+        }
+        for (int c = lane; c < C; c += 32) {
+            float v[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) v[j] = t[j] >= 0 ? ldf(dout, (size_t)(r + j * nw) * C + c) : 0.f;
+#pragma unroll
+            for (int j = 0; j < R; ++j)
+                if (t[j] >= 0) mine[t[j] * C + c] += v[j];
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < VC; i += blockDim.x) {
@@ -307,7 +342,12 @@ extern "C" {
 int pb_embedding_fwd(const int64_t* tok, const float* table, void* out, long long n_tok, int C, int V, int dt, void* stream) {
     PB_REQUIRE(n_tok > 0 && C > 0 && V > 0, PB_ERR_SHAPE, "embedding_fwd: bad shape");
     const int grid = (int)min((long long)ceil_div(n_tok * C, 256), 148LL * 16);
-    DISPATCH_DT(dt, (embedding_fwd_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(tok, table, (T*)out, n_tok, C, V)));
+    if (dt == PB_BF16 && C % 8 == 0) {
+        const int gv = (int)min((long long)ceil_div(n_tok * (C / 8), 256), 148LL * 16);
+        embedding_fwd_vec_kernel<<<gv, 256, 0, (cudaStream_t)stream>>>(tok, table, (bf16*)out, n_tok, C, V);
+    } else {
+        DISPATCH_DT(dt, (embedding_fwd_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(tok, table, (T*)out, n_tok, C, V)));
+    }
     pb_count_launch(1);
     return pb_check_launch("pb_embedding_fwd");
 }
@@ -323,7 +363,7 @@ int pb_embedding_bwd(const int64_t* tok, const void* dout, float* dtable, long l
     DISPATCH_DT(dt, {
         if (smem_w <= 200 * 1024) {
             if (smem_w > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_warp_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w));
-            embedding_bwd_warp_kernel<T><<<min(grid, 148), 256, smem_w, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
+            embedding_bwd_warp_kernel<T><<<min(grid, smem_w <= 110 * 1024 ? 296 : 148), 256, smem_w, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);
         } else {
             if (smem > 48 * 1024) PB_CUDA(cudaFuncSetAttribute(embedding_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             embedding_bwd_kernel<T><<<grid, 256, smem, st>>>(tok, (const T*)dout, dtable, n_tok, C, V);

@@ -118,7 +118,7 @@ class ProteinBERTBlock(nn.Module):
         self.global_linear_layer_2 = nn.Sequential(nn.Linear(global_dim, global_dim, device=device), nn.GELU())
         self.global_norm_2 = nn.LayerNorm(normalized_shape=global_dim, device=device)
 
-    def forward_channels_last(self, xl: torch.Tensor, g: torch.Tensor):
+    def forward_channels_last(self, xl: torch.Tensor, g: torch.Tensor, arena=None):
         """xl [B,L,C] in the activation dtype, g [B,G] float -> (h [B,L,C], g_out [B,G])."""
         if xl.shape[1] != self.sequences_length:
             raise ValueError(f"sequence length {xl.shape[1]} != sequences_length {self.sequences_length} "
@@ -143,7 +143,7 @@ class ProteinBERTBlock(nn.Module):
             xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
             self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
             self.local_norm_2.weight, self.local_norm_2.bias, staged,
-            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads,
+            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads, arena,
             *[hd.Wv_parameter for hd in att.global_attention_heads])
         if fused:       # LN(g + gh + att), Linear+GELU, LN in one launch                       # :223-229
             g2 = ops.GlobalPostFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias,
@@ -219,11 +219,13 @@ class ProteinBERT(nn.Module):
         blocks = list(self.proteinBERT_blocks)
         ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
         cut = getattr(self, "_boundary_at", None)        # training.GraphedPretrainStep: where backward is split in two
+        Bsz, Lseq, Cloc = h.shape
+        arena = ops.ZeroArena(len(blocks) * ops.ZeroArena.block_bytes(Bsz, Lseq, Cloc, g.shape[1]), h.device)   # one fill per step
         for i, blk in enumerate(blocks):
             if cut is not None and i == cut:
                 self._boundary = (h, g)
             blk._prestaged = dt
-            h, g = blk.forward_channels_last(h, g)
+            h, g = blk.forward_channels_last(h, g, arena)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
         p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284
         p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID, tc)                       # :286-293

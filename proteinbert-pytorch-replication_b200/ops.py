@@ -369,13 +369,45 @@ def global_fused_ok(B, G, C) -> bool:
     return bool(lib().pb_global_fused_ok(B, G, C))
 
 
+class ZeroArena:
+    """One zero-filled buffer per model forward from which every block takes its "zero on entry" operands (LayerNorm
+    statistics, pooling accumulator, and the accumulated gradients of its backward): one fill launch per step instead of
+    three per block.  Slices are handed out once; a LocalTrackFn backward that runs a second time on the same graph
+    allocates fresh zeros instead."""
+
+    def __init__(self, nbytes: int, device):
+        self.buf = torch.zeros(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        self.off = 0
+
+    @staticmethod
+    def _acc_floats(B, L, C):
+        return (4 * L * C + 3 * C + B * C + 3) // 4 * 4 + 8 * B
+
+    @staticmethod
+    def block_bytes(B, L, C, G):
+        def up(n):
+            return (n + 255) // 256 * 256
+        return up(2 * B * 2 * 8) + up(B * G * 4) + up(ZeroArena._acc_floats(B, L, C) * 4)
+
+    def take(self, shape, dtype):
+        n = 1
+        for d in shape:
+            n *= int(d)
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        o = self.off
+        if o + nbytes > self.buf.numel():
+            return torch.zeros(shape, dtype=dtype, device=self.buf.device)
+        self.off = (o + nbytes + 255) // 256 * 256
+        return self.buf[o:o + nbytes].view(dtype).view(shape)
+
+
 class LocalTrackFn(torch.autograd.Function):
     """The local track of one ProteinBERTBlock plus the attention pooling it feeds
     (modules.py:205-219): conv pair + GELU + 4-way add -> joint LN -> Linear+GELU+residual -> joint LN
     -> pool[b,g] = sum_l gelu(h . Wv).  Returns (h2 [B,L,C] act, pool [B,G] f32)."""
 
     @staticmethod
-    def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, staged, ksize, dil, head_grads, *head_wv):
+    def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, staged, ksize, dil, head_grads, arena, *head_wv):
         _need_cuda(x, g2l, Wn)
         x = x.contiguous()
         dt = dt_of(x)
@@ -390,7 +422,10 @@ class LocalTrackFn(torch.autograd.Function):
         W2w, wvTw = staged.W2w, staged.wvT
         # transposed copies: the K-major operands of the tensor-core data-gradient GEMMs
         W2Tw, wvw = staged.W2Tw, staged.wv
-        stats = torch.zeros((2, B, 2), dtype=torch.float64, device=dev)
+        if arena is not None:
+            stats = arena.take((2, B, 2), torch.float64)
+        else:
+            stats = torch.zeros((2, B, 2), dtype=torch.float64, device=dev)
         stats1, stats2 = stats[0], stats[1]
         zn, zw, u1, h1, z2, u2, h2 = (torch.empty_like(x) for _ in range(7))
         g2l = g2l.contiguous()
@@ -399,9 +434,11 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_ln_joint_apply", _p(u1), _p(stats1), _p(ln1w), _p(ln1b), _p(h1), B, L, C, LN_EPS, dt, st)
         _call("pb_local_linear_fwd", _p(h1), _p(W2w), _p(b2), _p(z2), _p(u2), _p(stats2), B, L, C, dt, st)
         _call("pb_ln_joint_apply", _p(u2), _p(stats2), _p(ln2w), _p(ln2b), _p(h2), B, L, C, LN_EPS, dt, st)
-        pool = torch.zeros((B, G), dtype=torch.float32, device=dev)
+        pool = arena.take((B, G), torch.float32) if arena is not None else torch.zeros((B, G), dtype=torch.float32, device=dev)
         _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
         ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, ln1w, ln2w)
+        # the zeroed accumulators of backward are reserved now, from the same per-step fill
+        ctx.bwd_zero = arena.take((ZeroArena._acc_floats(B, L, C),), torch.float32) if arena is not None else None
         ctx.staged = staged
         ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads), len(head_wv))
         return h2, pool
@@ -426,7 +463,9 @@ class LocalTrackFn(torch.autograd.Function):
 
         # every accumulated ("zero on entry") output of this backward lives in one arena cleared by one fill
         n_acc = (4 * L * C + 3 * C + B * C + 3) // 4 * 4                 # keeps the double area 16-byte aligned
-        arena = torch.zeros(n_acc + 8 * B, dtype=torch.float32, device=dev)
+        arena, ctx.bwd_zero = ctx.bwd_zero, None          # a second backward over the same graph must not reuse it
+        if arena is None or arena.numel() != n_acc + 8 * B:
+            arena = torch.zeros(n_acc + 8 * B, dtype=torch.float32, device=dev)
         dln1w, dln1b = arena[0:L * C].view(L, C), arena[L * C:2 * L * C].view(L, C)
         dln2w, dln2b = arena[2 * L * C:3 * L * C].view(L, C), arena[3 * L * C:4 * L * C].view(L, C)
         o = 4 * L * C
@@ -479,7 +518,7 @@ class LocalTrackFn(torch.autograd.Function):
             dheads = tuple(dWv[h] for h in range(n_heads))
         else:
             dheads = (None,) * n_heads
-        return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, None, None, None, None) + dheads
+        return (dx, dg2l, dWn, dbn, dWw, dbw, dln1w, dln1b, dW2, db2, dln2w, dln2b, None, None, None, None, None) + dheads
 
 
 class AttnPoolFn(torch.autograd.Function):
@@ -602,4 +641,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "ZeroArena", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
