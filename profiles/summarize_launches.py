@@ -20,7 +20,7 @@ def main(path, title=""):
         a[1] += v
         tot += v
         n += 1
-    print(f"# {title}\n\n{n} launches, {tot:.0f} us total (cold-cache, serialised: compare shares)\n")
+    print(f"# {title}\n\n{n} launches, {tot:.0f} us total (serialised launches; cold L2 unless the title says --cache-control none: compare shares)\n")
     print("| kernel | launches | total us | us/launch | share |\n|---|---:|---:|---:|---:|")
     for k, (c, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
         print(f"| `{k}` | {c} | {t:.1f} | {t / c:.1f} | {100 * t / tot:.1f}% |")
