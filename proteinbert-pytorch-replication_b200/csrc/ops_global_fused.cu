@@ -131,53 +131,37 @@ __device__ __forceinline__ void fill_tile(float* A_s, int lda, int MT, int mt, i
     }
 }
 
-// dW rows of this CTA's slice: acc[q][j] += sum_m D_s[m*8 + j] * X[(row0+m)*ldx + kcol], kcol = tid + q*512.
-// Rows are taken R at a time with all global loads issued before the FMAs: the sweep is a chain of mt / R round trips
-// to L2, so R is as large as the registers allow without spilling (16 rows when one column per thread covers Kout, else 8).
-template <int Q, int R>
-__device__ __forceinline__ void dw_accumulate_q(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
-                                                int row0, int mt, int Kout) {
-    for (int m0 = 0; m0 < mt; m0 += R) {
-        float x[R][Q];
+// Weight gradients from the staged tile: the A tile in shared memory already holds every row of dZ for ALL its columns,
+// so a CTA can produce dW[n, k0 .. k0+7] for every n from it and an 8-column slice of X (64 x 8 floats) -- instead of
+// sweeping all rows of X from L2 for its own 8 rows of dW.  acc[q][j] += sum_m A_s[m][n] * Xs[m][j], n = tid + q*512.
+__device__ __forceinline__ void fill_x_slice(float* Xs, const float* __restrict__ X, int ldx, int row0, int mt, int MT, int k0) {
+    for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
+        const int m = i / kNT, j = i - m * kNT;
+        Xs[i] = m < mt ? __ldg(X + (size_t)(row0 + m) * ldx + k0 + j) : 0.f;
+    }
+}
+__device__ __forceinline__ void dw_from_tile(float (&acc)[kQ][kNT], const float* A_s, int lda, const float* Xs, int mt, int Nrows) {
+#pragma unroll 4
+    for (int m = 0; m < mt; ++m) {
+        const float4 x0 = *reinterpret_cast<const float4*>(Xs + m * kNT);
+        const float4 x1 = *reinterpret_cast<const float4*>(Xs + m * kNT + 4);
 #pragma unroll
-        for (int i = 0; i < R; ++i)
-#pragma unroll
-            for (int q = 0; q < Q; ++q) {
-                const int kc = threadIdx.x + q * kThreads;
-                x[i][q] = (m0 + i < mt && kc < Kout) ? __ldg(X + (size_t)(row0 + m0 + i) * ldx + kc) : 0.f;
-            }
-#pragma unroll
-        for (int i = 0; i < R; ++i) {
-            if (m0 + i < mt) {
-                const float4 d0 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT);
-                const float4 d1 = *reinterpret_cast<const float4*>(D_s + (m0 + i) * kNT + 4);
-#pragma unroll
-                for (int q = 0; q < Q; ++q) {
-                    const float xv = x[i][q];
-                    acc[q][0] = fmaf(d0.x, xv, acc[q][0]); acc[q][1] = fmaf(d0.y, xv, acc[q][1]);
-                    acc[q][2] = fmaf(d0.z, xv, acc[q][2]); acc[q][3] = fmaf(d0.w, xv, acc[q][3]);
-                    acc[q][4] = fmaf(d1.x, xv, acc[q][4]); acc[q][5] = fmaf(d1.y, xv, acc[q][5]);
-                    acc[q][6] = fmaf(d1.z, xv, acc[q][6]); acc[q][7] = fmaf(d1.w, xv, acc[q][7]);
-                }
+        for (int q = 0; q < kQ; ++q) {
+            const int n = threadIdx.x + q * kThreads;
+            if (n < Nrows) {
+                const float a = A_s[(size_t)m * lda + n];
+                acc[q][0] = fmaf(a, x0.x, acc[q][0]); acc[q][1] = fmaf(a, x0.y, acc[q][1]);
+                acc[q][2] = fmaf(a, x0.z, acc[q][2]); acc[q][3] = fmaf(a, x0.w, acc[q][3]);
+                acc[q][4] = fmaf(a, x1.x, acc[q][4]); acc[q][5] = fmaf(a, x1.y, acc[q][5]);
+                acc[q][6] = fmaf(a, x1.z, acc[q][6]); acc[q][7] = fmaf(a, x1.w, acc[q][7]);
             }
         }
     }
 }
-__device__ __forceinline__ void dw_accumulate(float (&acc)[kQ][kNT], const float* D_s, const float* __restrict__ X, int ldx,
-                                              int row0, int mt, int Kout) {
-    if (Kout <= kThreads) dw_accumulate_q<1, 16>(acc, D_s, X, ldx, row0, mt, Kout);
-    else dw_accumulate_q<kQ, 8>(acc, D_s, X, ldx, row0, mt, Kout);
+__device__ __forceinline__ void store8(float* dst, const float (&v)[kNT]) {
+    *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
 }
-__device__ __forceinline__ void dw_store(const float (&acc)[kQ][kNT], float* __restrict__ dW, int ldw, int n0, int Kout) {
-#pragma unroll
-    for (int q = 0; q < kQ; ++q) {
-        const int kc = threadIdx.x + q * kThreads;
-        if (kc < Kout)
-#pragma unroll
-            for (int j = 0; j < kNT; ++j) dW[(size_t)(n0 + j) * ldw + kc] = acc[q][j];
-    }
-}
-
 __device__ __forceinline__ float coef_of(const float* __restrict__ Wp, int Kdim, float* red /* >= 32 */) {
     float t = 0.f;
     for (int k = threadIdx.x; k < Kdim; k += kThreads) t += Wp[k];
@@ -257,8 +241,8 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     float* A_s = sm;                                   // [MT][lda] = [dz3 | dzg]
     float* Bt_s = A_s + (size_t)MT * lda;              // [KA][8]
     float* red_s = Bt_s + (size_t)KA * kNT;            // [512*8]
-    float* D_s = red_s + kThreads * kNT;               // [MT][8] slice of dz for the dW product
-    // CTA i owns columns [8i, 8i+8) of dg (if < G) and rows [8i, 8i+8) of the stacked [dW3 ; dW1] matrix.
+    float* D_s = red_s + kThreads * kNT;               // [MT][8] slice g[:, n0 .. n0+7] for the dW product
+    // CTA i owns columns [8i, 8i+8) of dg and of the stacked [dW3 ; dW1] matrix (if 8i < G), and db entries [8i, 8i+8).
     pdl_wait();
     const int n0 = blockIdx.x * kNT;                   // 0 .. G + C
     const bool has_dg = n0 < G;
@@ -285,19 +269,16 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
         fill_tile<2, false>(A_s + G, lda, MT, mt, C, p.dg2l, p.zg, C, row0, MulGeluGrad4());
         __syncthreads();
         stamp(p.dbg, 17);
-        for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
-            const int m = i / kNT, j = i - m * kNT;
-            D_s[i] = A_s[(size_t)m * lda + n0 + j];    // n0 + j < KA always ((G + C) % 8 == 0)
-        }
-        __syncthreads();
-        if (threadIdx.x < 32) {
+        if (has_dg) fill_x_slice(D_s, p.g, G, row0, mt, MT, n0);         // g[:, n0 .. n0+7]
+        if (threadIdx.x < 32) {                        // db of columns n0 .. n0+7 of [dz3 | dzg] (n0 + j < KA always)
             float a = 0.f;
-            for (int m = threadIdx.x >> 3; m < mt; m += 4) a += D_s[m * kNT + (threadIdx.x & 7)];
+            for (int m = threadIdx.x >> 3; m < mt; m += 4) a += A_s[(size_t)m * lda + n0 + (threadIdx.x & 7)];
             a += __shfl_xor_sync(0xffffffffu, a, 8); a += __shfl_xor_sync(0xffffffffu, a, 16);
             colsum += a;                               // read by threads < 8 only
         }
+        __syncthreads();
         stamp(p.dbg, 18);
-        dw_accumulate(accw, D_s, p.g, G, row0, mt, G);
+        if (has_dg) dw_from_tile(accw, A_s, lda, D_s, mt, KA);          // [dW3 ; dW1][:, n0 .. n0+7]
         stamp(p.dbg, 19);
         if (has_dg) {
             float out[kNT];
@@ -310,7 +291,13 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
         }
     }
     stamp(p.dbg, 20);
-    dw_store(accw, w_is_3 ? p.dW3 : p.dW1, G, wrow0, G);
+    if (has_dg) {
+#pragma unroll
+        for (int q = 0; q < kQ; ++q) {
+            const int n = threadIdx.x + q * kThreads;
+            if (n < KA) store8((n < G ? p.dW3 + (size_t)n * G : p.dW1 + (size_t)(n - G) * G) + n0, accw[q]);
+        }
+    }
     if (threadIdx.x < kNT) (w_is_3 ? p.db3 : p.db1)[wrow0 + threadIdx.x] = colsum;
     stamp(p.dbg, 21);
 }
@@ -471,11 +458,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
         fill_tile<1, true>(A_s, lda, MT, mt, G, p.dz4, nullptr, G, row0, Copy4());
         __syncthreads();
         stamp(p.dbg, 35);
-        for (int i = threadIdx.x; i < MT * kNT; i += kThreads) {
-            const int m = i / kNT, j = i - m * kNT;
-            D_s[i] = A_s[(size_t)m * lda + n0 + j];
-        }
-        __syncthreads();
+        fill_x_slice(D_s, p.g1, G, row0, mt, MT, n0);                   // g1[:, n0 .. n0+7]
         if (threadIdx.x < 32) {          // one warp: 8 columns x 4 row lanes, folded with two shuffles
             const int j = threadIdx.x & 7, c = n0 + j;
             float a = 0.f, b = 0.f, e = 0.f;
@@ -483,7 +466,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             for (int m = threadIdx.x >> 3; m < mt; m += 4) {
                 const size_t o = (size_t)(row0 + m) * G + c;
                 const float dv = p.dg2[o];
-                a += D_s[m * kNT + j];
+                a += A_s[(size_t)m * lda + c];
                 b += dv * p.xhat2[o];
                 e += dv;
             }
@@ -492,8 +475,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             e += __shfl_xor_sync(0xffffffffu, e, 8); e += __shfl_xor_sync(0xffffffffu, e, 16);
             c_db4 += a; c_dg2 += b; c_db2 += e;       // read by threads < 8 only
         }
+        __syncthreads();
         stamp(p.dbg, 36);
-        dw_accumulate(accw, D_s, p.g1, G, row0, mt, G);                 // dW4[n0.., :] += dz4[:, n0..]^T g1
+        dw_from_tile(accw, A_s, lda, D_s, mt, G);                       // dW4[:, n0 .. n0+7] = dz4^T g1[:, n0 ..]
         stamp(p.dbg, 37);
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);                   // dz4 W4[:, n0..]
@@ -505,7 +489,11 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             *reinterpret_cast<float4*>(p.dg1 + o + 4) = make_float4(out[4] + x1.x, out[5] + x1.y, out[6] + x1.z, out[7] + x1.w);
         }
     }
-    dw_store(accw, p.dW4, G, n0, G);
+#pragma unroll
+    for (int q = 0; q < kQ; ++q) {
+        const int n = threadIdx.x + q * kThreads;
+        if (n < G) store8(p.dW4 + (size_t)n * G + n0, accw[q]);
+    }
     if (threadIdx.x < kNT) {
         p.db4[n0 + threadIdx.x] = c_db4;
         p.dgamma2[n0 + threadIdx.x] = c_dg2;
