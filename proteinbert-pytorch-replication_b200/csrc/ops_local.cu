@@ -342,7 +342,25 @@ __global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __rest
     const LnStat st = ln_stat(stats, b, (double)n, eps);
     const long long nv = n / 8;
     float s1 = 0.f, s2 = 0.f;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+    const long long step = (long long)gridDim.x * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    // two vectors per trip, all six loads issued before the arithmetic: the kernel is a chain of memory round trips
+    for (; i + step < nv; i += 2 * step) {
+        float d0[8], x0[8], g0[8], d1[8], x1[8], g1[8];
+        V8<T>::ld(dy + (size_t)b * n + i * 8, d0);
+        V8<T>::ld(u + (size_t)b * n + i * 8, x0);
+        V8<T>::ld(dy + (size_t)b * n + (i + step) * 8, d1);
+        V8<T>::ld(u + (size_t)b * n + (i + step) * 8, x1);
+        ldf8(gamma + i * 8, g0);
+        ldf8(gamma + (i + step) * 8, g1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float a = d0[j] * g0[j], c = d1[j] * g1[j];
+            s1 += a + c;
+            s2 += a * ((x0[j] - st.mean) * st.rstd) + c * ((x1[j] - st.mean) * st.rstd);
+        }
+    }
+    for (; i < nv; i += step) {
         float d[8], x[8], g[8];
         V8<T>::ld(dy + (size_t)b * n + i * 8, d);
         V8<T>::ld(u + (size_t)b * n + i * 8, x);
@@ -690,7 +708,9 @@ int pb_ln_joint_bwd_gelu(const void* dy, const void* u, const double* stats, con
     cudaStream_t st = (cudaStream_t)stream;
     const long long n = (long long)L * C;
     const long long nv = n / 8;
-    int groups = (int)((75776 + nv - 1) / nv);
+    // 128 registers x 256 threads: two CTAs per SM, 296 resident CTAs; stay within ONE wave (a second, partial wave of
+    // CTAs that each walk their samples serially would double the time)
+    int groups = (int)(296 / ((nv + 255) / 256));
     if (groups > B) groups = B;
     if (groups < 1) groups = 1;
     int per_group = (B + groups - 1) / groups;
