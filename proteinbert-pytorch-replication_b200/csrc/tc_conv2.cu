@@ -7,7 +7,10 @@
 //     a UMMA descriptor whose start address is moved down by (tap offset) rows of 128 bytes;
 //   * each 16 KB weight tile that arrives in the ring feeds 8 MMAs (two 128-position sub-tiles x 4 k-steps)
 //     instead of 4, so the weight stream per position is halved;
-//   * four accumulators (2 sub-tiles x 2 convolutions) fill the 512 TMEM columns; eight epilogue warps.
+//   * four accumulators (2 sub-tiles x 2 convolutions) fill the 512 TMEM columns; eight epilogue warps;
+//   * forward: the GELU epilogue is 60 % as long as the MMA phase (cycle counters: 19 k vs 31 k cycles), so it is cut in
+//     two: the narrow convolution's half (zn out, x + gelu(zn) + g2l written back into its TMEM columns with
+//     tcgen05.st) runs while the dilated convolution's MMAs are still being issued; only the second half is exposed.
 // L2 -> smem traffic drops to ~0.65 MB per 256 positions (3.5x less per position).
 #include <stdlib.h>
 #include "tc_common.cuh"
@@ -59,12 +62,16 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     // narrow convolution has consumed chunk kc, the same buffer is refilled with dzw for the dilated one.
     const int a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
     uint8_t* ring = smem + 2 * a_buf;
-    uint64_t* full_bar = (uint64_t*)(ring + kStages * kBTile);
+    // forward: the first half of the epilogue (narrow convolution) runs while the ring still streams the dilated
+    // convolution's weights, so the staging tiles get their own area (one 3 x 2 KB buffer per epilogue warp) behind the
+    // ring; dgrad stages inside the ring, idle by then.
+    uint8_t* stage_base = kFwd ? ring + kStages * kBTile : ring;
+    uint64_t* full_bar = (uint64_t*)(kFwd ? stage_base + 8 * 3 * 2048 : ring + kStages * kBTile);
     uint64_t* empty_bar = full_bar + kStages;
     uint64_t* a_full = empty_bar + kStages;          // [2 inputs][2 chunks]
     uint64_t* a_free = a_full + 4;                   // [2 chunks]: narrow conv done with the buffer (dgrad)
-    uint64_t* tmem_full_bar = a_free + 2;
-    uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 1);
+    uint64_t* tmem_full_bar = a_free + 2;            // [2]: forward: narrow conv's accumulators / all; dgrad uses [1] only
+    uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tiles_per_sample = p.L / kRows;
@@ -78,7 +85,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         for (int i = 0; i < 4; ++i) mbar_init(&a_full[i], 1);
         mbar_init(&a_free[0], 1); mbar_init(&a_free[1], 1);
-        mbar_init(tmem_full_bar, 1);
+        mbar_init(&tmem_full_bar[0], 1); mbar_init(&tmem_full_bar[1], 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<512>(tmem_slot);
@@ -152,11 +159,12 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 }
                 umma_commit(&empty_bar[s]);
                 if (!kFwd && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
+                if (kFwd && i == p.ksize * 2 - 1) umma_commit(&tmem_full_bar[0]);       // narrow conv: both sub-tiles complete
             }
-            umma_commit(tmem_full_bar);
+            umma_commit(&tmem_full_bar[1]);
             if (p.dbg && blockIdx.x == 0) {
                 const long long t_issue_end = clock64();
-                mbar_wait(tmem_full_bar, 0);
+                mbar_wait(&tmem_full_bar[1], 0);
                 const long long t_done = clock64();
                 p.dbg[0] = t_issue_end - t_begin; p.dbg[1] = t_wait_full; p.dbg[2] = t_wait_a; p.dbg[3] = t_done - t_begin;
             }
@@ -164,61 +172,107 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     } else {
         // ===== epilogue: warps 2..9; sub-tile = (warp-2)/4, TMEM lane quarter = warp % 4 =====
         const long long e0 = clock64();
-        mbar_wait(tmem_full_bar, 0);
-        const long long e1 = clock64();
-        tc_fence_after();
         const int tile = (warp - 2) >> 2, q = warp & 3;
         const int row = tile * 128 + q * 32 + lane;                     // position inside the CTA's 256
         const size_t grow = ((size_t)b * p.L + l0 + row) * kC;
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + tile * 2 * kC;
         // Output tiles leave through TMA: each warp stages its 32 x 32 bf16 sub-tile per tensor in shared memory
-        // (64-byte swizzle, conflict-free 16-byte stores), then one lane issues the bulk tensor store.  The staging
-        // area is the weight ring, idle now; two buffers per warp so a store can drain while the next chunk is computed.
-        uint8_t* stage = ring + (warp - 2) * (2 * 3 * 2048);
+        // (64-byte swizzle, conflict-free 16-byte stores), then one lane issues the bulk tensor store.
+        uint8_t* stage = stage_base + (warp - 2) * (kFwd ? 3 * 2048 : 2 * 3 * 2048);
         const int sw = (lane >> 1) & 3;                                 // 64B swizzle: 16-byte chunk ^= (row / 2) & 3
-        // x for the residual comes from the halo tile that fed the MMAs (forward only)
-        const int hrow = half * p.dil + row;
+        const int lrow = l0 + tile * 128 + q * 32;
         float s_sum = 0.f, s_sq = 0.f;
+        long long e1 = e0;
+        if (kFwd) {
+            // ---- first half, under the MMAs of the dilated convolution: zn = acc + bn (stored), and the partial sum
+            //      x + gelu(zn) + g2l goes back into the accumulator's TMEM columns (tcgen05.st) for the second half.
+            //      x comes from the halo tile that feeds the MMAs.
+            const int hrow = half * p.dil + row;
+            mbar_wait(&tmem_full_bar[0], 0);
+            e1 = clock64();
+            tc_fence_after();
 #pragma unroll 1
-        for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
-            float an[32], aw[32];
-            tmem_ld32(taddr + ch * 32, an);
-            tmem_ld32(taddr + kC + ch * 32, aw);
-            const int c0 = ch * 32;
-            uint8_t* sbuf = stage + (ch & 1) * (3 * 2048);
-            if (ch >= 2) {                                               // the buffer's previous store must have read it
-                if (lane == 0) tma_store_wait_read<1>();
-                __syncwarp();
-            }
-            if (kFwd) {
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+                float an[32];
+                tmem_ld32(taddr + ch * 32, an);
+                const int c0 = ch * 32;
+                uint8_t* sbuf = stage + (ch & 1) * 2048;
                 uint4 xv[4];
                 const uint8_t* xrow = smem + (ch >> 1) * a_buf + (size_t)hrow * 128;
 #pragma unroll
                 for (int v = 0; v < 4; ++v) xv[v] = *reinterpret_cast<const uint4*>(xrow + ((((ch & 1) * 4 + v) ^ (hrow & 7)) * 16));
                 const bf16* xb = reinterpret_cast<const bf16*>(xv);
-                const float bnl = __ldg(p.bn + c0 + lane), bwl = __ldg(p.bw + c0 + lane), gl = __ldg(p.g2l + (size_t)b * kC + c0 + lane);
-                __align__(16) bf16 on[32], ow[32], ou[32];
+                const float bnl = __ldg(p.bn + c0 + lane), gl = __ldg(p.g2l + (size_t)b * kC + c0 + lane);
+                __align__(16) bf16 on[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const bf16 zn = __float2bfloat16_rn(an[j] + __shfl_sync(0xffffffffu, bnl, j));
+                    on[j] = zn;
+                    an[j] = (__bfloat162float(xb[j]) + gelu_fast(__bfloat162float(zn))) + __shfl_sync(0xffffffffu, gl, j);
+                }
+                tmem_st32(taddr + ch * 32, an);
+                if (ch >= 2) {                                           // the buffer's previous store must have read it
+                    if (lane == 0) tma_store_wait_read<1>();
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int v = 0; v < 4; ++v)
+                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(on)[v];
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, c0, lrow, b); tma_store_commit(); }
+            }
+            // ---- second half, after the last MMA: zw = acc + bw, u = partial + gelu(zw), LayerNorm sums
+            mbar_wait(&tmem_full_bar[1], 0);
+            tc_fence_after();
+#pragma unroll 1
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+                float pa[32], aw[32];
+                tmem_ld32(taddr + ch * 32, pa);
+                tmem_ld32(taddr + kC + ch * 32, aw);
+                const int c0 = ch * 32;
+                const float bwl = __ldg(p.bw + c0 + lane);
+                __align__(16) bf16 ow[32], ou[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
                     const bf16 zw = __float2bfloat16_rn(aw[j] + __shfl_sync(0xffffffffu, bwl, j));
-                    on[j] = zn; ow[j] = zw;
-                    float v = __bfloat162float(xb[j]) + gelu_fast(__bfloat162float(zn));
-                    v += gelu_fast(__bfloat162float(zw));
-                    v += __shfl_sync(0xffffffffu, gl, j);
-                    const bf16 ub = __float2bfloat16_rn(v);
+                    ow[j] = zw;
+                    const bf16 ub = __float2bfloat16_rn(pa[j] + gelu_fast(__bfloat162float(zw)));
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;
                 }
+                if (lane == 0) tma_store_wait_read<0>();                 // one pair of staging tiles: the previous stores have read them
+                __syncwarp();
 #pragma unroll
                 for (int v = 0; v < 4; ++v) {
                     const int off = lane * 64 + ((v ^ sw) * 16);
-                    *reinterpret_cast<uint4*>(sbuf + off) = reinterpret_cast<const uint4*>(on)[v];
-                    *reinterpret_cast<uint4*>(sbuf + 2048 + off) = reinterpret_cast<const uint4*>(ow)[v];
-                    *reinterpret_cast<uint4*>(sbuf + 4096 + off) = reinterpret_cast<const uint4*>(ou)[v];
+                    *reinterpret_cast<uint4*>(stage + off) = reinterpret_cast<const uint4*>(ow)[v];
+                    *reinterpret_cast<uint4*>(stage + 2048 + off) = reinterpret_cast<const uint4*>(ou)[v];
                 }
-            } else {
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_3d(&mapS1, stage, c0, lrow, b);
+                    tma_store_3d(&mapS2, stage + 2048, c0, lrow, b);
+                    tma_store_commit();
+                }
+            }
+        } else {
+            mbar_wait(&tmem_full_bar[1], 0);
+            e1 = clock64();
+            tc_fence_after();
+#pragma unroll 1
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+                float an[32], aw[32];
+                tmem_ld32(taddr + ch * 32, an);
+                tmem_ld32(taddr + kC + ch * 32, aw);
+                const int c0 = ch * 32;
+                uint8_t* sbuf = stage + (ch & 1) * (3 * 2048);
+                if (ch >= 2) {                                           // the buffer's previous store must have read it
+                    if (lane == 0) tma_store_wait_read<1>();
+                    __syncwarp();
+                }
                 uint4 dv[4];
 #pragma unroll
                 for (int v = 0; v < 4; ++v) dv[v] = *reinterpret_cast<const uint4*>(p.du + grow + c0 + v * 8);
@@ -229,17 +283,9 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
                     *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
-            }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-                const int lrow = l0 + tile * 128 + q * 32;
-                tma_store_3d(&mapS0, sbuf, c0, lrow, b);
-                if (kFwd) {
-                    tma_store_3d(&mapS1, sbuf + 2048, c0, lrow, b);
-                    tma_store_3d(&mapS2, sbuf + 4096, c0, lrow, b);
-                }
-                tma_store_commit();
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, c0, lrow, b); tma_store_commit(); }
             }
         }
         if (lane == 0) tma_store_wait<0>();
@@ -298,7 +344,7 @@ int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv
     if ((rc = w_map(&mB0, w0, p.ksize))) return rc;
     if ((rc = w_map(&mB1, w1, p.ksize))) return rc;
     const size_t a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
-    const size_t smem = 2 * a_buf + (size_t)kStages * kBTile + 1024 + 256;
+    const size_t smem = 2 * a_buf + (size_t)kStages * kBTile + (kFwd ? 8 * 3 * 2048 : 0) + 1024 + 256;
     PB_REQUIRE(smem <= 232448, PB_ERR_UNSUPPORTED, "conv2: %zu bytes of shared memory needed", smem);
     PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     PB_CUDA(pb_launch_pdl(tc_conv2_kernel<kFwd, kStages>, dim3(B * (L / kRows)), dim3(kThreads), smem, st, mA0m, mA0t, mA1m, mA1t,
@@ -316,7 +362,7 @@ bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil) {
     if ((2 * half) % 8 != 0 || (2 * half * dil) % 8 != 0) return false;     // halo tails are whole 8-row swizzle groups
     const size_t a0 = (size_t)(kRows + 2 * half) * 128, a1 = (size_t)(kRows + 2 * half * dil) * 128;
     const size_t am = a0 > a1 ? a0 : a1;
-    return 2 * am + 9 * kBTile + 2048 <= 232448 && 2 * half * dil <= 256;
+    return 2 * am + 9 * kBTile + 2048 <= 232448 && 2 * am + 6 * kBTile + 8 * 3 * 2048 + 2048 <= 232448 && 2 * half * dil <= 256;
 }
 
 int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
@@ -325,7 +371,7 @@ int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* 
     p.x = (const bf16*)x; p.bn = bn; p.bw = bw; p.g2l = g2l;
     p.zn = (bf16*)zn; p.zw = (bf16*)zw; p.u = (bf16*)u; p.stats = stats;
     p.L = L; p.ksize = ksize; p.dil = dil; p.base_offset_mode = bo_mode;
-    return launch2<true, 9>(x, x, wn, ww, p, B, L, st);
+    return launch2<true, 6>(x, x, wn, ww, p, B, L, st);      // 6-stage ring + 48 KB of epilogue staging
 }
 
 int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
