@@ -30,6 +30,11 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
 int pb_tc_ln_apply(const void* u, const double* stats, const float* gamma, const float* beta, void* h, int B, int L, int C,
                    float eps, cudaStream_t st);
 
+// persistent pooling GEMMs (tc_pool.cu): C = 128, G <= 512
+bool pb_tc_pool_ok(int B, int L, int C, int G);
+int pb_tc_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int G, cudaStream_t st);
+int pb_tc_pool_dz(const void* h, const void* wvT, const float* dpool, void* dzv, int B, int L, int G, cudaStream_t st);
+
 bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil);
 int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
                     void* zw, void* u, double* stats, int B, int L, int ksize, int dil, int bo_mode, cudaStream_t st);

@@ -130,6 +130,23 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const float (&v)[32]) 
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// transpose-reduce: on return lane i holds the sum over the warp's 32 lanes of v[i]
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            if (j < n / 2) {
+                const float send = up ? v[j] : v[j + n / 2];
+                const float keep = up ? v[j + n / 2] : v[j];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+    }
+    return v[0];
+}
+
 // ---------------------------------------------------------------------------------------------
 // descriptors
 // ---------------------------------------------------------------------------------------------

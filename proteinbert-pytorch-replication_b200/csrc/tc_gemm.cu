@@ -37,23 +37,6 @@ struct GemmEpi {
     int base_in_smem;              // LINEAR_FWD with K == N == 128: the residual h tile is the A operand still in the ring
 };
 
-// transpose-reduce: on return lane i holds the sum over the warp's 32 lanes of v[i]
-__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
-#pragma unroll
-    for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
-        const bool up = (lane & off) != 0;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            if (j < n / 2) {
-                const float send = up ? v[j] : v[j + n / 2];
-                const float keep = up ? v[j + n / 2] : v[j];
-                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-            }
-        }
-    }
-    return v[0];
-}
-
 // The two pooling GEMMs (K = C = 128: two 64-wide chunks) are bound by their GELU epilogues, i.e. by how many
 // epilogue warps an SM holds: they take a two-stage ring so that three CTAs fit per SM.
 template <int EPI> struct GemmCfg {
@@ -524,6 +507,7 @@ int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const
 int pb_tc_attn_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int C, int G, cudaStream_t st) {
     GemmEpi ep{};
     ep.ldn = G; ep.L = L; ep.pool = pool;
+    if (pb_tc_pool_ok(B, L, C, G)) return pb_tc_pool_fwd(h, wvT, pool, B, L, G, st);      // persistent kernel, weights resident
     return launch_gemm<EPI_POOL_FWD>(h, wvT, ep, B * L, G, C, st, "tc_attn_pool_fwd");
 }
 
@@ -531,7 +515,8 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
                         void* dh_out, float* dWvT, int head_dv, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st) {
     GemmEpi e1{};
     e1.ldn = G; e1.L = L; e1.dpool = dpool; e1.out0 = (bf16*)dzv;
-    int rc = launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
+    int rc = pb_tc_pool_ok(B, L, C, G) ? pb_tc_pool_dz(h, wvT, dpool, dzv, B, L, G, st)
+                                       : launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
     if (rc) return rc;
     GemmEpi e2{};
     e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
