@@ -5,8 +5,8 @@
 // pipe in their epilogues (profiles/r01_tc_gemm_ncu.md).  With one tile per CTA the epilogue warps idle while the next
 // CTA sets up (barriers, TMEM allocation, TMA round trip, MMAs).  Here the whole weight matrix Wv^T [G x 128] stays in
 // shared memory (128 KB), the CTA walks (row tile, column tile) units, the MMA warp runs up to four units ahead into
-// four TMEM accumulators (all 512 columns) and two groups of four epilogue warps drain alternate accumulators, so the
-// FP32 pipe never waits for a tile.
+// four TMEM accumulators (all 512 columns) and four groups of four epilogue warps drain one accumulator each, so the
+// FP32 pipe never waits for a tile and every scheduler has four epilogue warps to pick from.
 #include "tc_common.cuh"
 #include "tc_api.cuh"
 
@@ -15,9 +15,10 @@ namespace {
 constexpr int kTile = 128 * 64 * 2;                  // one 128-row x 64-k bf16 tile: 16 KB
 constexpr int kAStages = 2;                          // A ring: stage = one 128 x 128 activation tile (two k-chunks)
 constexpr int kMaxTilesN = 4;                        // resident weights: 4 column tiles x 2 k-chunks x 16 KB = 128 KB
-constexpr int kStageArea = 8 * 2 * 2048;             // POOL_DZ: two 2 KB staging tiles per epilogue warp; POOL_FWD: column sums
+constexpr int kGroups = 4;                           // epilogue groups of four warps, one per TMEM accumulator
+constexpr int kStageArea = kGroups * 4 * 2048;       // POOL_DZ: one 2 KB staging tile per epilogue warp; POOL_FWD: column sums
 constexpr int kSmemBytes = kMaxTilesN * 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;
-constexpr int kThreads = 320;                        // warp 0 TMA, warp 1 MMA + TMEM, warps 2..9 epilogue (two groups)
+constexpr int kThreads = 64 + kGroups * 128;         // warp 0 TMA, warp 1 MMA + TMEM, then the epilogue groups
 
 enum { POOL_FWD = 0, POOL_DZ = 1 };
 
@@ -99,15 +100,16 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             }
         }
     } else {
-        // ===== epilogue: warps 2..9 in two groups of four; group g drains units g, g + 2, ...; TMEM lane quarter = warp % 4 =====
+        // ===== epilogue: groups of four warps; group g drains units g, g + kGroups, ... (always accumulator g);
+        //       TMEM lane quarter = warp % 4.  Four groups = four warps per scheduler: the epilogue is FP32-issue bound =====
         const int grp = (warp - 2) >> 2, q = warp & 3;
         const int gt = ((warp - 2) & 3) * 32 + lane;                 // thread index inside the group
         float* colsum = reinterpret_cast<float*>(stage_area) + grp * (4 * 128);      // POOL_FWD: [4 lane quarters][128 columns]
-        uint8_t* stage = stage_area + (warp - 2) * (2 * 2048);                       // POOL_DZ: two staging tiles per warp
+        uint8_t* stage = stage_area + (warp - 2) * 2048;                             // POOL_DZ: one staging tile per warp
         const int sw = (lane >> 1) & 3;
         int n_staged = 0;
 #pragma unroll 1
-        for (int i = grp; i < n_mine; i += 2) {
+        for (int i = grp; i < n_mine; i += kGroups) {
             const int a = i & 3;
             const int u = (int)blockIdx.x + i * (int)gridDim.x;
             const int m = u / p.tiles_n, n = u % p.tiles_n;
@@ -134,9 +136,9 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     __align__(16) bf16 od[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * gelu_grad_fast(acc[j]));
-                    uint8_t* sbuf = stage + (n_staged & 1) * 2048;
-                    if (n_staged >= 2) {                             // the buffer's previous store must have read it
-                        if (lane == 0) tma_store_wait_read<1>();
+                    uint8_t* sbuf = stage;
+                    if (n_staged >= 1) {                             // the buffer's previous store must have read it
+                        if (lane == 0) tma_store_wait_read<0>();
                         __syncwarp();
                     }
                     ++n_staged;
