@@ -139,32 +139,42 @@ tc_conv_wgrad3_kernel(const __grid_constant__ CUtensorMap mapP0, const __grid_co
     }
 }
 
-// out[src][co, ci, t] = sum over splits.  One CTA per (co, src): 32 float4 lanes over ci x 8 tap lanes read the
-// partial tiles with every load independent, the [ci][t] row is assembled in shared memory and leaves as one
-// contiguous run of 128 * ksize floats.
-__global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out0,
+// out[src][co, ci, t] = sum over splits.  One CTA per (co, src): 32 float4 lanes over ci x one thread row per tap read the
+// partial tiles, twelve independent 16-byte loads in flight per thread (the kernel is a chain of L2 round trips); the
+// [ci][t] row is assembled in shared memory and leaves as one contiguous run of 128 * ksize floats.
+__global__ void __launch_bounds__(512) conv_wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ out0,
                                                                 float* __restrict__ out1, int splits, int ksize) {
     extern __shared__ float row[];                    // [128][ksize]
     pdl_wait();
     const int m = blockIdx.x, src = blockIdx.y;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const size_t total = (size_t)gridDim.y * ksize * kTile;
-    for (int t = ty; t < ksize; t += 8) {
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, nty = blockDim.x >> 5;
+    const size_t total4 = (size_t)gridDim.y * ksize * kTile / 4;
+    for (int t = ty; t < ksize; t += nty) {
         const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)(src * ksize + t) * 128 + m) * 128) + tx;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-        for (int k = 0; k < splits; ++k) {
-            const float4 v = p[(size_t)k * (total / 4)];
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+        int k = 0;
+        for (; k + 12 <= splits; k += 12) {
+            float4 v[12];
+#pragma unroll
+            for (int i = 0; i < 12; ++i) v[i] = p[(size_t)(k + i) * total4];
+#pragma unroll
+            for (int i = 0; i < 12; i += 2) {
+                a.x += v[i].x; a.y += v[i].y; a.z += v[i].z; a.w += v[i].w;
+                c.x += v[i + 1].x; c.y += v[i + 1].y; c.z += v[i + 1].z; c.w += v[i + 1].w;
+            }
+        }
+        for (; k < splits; ++k) {
+            const float4 v = p[(size_t)k * total4];
             a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
         }
-        row[(tx * 4 + 0) * ksize + t] = a.x;
-        row[(tx * 4 + 1) * ksize + t] = a.y;
-        row[(tx * 4 + 2) * ksize + t] = a.z;
-        row[(tx * 4 + 3) * ksize + t] = a.w;
+        row[(tx * 4 + 0) * ksize + t] = a.x + c.x;
+        row[(tx * 4 + 1) * ksize + t] = a.y + c.y;
+        row[(tx * 4 + 2) * ksize + t] = a.z + c.z;
+        row[(tx * 4 + 3) * ksize + t] = a.w + c.w;
     }
     __syncthreads();
     float* dst = (src == 0 ? out0 : out1) + (size_t)m * 128 * ksize;
-    for (int i = threadIdx.x; i < 128 * ksize; i += 256) dst[i] = row[i];
+    for (int i = threadIdx.x; i < 128 * ksize; i += blockDim.x) dst[i] = row[i];
 }
 
 }  // namespace
@@ -205,7 +215,8 @@ int pb_tc_conv_wgrad3(const void* dzn, const void* dzw, const void* x, float* dW
     wp.chunks_per_split = (wp.chunks_total + splits - 1) / splits;
     splits = (wp.chunks_total + wp.chunks_per_split - 1) / wp.chunks_per_split;
     PB_CUDA(pb_launch_pdl(tc_conv_wgrad3_kernel, dim3(groups, 2, splits), dim3(kThreads), kSmemBytes, st, mP0, mP1, mX0, mX1, wp));
-    PB_CUDA(pb_launch_pdl(conv_wgrad_reduce_kernel, dim3(128, 2), dim3(256), (size_t)128 * ksize * sizeof(float), st, (const float*)wp.ws,
+    const int red_threads = 32 * (ksize < 16 ? ksize : 16);                 // one thread row per tap
+    PB_CUDA(pb_launch_pdl(conv_wgrad_reduce_kernel, dim3(128, 2), dim3(red_threads), (size_t)128 * ksize * sizeof(float), st, (const float*)wp.ws,
                           dWn, dWw, splits, ksize));
     pb_count_launch(2);
     return pb_check_launch("tc_conv_wgrad3");
