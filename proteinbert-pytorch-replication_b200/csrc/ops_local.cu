@@ -332,19 +332,19 @@ template <> struct V8<bf16> {
 };
 __device__ __forceinline__ void ldf8(const float* p, float (&v)[8]) { V8<float>::ld(p, v); }
 
-// per-sample sums s1 = sum dy*gamma, s2 = sum dy*gamma*xhat.  grid = (chunks, B)
+// per-sample RAW sums s1 = sum dy*gamma, t2 = sum dy*gamma*u.  grid = (chunks, B).  The consumer turns t2 into
+// sum dy*gamma*xhat = rstd*(t2 - mean*s1) (ln_m2_from_raw), so this pass needs neither the statistics nor any double
+// arithmetic before its loads -- it is one round trip to memory plus a reduction.
 template <typename T>
-__global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __restrict__ u, const double* __restrict__ stats,
-                                       const float* __restrict__ gamma, double* __restrict__ sums, long long n, float eps) {
+__global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __restrict__ u, const float* __restrict__ gamma,
+                                       double* __restrict__ sums, long long n) {
     __shared__ double red[32];
     pdl_wait();
     const int b = blockIdx.y;
-    const LnStat st = ln_stat(stats, b, (double)n, eps);
     const long long nv = n / 8;
     float s1 = 0.f, s2 = 0.f;
     const long long step = (long long)gridDim.x * blockDim.x;
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    // two vectors per trip, all six loads issued before the arithmetic: the kernel is a chain of memory round trips
     for (; i + step < nv; i += 2 * step) {
         float d0[8], x0[8], g0[8], d1[8], x1[8], g1[8];
         V8<T>::ld(dy + (size_t)b * n + i * 8, d0);
@@ -357,7 +357,7 @@ __global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __rest
         for (int j = 0; j < 8; ++j) {
             const float a = d0[j] * g0[j], c = d1[j] * g1[j];
             s1 += a + c;
-            s2 += a * ((x0[j] - st.mean) * st.rstd) + c * ((x1[j] - st.mean) * st.rstd);
+            s2 += a * x0[j] + c * x1[j];
         }
     }
     for (; i < nv; i += step) {
@@ -369,11 +369,18 @@ __global__ void ln_bwd_sums_vec_kernel(const T* __restrict__ dy, const T* __rest
         for (int j = 0; j < 8; ++j) {
             const float a = d[j] * g[j];
             s1 += a;
-            s2 += a * ((x[j] - st.mean) * st.rstd);
+            s2 += a * x[j];
         }
     }
     const double d1 = block_sum((double)s1, red), d2 = block_sum((double)s2, red);
     if (threadIdx.x == 0) { atomicAdd(&sums[2 * b], d1); atomicAdd(&sums[2 * b + 1], d2); }
+}
+// (sum dy*gamma*xhat) / n from the raw sums, in double: xhat = (u - mean) * rstd
+__device__ __forceinline__ float ln_m2_from_raw(const double* stats, int b, double n, float eps, double s1, double t2) {
+    const double mean = stats[2 * b] / n;
+    double var = stats[2 * b + 1] / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    return (float)((t2 - mean * s1) * rsqrt(var + (double)eps) / n);
 }
 
 // du = rstd*(dy*gamma - m1 - xhat*m2); dgamma/dbeta accumulated over this CTA's group of samples.
@@ -391,7 +398,7 @@ __global__ void ln_bwd_apply_vec_kernel(const T* __restrict__ dy, const T* __res
         const LnStat st = ln_stat(stats, b0 + k, (double)n, eps);
         prm[4 * k] = st.mean; prm[4 * k + 1] = st.rstd;
         prm[4 * k + 2] = (float)(sums[2 * (b0 + k)] / (double)n);
-        prm[4 * k + 3] = (float)(sums[2 * (b0 + k) + 1] / (double)n);
+        prm[4 * k + 3] = ln_m2_from_raw(stats, b0 + k, (double)n, eps, sums[2 * (b0 + k)], sums[2 * (b0 + k) + 1]);
     }
     __syncthreads();
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -515,7 +522,7 @@ ln_bwd_apply_gelu_kernel(const T* __restrict__ dy, const T* __restrict__ u, cons
         const LnStat st = ln_stat(stats, b0 + k, (double)n, eps);
         prm[4 * k] = st.mean; prm[4 * k + 1] = st.rstd;
         prm[4 * k + 2] = (float)(sums[2 * (b0 + k)] / (double)n);
-        prm[4 * k + 3] = (float)(sums[2 * (b0 + k) + 1] / (double)n);
+        prm[4 * k + 3] = ln_m2_from_raw(stats, b0 + k, (double)n, eps, sums[2 * (b0 + k)], sums[2 * (b0 + k) + 1]);
     }
     __syncthreads();
     const int vpr = C / 8;
@@ -679,7 +686,7 @@ int pb_ln_joint_bwd(const void* dy, const void* u, const double* stats, const fl
         dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
         dim3 g2((unsigned)ceil_div(nv, 256), groups);
         DISPATCH_DT(dt, {
-            PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, stats, gamma, sums, n, eps));
+            PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, gamma, sums, n));
             PB_CUDA(pb_launch_pdl(ln_bwd_apply_vec_kernel<T>, g2, dim3(256), 4 * per_group * sizeof(float), st, (const T*)dy, (const T*)u,
                                   stats, gamma, (const double*)sums, (T*)du, dgamma, dbeta, B, n, eps, per_group, groups > 1 ? 1 : 0));
         });
@@ -721,7 +728,7 @@ int pb_ln_joint_bwd_gelu(const void* dy, const void* u, const double* stats, con
     dim3 g1((unsigned)max(1, min(ceil_div(nv, 256), 16)), B);
     dim3 g2((unsigned)ceil_div(nv, 256), groups);
     DISPATCH_DT(dt, {
-        PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, stats, gamma, sums, n, eps));
+        PB_CUDA(pb_launch_pdl(ln_bwd_sums_vec_kernel<T>, g1, dim3(256), 0, st, (const T*)dy, (const T*)u, gamma, sums, n));
         if (z1 != nullptr) {
             PB_CUDA(pb_launch_pdl(ln_bwd_apply_gelu_kernel<T, true>, g2, dim3(256), smem, st, (const T*)dy, (const T*)u, stats, gamma,
                                   (const double*)sums, (const T*)z0, (const T*)z1, (T*)du, (T*)dz0, (T*)dz1, dgamma, dbeta, dsample, db0,
