@@ -221,49 +221,76 @@ __global__ void token_head_bwd_kernel(const float* __restrict__ dP, const float*
 }
 
 // ---- token head, tensor-core path: the GEMMs run in tc_gemm.cu; these are the batch-axis softmax around them ----
-// logits32 [B*L, 32] fp32 (columns >= V unused) -> p_local [B, L, V]; one thread per (l, v), walking the batch
-__global__ void softmax_batch_kernel(const float* __restrict__ logits32, const float* __restrict__ bo, float* __restrict__ p_local,
-                                     int B, int L, int V) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= L * 32) return;
-    const int l = i >> 5, v = i & 31;
-    if (v >= V) return;
-    const float bias = bo[v];
+// logits32 [B*L, 32] fp32 (columns >= V unused) -> p_local [B, L, V].  One CTA per position l: 32 vocabulary lanes x 8
+// batch lanes, each thread holds up to 8 samples of its (l, v) column in registers (all loads in flight at once); the
+// batch-axis max / sum are combined through shared memory.  B <= 64 per register budget; larger batches loop.
+constexpr int kTokBL = 8;            // batch lanes (warps) per CTA
+constexpr int kTokPer = 8;           // samples per thread and trip
+__global__ void __launch_bounds__(32 * kTokBL) softmax_batch_kernel(const float* __restrict__ logits32, const float* __restrict__ bo,
+                                                                   float* __restrict__ p_local, int B, int L, int V) {
+    __shared__ float sm_m[kTokBL][32], sm_s[kTokBL][32];
+    const int l = blockIdx.x, v = threadIdx.x & 31, bl = threadIdx.x >> 5;
+    const float bias = v < V ? bo[v] : 0.f;
     float mx = -INFINITY, s = 0.f;
-#pragma unroll 8
-    for (int b = 0; b < B; ++b) {                       // online max / sum
-        const float x = logits32[((size_t)b * L + l) * 32 + v] + bias;
-        const float m2 = fmaxf(mx, x);
-        s = s * expf(mx - m2) + expf(x - m2);
-        mx = m2;
+    for (int b0 = bl; b0 < B; b0 += kTokBL * kTokPer) {          // online max / sum over this thread's samples
+        float x[kTokPer];
+#pragma unroll
+        for (int i = 0; i < kTokPer; ++i) {
+            const int b = b0 + i * kTokBL;
+            x[i] = (b < B && v < V) ? logits32[((size_t)b * L + l) * 32 + v] + bias : -INFINITY;
+        }
+        float m2 = mx;
+#pragma unroll
+        for (int i = 0; i < kTokPer; ++i) m2 = fmaxf(m2, x[i]);
+        if (m2 > -INFINITY) {
+            s *= expf(mx - m2);
+#pragma unroll
+            for (int i = 0; i < kTokPer; ++i) s += expf(x[i] - m2);
+            mx = m2;
+        }
     }
-    const float inv = 1.0f / s;
-#pragma unroll 8
-    for (int b = 0; b < B; ++b) {
+    sm_m[bl][v] = mx; sm_s[bl][v] = s;
+    __syncthreads();
+    float M = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < kTokBL; ++i) M = fmaxf(M, sm_m[i][v]);
+    float S = 0.f;
+#pragma unroll
+    for (int i = 0; i < kTokBL; ++i) S += sm_m[i][v] > -INFINITY ? sm_s[i][v] * expf(sm_m[i][v] - M) : 0.f;
+    if (v >= V) return;
+    const float inv = 1.0f / S;
+    for (int b = bl; b < B; b += kTokBL) {
         const float x = logits32[((size_t)b * L + l) * 32 + v] + bias;
-        p_local[((size_t)b * L + l) * V + v] = expf(x - mx) * inv;
+        p_local[((size_t)b * L + l) * V + v] = expf(x - M) * inv;
     }
 }
 
-// dlogit[b,l,v] = s * p * (dP - sum_b' p dP) as bf16 into a [B*L, 128] buffer (columns >= V zero); dbo[v] += sum
-__global__ void token_dlogit_kernel(const float* __restrict__ dP, const float* __restrict__ p_local, const double* __restrict__ gscale,
-                                    bf16* __restrict__ dlogit_pad, float* __restrict__ dbo, int B, int L, int V) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= L * 32) return;
-    const int l = i >> 5, v = i & 31;
+// dlogit[b,l,v] = s * p * (dP - sum_b' p dP) as bf16 into a [B*L, 128] buffer (columns >= V zero); dbo[v] += sum.
+// Same layout: one CTA per position, 32 vocabulary lanes x 8 batch lanes.
+__global__ void __launch_bounds__(32 * kTokBL) token_dlogit_kernel(const float* __restrict__ dP, const float* __restrict__ p_local,
+                                                                  const double* __restrict__ gscale, bf16* __restrict__ dlogit_pad,
+                                                                  float* __restrict__ dbo, int B, int L, int V) {
+    __shared__ float sm_d[kTokBL][32];
+    const int l = blockIdx.x, v = threadIdx.x & 31, bl = threadIdx.x >> 5;
     const float gs = gscale ? (float)(*gscale) : 1.0f;
     float dot = 0.f;
     if (v < V) {
 #pragma unroll 8
-        for (int b = 0; b < B; ++b) {
+        for (int b = bl; b < B; b += kTokBL) {
             const size_t gi = ((size_t)b * L + l) * V + v;
             dot += p_local[gi] * dP[gi];
         }
     }
+    sm_d[bl][v] = dot;
+    __syncthreads();
+    dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < kTokBL; ++i) dot += sm_d[i][v];
+    __syncthreads();
     float sb = 0.f;
     const bf16 zero = __float2bfloat16_rn(0.f);
 #pragma unroll 4
-    for (int b = 0; b < B; ++b) {
+    for (int b = bl; b < B; b += kTokBL) {
         float d = 0.f;
         if (v < V) {
             const size_t gi = ((size_t)b * L + l) * V + v;
@@ -275,7 +302,14 @@ __global__ void token_dlogit_kernel(const float* __restrict__ dP, const float* _
         row[v + 32] = zero; row[v + 64] = zero; row[v + 96] = zero;
         sb += __bfloat162float(db_);
     }
-    if (v < V) atomicAdd(&dbo[v], sb);
+    sm_d[bl][v] = sb;
+    __syncthreads();
+    if (bl == 0 && v < V) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < kTokBL; ++i) t += sm_d[i][v];
+        atomicAdd(&dbo[v], t);
+    }
 }
 
 // ---- loss ---------------------------------------------------------------------------------------
@@ -290,21 +324,42 @@ __global__ void loss_kernel(const float* __restrict__ p_local, const float* __re
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const double inv_tok = 1.0 / (double)n_tok, inv_ann = 1.0 / (double)n_ann;
-    for (long long r = tid; r < n_tok; r += stride) {
-        const float* pr = p_local + (size_t)r * V;
-        float mx = -INFINITY;
-        for (int v = 0; v < V; ++v) mx = fmaxf(mx, pr[v]);
-        float s = 0.f;
-        for (int v = 0; v < V; ++v) s += expf(pr[v] - mx);
-        const float lse = mx + logf(s);
-        const int64_t y = y_local[r];
-        const double w = w_local[r];
-        const bool ok = (y >= 0 && y < V);
-        if (ok) acc_l += (double)(lse - pr[y]) * w;
-        if (dP_local) {
-            const float wf = ok ? (float)(w * inv_tok) : 0.f;
-            float* dr = dP_local + (size_t)r * V;
-            for (int v = 0; v < V; ++v) dr[v] = wf * (expf(pr[v] - lse) - (v == (int)y ? 1.f : 0.f));
+    if (V <= 32) {
+        // one warp per token row, lane = vocabulary entry: coalesced row reads/writes, max and sum by shuffles, one expf
+        const int lane = threadIdx.x & 31;
+        const long long nwarp = stride >> 5;
+        for (long long r = tid >> 5; r < n_tok; r += nwarp) {
+            const float pv = lane < V ? p_local[(size_t)r * V + lane] : -INFINITY;
+            const float mx = warp_max(pv);
+            const float e = lane < V ? expf(pv - mx) : 0.f;
+            const float ssum = warp_sum(e);
+            const float lse = mx + logf(ssum);
+            const int64_t y = y_local[r];
+            const double w = w_local[r];
+            const bool ok = (y >= 0 && y < V);
+            if (ok && lane == (int)y) acc_l += (double)(lse - pv) * w;
+            if (dP_local && lane < V) {
+                const float wf = ok ? (float)(w * inv_tok) : 0.f;
+                dP_local[(size_t)r * V + lane] = wf * (expf(pv - lse) - (lane == (int)y ? 1.f : 0.f));
+            }
+        }
+    } else {
+        for (long long r = tid; r < n_tok; r += stride) {
+            const float* pr = p_local + (size_t)r * V;
+            float mx = -INFINITY;
+            for (int v = 0; v < V; ++v) mx = fmaxf(mx, pr[v]);
+            float s = 0.f;
+            for (int v = 0; v < V; ++v) s += expf(pr[v] - mx);
+            const float lse = mx + logf(s);
+            const int64_t y = y_local[r];
+            const double w = w_local[r];
+            const bool ok = (y >= 0 && y < V);
+            if (ok) acc_l += (double)(lse - pr[y]) * w;
+            if (dP_local) {
+                const float wf = ok ? (float)(w * inv_tok) : 0.f;
+                float* dr = dP_local + (size_t)r * V;
+                for (int v = 0; v < V; ++v) dr[v] = wf * (expf(pr[v] - lse) - (v == (int)y ? 1.f : 0.f));
+            }
         }
     }
     for (long long i = tid; i < n_ann; i += stride) {
@@ -411,8 +466,9 @@ int pb_pretrain_loss(const float* p_local, const float* p_global, const int64_t*
     cudaStream_t st = (cudaStream_t)stream;
     PB_CUDA(cudaMemsetAsync(loss, 0, 3 * sizeof(double), st));
     const long long n_tok = (long long)B * L, n_ann = (long long)B * A;
-    const int grid = (int)min((long long)ceil_div(n_ann > n_tok ? n_ann : n_tok, 256), 148LL * 8);
-    loss_kernel<<<grid, 256, 0, st>>>(p_local, p_global, y_local, y_global, w_local, w_global, loss, dP_local, dP_global, n_tok,
+    // one resident wave of fat CTAs: every CTA ends with three same-address double atomics, so there are few of them
+    const int grid = (int)min((long long)ceil_div(n_ann > n_tok ? n_ann : n_tok, 512), 148LL * 2);
+    loss_kernel<<<grid, 512, 0, st>>>(p_local, p_global, y_local, y_global, w_local, w_global, loss, dP_local, dP_global, n_tok,
                                       V, n_ann);
     pb_count_launch(1);
     return pb_check_launch("pb_pretrain_loss");
@@ -437,7 +493,7 @@ int pb_token_head_fwd_tc(const void* h, const void* wo_pad, const float* bo, flo
     cudaStream_t st = (cudaStream_t)stream;
     int rc = pb_tc_token_logits(h, wo_pad, logits_ws, B, L, C, st);
     if (rc) return rc;
-    softmax_batch_kernel<<<ceil_div((long)L * 32, 128), 128, 0, st>>>(logits_ws, bo, p_local, B, L, V);
+    softmax_batch_kernel<<<L, 32 * kTokBL, 0, st>>>(logits_ws, bo, p_local, B, L, V);
     pb_count_launch(1);
     return pb_check_launch("pb_token_head_fwd_tc");
 }
@@ -447,7 +503,7 @@ int pb_token_head_bwd_tc(const float* dP, const float* p_local, const void* h, c
                          size_t ws_bytes, void* stream) {
     PB_REQUIRE(pb_tc_token_ok(B, L, C, V), PB_ERR_UNSUPPORTED, "token_head_bwd_tc: shape not covered");
     cudaStream_t st = (cudaStream_t)stream;
-    token_dlogit_kernel<<<ceil_div((long)L * 32, 128), 128, 0, st>>>(dP, p_local, grad_scale, (bf16*)dlogit_ws, dbo, B, L, V);
+    token_dlogit_kernel<<<L, 32 * kTokBL, 0, st>>>(dP, p_local, grad_scale, (bf16*)dlogit_ws, dbo, B, L, V);
     pb_count_launch(1);
     int rc = pb_check_launch("pb_token_head_bwd_tc(dlogit)");
     if (rc) return rc;
