@@ -257,8 +257,37 @@ def main():
     torch.cuda.synchronize()
     ops.PROFILE = None
     conv_ms = sorted(a.elapsed_time(b) for a, b in prof)
-    conv_ms_mean = sum(conv_ms) / len(conv_ms)
+    conv_ms_eager = sum(conv_ms) / len(conv_ms)      # includes the host time between the event and the launch (idle GPU)
     L, C = CFG["sequences_length"], CFG["local_dim"]
+    # the same entry point on config-2 tensors with block 0's weights, launched back to back so that the stream never
+    # drains: the event pair then brackets kernel time only
+    blk0 = model.proteinBERT_blocks[0]
+    adt = torch.bfloat16 if args.precision == "bf16" else torch.float32
+    dtc = 1 if args.precision == "bf16" else 0
+    xin = torch.randn(B, L, C, device=dev).to(adt)
+    packs = [ops.conv_pack(m[0].weight.detach(), dtc) for m in (blk0.local_narrow_conv_layer, blk0.local_wide_conv_layer)]
+    bn_, bw_ = blk0.local_narrow_conv_layer[0].bias.detach(), blk0.local_wide_conv_layer[0].bias.detach()
+    g2l_ = torch.randn(B, C, device=dev)
+    zn_, zw_, u_ = torch.empty_like(xin), torch.empty_like(xin), torch.empty_like(xin)
+    st_ = torch.zeros(B, 2, dtype=torch.float64, device=dev)
+    cs = torch.cuda.current_stream().cuda_stream
+
+    def conv_once():
+        ops._call("pb_conv_pair_fwd", xin.data_ptr(), packs[0][0].data_ptr(), packs[1][0].data_ptr(), bn_.data_ptr(), bw_.data_ptr(),
+                  g2l_.data_ptr(), zn_.data_ptr(), zw_.data_ptr(), u_.data_ptr(), st_.data_ptr(), B, L, C, blk0.conv_kernel_size,
+                  blk0.wide_conv_dilation, dtc, cs)
+
+    for _ in range(5):
+        conv_once()
+    n_conv = 60
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    c0.record()
+    for _ in range(n_conv):
+        conv_once()
+    c1.record()
+    torch.cuda.synchronize()
+    conv_ms_mean = c0.elapsed_time(c1) / n_conv
     conv_flops = 2 * (2.0 * B * L * C * C * 9)            # two convolutions, one launch (19.33 GF at B=64)
     peaks = load_peaks()
     peak_tf = peaks["bf16_tflops_sustained"]
@@ -270,13 +299,17 @@ def main():
         traffic = t["dram_bytes_read"] + t["dram_bytes_write"]
     roofline = {"kernel": "conv_pair_fwd", "bound": "tensor", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": achieved_tf / peak_tf, "traffic": traffic, "peak_source": f"{peaks['_source']} bf16_tflops_sustained",
-                "us_per_launch": conv_ms_mean * 1e3, "launches_timed": len(conv_ms)}
+                "us_per_launch": conv_ms_mean * 1e3, "launches_timed": n_conv,
+                "timing": "CUDA events around 60 back-to-back launches of pb_conv_pair_fwd on config-2 tensors (block 0 weights)",
+                "us_per_launch_in_eager_step": conv_ms_eager * 1e3}
 
     # ---- e2e: public API from pinned host buffers, H2D of inputs + D2H of the loss inside the timed region ----
     def e2e_step():
         if graph is not None:            # public fast path: H2D into the static buffers, graph replay, D2H of the loss
             Xh, Yh, Wh = dicts(host)
-            return graph(Xh, Yh, Wh).item()
+            # the next batch's H2D (here: the same pinned host tensors again, a full 9.9 MB copy per step) is started on a
+            # side stream while this step computes -- what a data loader with one batch of look-ahead does
+            return graph(Xh, Yh, Wh, prefetch=(Xh, Yh, Wh)).item()
         b = [t.to(dev, non_blocking=True) for t in host]
         Xh, Yh, Wh = dicts(b)
         loss = pb.pretraining_step(model, Xh, Yh, Wh, reducer)

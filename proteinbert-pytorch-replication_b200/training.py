@@ -116,6 +116,7 @@ class GraphedPretrainStep:
         dev = next(model.parameters()).device
         self.model = model
         self.device = dev
+        self._staging = self._copy_stream = self._staged_key = None
         self.static = [t.to(dev).clone() for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])]
         sx, sy, sw = self._dicts()
         distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
@@ -188,12 +189,46 @@ class GraphedPretrainStep:
         s = self.static
         return ({"local": s[0], "global": s[1]}, {"local": s[2], "global": s[3]}, {"local": s[4], "global": s[5]})
 
-    def __call__(self, X, Y, W):
-        src = (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])
-        for dst, t in zip(self.static, src):
-            if t is not dst:
+    @staticmethod
+    def _flat(X, Y, W):
+        return (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])
+
+    def prefetch(self, X, Y, W):
+        """Start the host->device copy of a FUTURE batch on a side stream, into staging buffers, so that it runs while
+        the current step computes (pinned host tensors make it a true async DMA).  The next ``__call__`` with the same
+        tensors picks the staged copy up with a device-to-device copy instead of waiting for PCIe."""
+        src = self._flat(X, Y, W)
+        dev = self.device
+        if self._staging is None:
+            self._staging = [torch.empty_like(t) for t in self.static]
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._staged_done = torch.cuda.Event()
+            self._staging_free = torch.cuda.Event()
+            self._staging_free.record(torch.cuda.current_stream(dev))
+        self._copy_stream.wait_event(self._staging_free)         # the previous staged batch has been moved out
+        with torch.cuda.stream(self._copy_stream):
+            for dst, t in zip(self._staging, src):
                 dst.copy_(t, non_blocking=True)
+            self._staged_done.record(self._copy_stream)
+        self._staged_key = tuple(id(t) for t in src)
+
+    def __call__(self, X, Y, W, prefetch=None):
+        """One step on the batch (X, Y, W).  ``prefetch=(Xn, Yn, Wn)`` starts copying the NEXT batch while this one runs."""
+        src = self._flat(X, Y, W)
+        cur = torch.cuda.current_stream(self.device)
+        if self._staged_key is not None and self._staged_key == tuple(id(t) for t in src):
+            cur.wait_event(self._staged_done)
+            for dst, t in zip(self.static, self._staging):
+                dst.copy_(t, non_blocking=True)
+            self._staging_free.record(cur)
+            self._staged_key = None
+        else:
+            for dst, t in zip(self.static, src):
+                if t is not dst:
+                    dst.copy_(t, non_blocking=True)
         self.graph.replay()
+        if prefetch is not None:
+            self.prefetch(*prefetch)
         if self.split:
             self.bucket_a.gather()
             work = self.bucket_a.all_reduce(async_op=True)       # NCCL on its own stream ...

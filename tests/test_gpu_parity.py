@@ -433,4 +433,17 @@ def test_graphed_step_and_two_stage_backward_match_eager(pb, wide_ref):
         assert abs(float(loss_g) - float(loss_e)) <= 1e-6 * abs(float(loss_e))
         for n, p in model.named_parameters():
             assert rel_fro(p.grad, ref[n]) < 2e-3 or float(ref[n].abs().max()) < 1e-6, (kwargs, n)
+        # host batches with one step of look-ahead: the staged copy of the next batch must be the one the step consumes
+        hostA = [t.cpu().pin_memory() for t in batch]
+        hostB = [t.cpu().pin_memory() for t in batch]
+        hostB[1] = (1.0 - hostB[1]).pin_memory()                    # a different annotation input -> a different loss
+        dA = ({"local": hostA[0], "global": hostA[1]}, {"local": hostA[2], "global": hostA[3]}, {"local": hostA[4], "global": hostA[5]})
+        dB = ({"local": hostB[0], "global": hostB[1]}, {"local": hostB[2], "global": hostB[3]}, {"local": hostB[4], "global": hostB[5]})
+        lA = float(step(*dA, prefetch=dB))
+        lB = float(step(*dB, prefetch=dA))
+        lA2 = float(step(*dA))
+        lB_direct = float(step(*dB))
+        tol = 1e-6 * abs(float(loss_e))                           # float atomics: replays agree to rounding, not bitwise
+        assert abs(lA - float(loss_e)) <= tol and abs(lA2 - lA) <= tol
+        assert abs(lB - lB_direct) <= tol and abs(lB - lA) > 100 * tol
         del step
