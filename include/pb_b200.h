@@ -84,6 +84,21 @@ typedef struct pb_chunk_desc {
 } pb_chunk_desc;
 int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream);
 
+/* ---- a20 / f-2: the optimizer step (utils.py:301 with Adam of dummy_tests.py:127-130), outside the metric's timed
+ * region.  One launch updates every tensor of the table in place: m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2,
+ * p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)  -- torch.optim.Adam's single-tensor formula (weight_decay adds
+ * wd*p to g first; amsgrad/maximize not offered).  `step` is t >= 1; the betas are doubles because torch forms 1 - beta
+ * in double before rounding to float.  Pieces of <= 64k elements fill the GPU.                                       */
+typedef struct pb_adam_desc {
+    float* p;
+    const float* g;
+    float* m;
+    float* v;
+    long long numel;
+} pb_adam_desc;
+int pb_adam_step(const pb_adam_desc* descs_dev, int n, float lr, double beta1, double beta2, float eps, float weight_decay,
+                 long long step, void* stream);
+
 /* ---- a2: token embedding (modules.py:249-253,300; backward = embedding_dense_backward) ------ */
 int pb_embedding_fwd(const int64_t* tok, const float* table, void* out_act, long long n_tok, int C, int V,
                      int dt, void* stream);

@@ -140,6 +140,40 @@ __global__ void flat_copy_kernel(const pb_chunk_desc* __restrict__ chunks, float
 
 extern "C" {
 
+// Adam (torch.optim.Adam defaults of dummy_tests.py:127-130: no amsgrad, no weight decay unless asked) over many tensors in
+// one launch: blockIdx.y walks a device table of <= 64k-element pieces.  Per element: 4 loads, 3 stores of 4 bytes.
+__global__ void __launch_bounds__(256) adam_kernel(const pb_adam_desc* __restrict__ descs, float step_size, float beta1, float beta2,
+                                                   float inv_sqrt_bc2, float eps, float weight_decay, float omb1, float omb2) {
+    const pb_adam_desc d = descs[blockIdx.y];
+    const bool vec = ((((uintptr_t)d.p | (uintptr_t)d.g | (uintptr_t)d.m | (uintptr_t)d.v) & 15) == 0);
+    const long long n4 = vec ? d.numel / 4 : 0;
+    const long long stride = (long long)gridDim.x * blockDim.x, tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    auto upd = [&](float& p, float g, float& m, float& v) {
+        if (weight_decay != 0.f) g = fmaf(weight_decay, p, g);
+        m = fmaf(beta1, m, omb1 * g);              // 1 - beta taken in double on the host, as torch does
+        v = fmaf(beta2, v, omb2 * g * g);
+        p -= step_size * m / (sqrtf(v) * inv_sqrt_bc2 + eps);
+    };
+    for (long long i = tid; i < n4; i += stride) {
+        float4 p = reinterpret_cast<float4*>(d.p)[i], m = reinterpret_cast<float4*>(d.m)[i], v = reinterpret_cast<float4*>(d.v)[i];
+        const float4 g = reinterpret_cast<const float4*>(d.g)[i];
+        upd(p.x, g.x, m.x, v.x); upd(p.y, g.y, m.y, v.y); upd(p.z, g.z, m.z, v.z); upd(p.w, g.w, m.w, v.w);
+        reinterpret_cast<float4*>(d.p)[i] = p; reinterpret_cast<float4*>(d.m)[i] = m; reinterpret_cast<float4*>(d.v)[i] = v;
+    }
+    for (long long i = n4 * 4 + tid; i < d.numel; i += stride) upd(d.p[i], d.g[i], d.m[i], d.v[i]);
+}
+
+int pb_adam_step(const pb_adam_desc* descs_dev, int n, float lr, double beta1, double beta2, float eps, float weight_decay, long long step,
+                 void* stream) {
+    if (n <= 0) return PB_OK;
+    PB_REQUIRE(descs_dev != nullptr && step >= 1, PB_ERR_SHAPE, "adam_step: null table or step < 1");
+    const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+    adam_kernel<<<dim3(32, n), 256, 0, (cudaStream_t)stream>>>(descs_dev, (float)(lr / bc1), (float)beta1, (float)beta2, (float)(1.0 / sqrt(bc2)), eps,
+                                                              weight_decay, (float)(1.0 - beta1), (float)(1.0 - beta2));
+    pb_count_launch(1);
+    return pb_check_launch("pb_adam_step");
+}
+
 int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream) {
     if (n <= 0) return PB_OK;
     PB_REQUIRE(chunks_dev != nullptr && flat != nullptr, PB_ERR_SHAPE, "flat_copy: null argument");

@@ -447,3 +447,47 @@ def test_graphed_step_and_two_stage_backward_match_eager(pb, wide_ref):
         assert abs(lA - float(loss_e)) <= tol and abs(lA2 - lA) <= tol
         assert abs(lB - lB_direct) <= tol and abs(lB - lA) > 100 * tol
         del step
+
+
+@pytest.mark.parametrize("name,B,cfg", [
+    ("C4: L=2048", 4, dict(sequences_length=2048, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=2)),
+    ("C5: C=256 G=1024 L=1024", 2, dict(sequences_length=1024, num_annotations=8943, local_dim=256, global_dim=1024, key_dim=64, num_heads=4, num_blocks=2)),
+])
+def test_other_baseline_configs_run_in_both_precisions(pb, name, B, cfg):
+    """BASELINE.json's long-sequence and wide configurations (block count cut to 2 for test time): the bf16 path (tensor
+    cores where the tiling covers the shape, the SIMT engine elsewhere) must agree with the fp32 path on the loss and
+    leave finite gradients."""
+    losses = {}
+    for prec in ("fp32", "bf16"):
+        torch.manual_seed(0)
+        model = pb.ProteinBERT(device=torch.device("cuda"), precision=prec, **cfg)
+        b = [t.cuda() for t in model_oracle.synthetic_batch(B, cfg["sequences_length"], cfg["num_annotations"], seed=1)]
+        X, Y, W = {"local": b[0], "global": b[1]}, {"local": b[2], "global": b[3]}, {"local": b[4], "global": b[5]}
+        losses[prec] = float(pb.pretraining_step(model, X, Y, W))
+        assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters()), (name, prec)
+    assert abs(losses["bf16"] - losses["fp32"]) <= 2e-3 * abs(losses["fp32"]), (name, losses)
+
+
+def test_fused_adam_matches_torch_adam(pb):
+    """pb_adam_step (FusedAdam) against torch.optim.Adam on the same parameters and gradients for several steps, odd sizes
+    and a tensor above the 64k-element piece size; interchangeable state_dict."""
+    g = torch.Generator().manual_seed(0)
+    shapes = [(7,), (33, 5), (300, 301), (128, 128, 9), (1,)]
+    p_ref = [torch.randn(s, generator=g).cuda().requires_grad_(True) for s in shapes]
+    p_new = [p.detach().clone().requires_grad_(True) for p in p_ref]
+    ref = torch.optim.Adam(p_ref, lr=2e-4, foreach=False, fused=False)
+    new = pb.FusedAdam(p_new, lr=2e-4)
+    for step in range(4):
+        for a, b_ in zip(p_ref, p_new):
+            gr = torch.randn(a.shape, generator=g).cuda() * (10.0 ** (step - 2))
+            a.grad, b_.grad = gr.clone(), gr.clone()
+        ref.step(); new.step()
+        for a, b_ in zip(p_ref, p_new):
+            assert_close_rel(b_.detach(), a.detach(), 1e-6, what=f"param step {step}")
+    for a, b_ in zip(p_ref, p_new):
+        assert_close_rel(new.state[b_]["exp_avg"], ref.state[a]["exp_avg"], 1e-6)
+        assert_close_rel(new.state[b_]["exp_avg_sq"], ref.state[a]["exp_avg_sq"], 1e-6)
+    ref2 = torch.optim.Adam(p_ref, lr=2e-4)
+    ref2.load_state_dict(new.state_dict())                      # same keys / layout as the torch optimizer
+    for a in p_ref:
+        assert float(ref2.state[a]["step"]) == float(ref.state[a]["step"]) == 4
