@@ -188,6 +188,12 @@ int pb_conv_pair_fwd(const void* x_act, const void* wn_pack, const void* ww_pack
  * dx = du + dgrad_n(dzn) + dgrad_w(dzw) (+ dx_extra when non-NULL), dWn/dWw [Co,Ci,k] float, dbn/dbw,
  * dg2l[b,c] = sum_l du (dbn, dbw, dg2l are ACCUMULATED: zero on entry).  wn_bwd/ww_bwd are bwd packs.  ws: split-K partial tiles of the weight-gradient
  * GEMMs, pb_workspace_bytes("wgrad", 0, 0, 0) bytes (NULL or too small: atomics are used instead).   */
+/* The three backward entry points of the local track (pb_conv_pair_bwd, pb_local_linear_bwd, pb_attn_pool_bwd) each have a
+ * data-gradient half and a weight-gradient half that only the optimizer needs.  Passing NULL for the data-gradient
+ * output (dx / dh / dh_out) runs the weight-gradient half alone, NULL for the weight gradient(s) (dWn+dWw / dW / dWvT) the
+ * data-gradient half alone: a caller can put the weight gradients on a second stream, off the critical path of
+ * backward.  In the weight-gradient-only call dzn/dzw, dz, dzv are INPUTS (written by the data-gradient call) and the
+ * pre-activations z* must be NULL. */
 int pb_conv_pair_bwd(const void* du_act, const void* zn_act, const void* zw_act, const void* x_act,
                      const void* wn_bwd, const void* ww_bwd, void* dzn_act, void* dzw_act, void* dx_act,
                      float* dWn, float* dWw, float* dbn, float* dbw, float* dg2l, int B, int L, int C, int ksize,

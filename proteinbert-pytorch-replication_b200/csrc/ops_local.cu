@@ -770,28 +770,39 @@ int pb_conv_pair_bwd(const void* du, const void* zn, const void* zw, const void*
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L, K = ksize * C, half = ksize / 2;
     const bool tc = dt == PB_BF16 && pb_tc_conv_ok(B, L, C, ksize, dil);
-    if (!tc) {
+    // dx == NULL skips the data-gradient half, dWn == NULL the weight-gradient half (the caller may run them on two streams)
+    const bool do_dx = dx != nullptr, do_dw = dWn != nullptr;
+    PB_REQUIRE(do_dx || do_dw, PB_ERR_SHAPE, "conv_pair_bwd: nothing to do (dx and dWn both NULL)");
+    PB_REQUIRE(!do_dw || dWw != nullptr, PB_ERR_SHAPE, "conv_pair_bwd: dWn and dWw go together");
+    if (!tc && do_dw) {
         PB_CUDA(cudaMemsetAsync(dWn, 0, (size_t)C * C * ksize * sizeof(float), st));
         PB_CUDA(cudaMemsetAsync(dWw, 0, (size_t)C * C * ksize * sizeof(float), st));
     }
     DISPATCH_DT(dt, {
-        if (zn != nullptr) launch_gelu_bwd_colsum<T>(du, zn, zw, dzn, dzw, dg2l, dbn, dbw, B, L, C, st);
+        if (zn != nullptr) {
+            PB_REQUIRE(do_dx, PB_ERR_SHAPE, "conv_pair_bwd: the GELU gradients belong to the data-gradient call (pass zn = NULL with dx = NULL)");
+            launch_gelu_bwd_colsum<T>(du, zn, zw, dzn, dzw, dg2l, dbn, dbw, B, L, C, st);
+        }
         if (tc) {
-            int rc = pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st);
+            int rc = do_dx ? pb_tc_conv_pair_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, st) : 0;
             if (rc) return rc;
-            rc = pb_tc_conv_wgrad(dzn, dzw, x, dWn, dWw, B, L, C, ksize, dil, ws, ws_bytes, st);
+            rc = do_dw ? pb_tc_conv_wgrad(dzn, dzw, x, dWn, dWw, B, L, C, ksize, dil, ws, ws_bytes, st) : 0;
             if (rc) return rc;
         } else {
-            // data gradient: same implicit GEMM with the taps mirrored (sign = -1) and the [t][ci][co] pack
-            gemm_auto(ConvA<T>{(const T*)dzn, L, C, 1, half, -1}, ConvPackB<T>{(const T*)wn_bwd, C},
-                      EpDgrad<T>{(const T*)du, nullptr, (T*)dx, C, 0}, M, C, K, 1, 1, st);
-            gemm_auto(ConvA<T>{(const T*)dzw, L, C, dil, half, -1}, ConvPackB<T>{(const T*)ww_bwd, C},
-                      EpDgrad<T>{nullptr, nullptr, (T*)dx, C, 1}, M, C, K, 1, 1, st);
-            // weight gradient: one [C x C] GEMM per tap, contraction over all B*L rows, split-K with atomics
-            const int tiles = ceil_div(C, C >= 128 ? 128 : 64) * ceil_div(C, C >= 128 ? 128 : 64) * ksize;
-            const int ns = split_for(tiles, M);
-            gemm_auto(WgradA<T>{(const T*)dzn, C}, WgradB<T>{(const T*)x, L, C, 1, half}, EpWgradAtomic{dWn, C, ksize}, C, C, M, ns, ksize, st);
-            gemm_auto(WgradA<T>{(const T*)dzw, C}, WgradB<T>{(const T*)x, L, C, dil, half}, EpWgradAtomic{dWw, C, ksize}, C, C, M, ns, ksize, st);
+            if (do_dx) {
+                // data gradient: same implicit GEMM with the taps mirrored (sign = -1) and the [t][ci][co] pack
+                gemm_auto(ConvA<T>{(const T*)dzn, L, C, 1, half, -1}, ConvPackB<T>{(const T*)wn_bwd, C},
+                          EpDgrad<T>{(const T*)du, nullptr, (T*)dx, C, 0}, M, C, K, 1, 1, st);
+                gemm_auto(ConvA<T>{(const T*)dzw, L, C, dil, half, -1}, ConvPackB<T>{(const T*)ww_bwd, C},
+                          EpDgrad<T>{nullptr, nullptr, (T*)dx, C, 1}, M, C, K, 1, 1, st);
+            }
+            if (do_dw) {
+                // weight gradient: one [C x C] GEMM per tap, contraction over all B*L rows, split-K with atomics
+                const int tiles = ceil_div(C, C >= 128 ? 128 : 64) * ceil_div(C, C >= 128 ? 128 : 64) * ksize;
+                const int ns = split_for(tiles, M);
+                gemm_auto(WgradA<T>{(const T*)dzn, C}, WgradB<T>{(const T*)x, L, C, 1, half}, EpWgradAtomic{dWn, C, ksize}, C, C, M, ns, ksize, st);
+                gemm_auto(WgradA<T>{(const T*)dzw, C}, WgradB<T>{(const T*)x, L, C, dil, half}, EpWgradAtomic{dWw, C, ksize}, C, C, M, ns, ksize, st);
+            }
         }
     });
     return pb_check_launch("pb_conv_pair_bwd");
@@ -819,18 +830,24 @@ int pb_local_linear_bwd(const void* du2, const void* z, const void* h, const voi
     cudaStream_t st = (cudaStream_t)stream;
     const int M = B * L;
     const bool tc = dt == PB_BF16 && Wt != nullptr && pb_tc_linear_ok(B, L, C);
-    if (!tc) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
+    // dh == NULL skips the data-gradient half, dW == NULL the weight-gradient half (the caller may run them on two streams)
+    const bool do_dx = dh != nullptr, do_dw = dW != nullptr;
+    PB_REQUIRE(do_dx || do_dw, PB_ERR_SHAPE, "local_linear_bwd: nothing to do (dh and dW both NULL)");
+    if (!tc && do_dw) PB_CUDA(cudaMemsetAsync(dW, 0, (size_t)C * C * sizeof(float), st));
     DISPATCH_DT(dt, {
-        if (z != nullptr) launch_gelu_bwd_colsum<T>(du2, z, nullptr, dz, nullptr, nullptr, db, nullptr, B, L, C, st);
+        if (z != nullptr) {
+            PB_REQUIRE(do_dx, PB_ERR_SHAPE, "local_linear_bwd: the GELU gradient belongs to the data-gradient call (pass z = NULL with dh = NULL)");
+            launch_gelu_bwd_colsum<T>(du2, z, nullptr, dz, nullptr, nullptr, db, nullptr, B, L, C, st);
+        }
         if (tc) {
             int rc = pb_tc_local_linear_bwd(du2, dz, h, Wt, dh, dW, B, L, C, ws, ws_bytes, st);
             if (rc) return rc;
         } else {
             // dh = du2 + dz W
-            gemm_auto(RowMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)W, C}, EpAddStore<T>{(const T*)du2, (T*)dh, C}, M, C, C, 1, 1, st);
+            if (do_dx) gemm_auto(RowMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)W, C}, EpAddStore<T>{(const T*)du2, (T*)dh, C}, M, C, C, 1, 1, st);
             // dW[n,c] = sum_rows dz[row,n] h[row,c]
             const int tiles = ceil_div(C, C >= 128 ? 128 : 64) * ceil_div(C, C >= 128 ? 128 : 64);
-            gemm_auto(ColMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)h, C}, EpAtomic{dW, C}, C, C, M, split_for(tiles, M), 1, st);
+            if (do_dw) gemm_auto(ColMajorA<T>{(const T*)dz, C}, MatKN<T>{(const T*)h, C}, EpAtomic{dW, C}, C, C, M, split_for(tiles, M), 1, st);
         }
     });
     return pb_check_launch("pb_local_linear_bwd");
@@ -853,8 +870,10 @@ int pb_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float
         return pb_tc_attn_pool_bwd(h, wvT, wv, dpool, dh_in, dzv, dh_out, dWvT, head_dv, B, L, C, G, ws, ws_bytes, st);
     if (dWvT) PB_CUDA(cudaMemsetAsync(dWvT, 0, (size_t)G * C * sizeof(float), st));
     DISPATCH_DT(dt, {
-        gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
-        gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);
+        if (dh_out != nullptr) {       // dh_out == NULL: weight-gradient half only, dzv is then an input
+            gemm_auto(RowMajorA<T>{(const T*)h, C}, WeightNK<T>{(const T*)wvT, C}, EpPoolBwd<T>{dpool, (T*)dzv, L, G}, M, G, C, 1, 1, st);
+            gemm_auto(RowMajorA<T>{(const T*)dzv, G}, MatKN<T>{(const T*)wvT, C}, EpAddStore<T>{(const T*)dh_in, (T*)dh_out, C}, M, C, G, 1, 1, st);
+        }
         if (dWvT) {
             const int tiles = ceil_div(G, 128) * ceil_div(C, 128);
             if (head_dv > 0)

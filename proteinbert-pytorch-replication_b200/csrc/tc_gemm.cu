@@ -499,8 +499,8 @@ int pb_tc_local_linear_bwd(const void* du2, const void* dz, const void* h, const
     // dh = du2 + dz W   (B operand = W^T [C_in, C_out], K-major)   ;   dW[n, c] = sum_rows dz[row, n] h[row, c]
     GemmEpi ep{};
     ep.ldn = C; ep.L = L; ep.base = (const bf16*)du2; ep.out0 = (bf16*)dh;
-    int rc = launch_gemm<EPI_ADD_STORE>(dz, Wt, ep, B * L, C, C, st, "tc_local_linear_bwd(dh)");
-    if (rc) return rc;
+    int rc = dh ? launch_gemm<EPI_ADD_STORE>(dz, Wt, ep, B * L, C, C, st, "tc_local_linear_bwd(dh)") : 0;      // dh == NULL: dW only
+    if (rc || dW == nullptr) return rc;                                                                        // dW == NULL: dh only
     return launch_wgrad(dz, nullptr, h, dW, nullptr, C, 1, 0, B, L, C, C, 1, 1, 1, ws, ws_bytes, st, "tc_local_linear_bwd(dW)");
 }
 
@@ -515,13 +515,16 @@ int pb_tc_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const fl
                         void* dh_out, float* dWvT, int head_dv, int B, int L, int C, int G, void* ws, size_t ws_bytes, cudaStream_t st) {
     GemmEpi e1{};
     e1.ldn = G; e1.L = L; e1.dpool = dpool; e1.out0 = (bf16*)dzv;
-    int rc = pb_tc_pool_ok(B, L, C, G) ? pb_tc_pool_dz(h, wvT, dpool, dzv, B, L, G, st)
+    int rc = 0;
+    if (dh_out != nullptr) {        // dh_out == NULL: weight-gradient half only, dzv is then an INPUT
+        rc = pb_tc_pool_ok(B, L, C, G) ? pb_tc_pool_dz(h, wvT, dpool, dzv, B, L, G, st)
                                        : launch_gemm<EPI_POOL_DZ>(h, wvT, e1, B * L, G, C, st, "tc_attn_pool_bwd(dzv)");
-    if (rc) return rc;
-    GemmEpi e2{};
-    e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
-    rc = launch_gemm<EPI_ADD_STORE>(dzv, wv, e2, B * L, C, G, st, "tc_attn_pool_bwd(dh)");
-    if (rc) return rc;
+        if (rc) return rc;
+        GemmEpi e2{};
+        e2.ldn = C; e2.L = L; e2.base = (const bf16*)dh_in; e2.out0 = (bf16*)dh_out;
+        rc = launch_gemm<EPI_ADD_STORE>(dzv, wv, e2, B * L, C, G, st, "tc_attn_pool_bwd(dh)");
+        if (rc) return rc;
+    }
     if (dWvT) rc = launch_wgrad(dzv, nullptr, h, dWvT, nullptr, C, 1, 0, B, L, G, C, 1, 1, 1, ws, ws_bytes, st, "tc_attn_pool_bwd(dWv)", head_dv);
     return rc;
 }

@@ -369,6 +369,35 @@ def global_fused_ok(B, G, C) -> bool:
     return bool(lib().pb_global_fused_ok(B, G, C))
 
 
+# ---- weight gradients off the critical path ------------------------------------------------------------------------
+# Only the optimizer reads the weight gradients, so LocalTrackFn.backward can issue the three weight-gradient GEMM groups
+# of a block on a second, low-priority stream: they then fill the SMs that the narrow kernels of the critical path leave
+# idle (the 64..80-CTA global-track kernels, the 128-CTA convolutions, every kernel's tail).  The side stream is joined
+# at the end of each block's backward, or -- inside pretraining_step / GraphedPretrainStep, which set DEFER_WGRAD_JOIN --
+# once after the whole backward (join_side_streams()).  PB_B200_WGRAD_STREAM=0 turns the second stream off.
+import os as _os
+
+WGRAD_STREAM = _os.environ.get("PB_B200_WGRAD_STREAM", "1") != "0"
+DEFER_WGRAD_JOIN = False
+_SIDE = {}
+_SIDE_PENDING = set()
+
+
+def _side_stream(dev):
+    s = _SIDE.get(dev)
+    if s is None:
+        s = torch.cuda.Stream(device=dev, priority=0)          # the main stream of a step may be high priority; this is not
+        _SIDE[dev] = s
+    return s
+
+
+def join_side_streams():
+    """Make the current stream of every device wait for the weight gradients issued on the side stream."""
+    for dev in list(_SIDE_PENDING):
+        torch.cuda.current_stream(dev).wait_stream(_SIDE[dev])
+    _SIDE_PENDING.clear()
+
+
 class ZeroArena:
     """One zero-filled buffer per model forward from which every block takes its "zero on entry" operands (LayerNorm
     statistics, pooling accumulator, and the accumulated gradients of its backward): one fill launch per step instead of
@@ -478,7 +507,26 @@ class LocalTrackFn(torch.autograd.Function):
         dh2t = torch.empty_like(x)
         Dv = G // n_heads
         dWv = f32(n_heads, C, Dv) if head_grads else None          # one contiguous [C, Dv] gradient per head
-        _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
+        side = _side_stream(dev) if WGRAD_STREAM else None
+        main = torch.cuda.current_stream(dev)
+
+        def on_side(fn, *used):
+            """Run fn (which launches on the then-current stream) on the side stream, after everything issued so far."""
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                fn()
+            for t in used:
+                if t is not None:
+                    t.record_stream(side)
+            _SIDE_PENDING.add(dev)
+
+        if side is None:
+            _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
+        else:
+            _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), None, Dv, B, L, C, G, dt, None, 0, st)
+            if dWv is not None:
+                on_side(lambda: _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), None, None, _p(dzv), None, _p(dWv), Dv, B, L, C, G, dt,
+                                      *_wgrad_ws(dev), _st()), h2, dzv, dWv, wvTw, wvw)
         del dzv
         fused = bool(L_.pb_ln_joint_bwd_gelu_ok(B, L, C))
         # LN2 (+ the linear layer's GELU gradient when the fused kernel takes the shape)
@@ -495,11 +543,17 @@ class LocalTrackFn(torch.autograd.Function):
             dz2 = dh2t                  # reuse as scratch
             dh1 = torch.empty_like(x)
         # local linear
-        _call("pb_local_linear_bwd", _p(du2), None if fused else _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2),
-                                     B, L, C, dt, *_wgrad_ws(dev), st)
+        if side is None:
+            _call("pb_local_linear_bwd", _p(du2), None if fused else _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), _p(dW2), _p(db2),
+                                         B, L, C, dt, *_wgrad_ws(dev), st)
+        else:
+            _call("pb_local_linear_bwd", _p(du2), None if fused else _p(z2), _p(h1), _p(W2w), _p(W2Tw), _p(dz2), _p(dh1), None, _p(db2),
+                                         B, L, C, dt, None, 0, st)
+            on_side(lambda: _call("pb_local_linear_bwd", None, None, _p(h1), _p(W2w), _p(W2Tw), _p(dz2), None, _p(dW2), None,
+                                  B, L, C, dt, *_wgrad_ws(dev), _st()), h1, dz2, dW2, W2w, W2Tw)
         # LN1 (+ both convolutions' GELU gradients and the per-sample sums behind dg2l)
         du1 = du2                       # du2 is dead after the linear backward
-        dzn = dz2                       # so is dz2
+        dzn = dz2 if side is None else torch.empty_like(x)     # dz2 is still being read by the side stream's dW2 GEMM
         if fused:
             dzw = torch.empty_like(x)
             _call("pb_ln_joint_bwd_gelu", _p(dh1), _p(u1), _p(stats1), _p(ln1w), _p(zn), _p(zw), _p(du1), _p(dzn), _p(dzw),
@@ -511,9 +565,17 @@ class LocalTrackFn(torch.autograd.Function):
         # conv pair
         dx = torch.empty_like(x)
         dWn, dWw = f32(C, C, ksize), f32(C, C, ksize)
-        _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
-                                  _p(dzw), _p(dx), _p(dWn), _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt,
-                                  *_wgrad_ws(dev), st)
+        if side is None:
+            _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
+                                      _p(dzw), _p(dx), _p(dWn), _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt,
+                                      *_wgrad_ws(dev), st)
+        else:
+            _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
+                                      _p(dzw), _p(dx), None, None, _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, None, 0, st)
+            on_side(lambda: _call("pb_conv_pair_bwd", None, None, None, _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), None, _p(dWn), _p(dWw),
+                                  None, None, None, B, L, C, ksize, dil, dt, *_wgrad_ws(dev), _st()), x, dzn, dzw, dWn, dWw)
+            if not DEFER_WGRAD_JOIN:
+                join_side_streams()
         if head_grads:
             dheads = tuple(dWv[h] for h in range(n_heads))
         else:
@@ -641,4 +703,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "ZeroArena", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]

@@ -40,7 +40,12 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None)
     loss = pretraining_loss(p_local, p_global, Y, W)
     if reducer is not None:
         reducer.prepare()
-    loss.backward()
+    ops.DEFER_WGRAD_JOIN = reducer is None          # the eager bucket hooks read gradients as they appear: join per block then
+    try:
+        loss.backward()
+    finally:
+        ops.DEFER_WGRAD_JOIN = False
+        ops.join_side_streams()                     # weight gradients issued on the side stream (ops.LocalTrackFn)
     if reducer is not None:
         reducer.finish()
     return loss.detach()
@@ -145,13 +150,23 @@ class GraphedPretrainStep:
             loss = pretraining_loss(p_local, p_global, sy, sw)
             hb, gb = model._boundary
             model._boundary = None
-            grads = torch.autograd.grad(loss, upper + upper_heads + [hb, gb], retain_graph=True)
+            ops.DEFER_WGRAD_JOIN = True
+            try:
+                grads = torch.autograd.grad(loss, upper + upper_heads + [hb, gb], retain_graph=True)
+            finally:
+                ops.DEFER_WGRAD_JOIN = False
+                ops.join_side_streams()
             for p, g in zip(upper + upper_heads, grads):
                 p.grad = g
             return loss.detach(), hb, gb, grads[-2], grads[-1]
 
         def stage_b(hb, gb, dhb, dgb):
-            torch.autograd.backward([hb, gb], [dhb, dgb])
+            ops.DEFER_WGRAD_JOIN = True
+            try:
+                torch.autograd.backward([hb, gb], [dhb, dgb])
+            finally:
+                ops.DEFER_WGRAD_JOIN = False
+                ops.join_side_streams()
 
         def full_step():
             if self.split:
