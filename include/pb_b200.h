@@ -164,7 +164,12 @@ int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const fl
  * every CTA the B x G GELU derivatives. */
 int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, const float* z3, const float* g,
                       const float* W1, const float* W3, float* dg, float* dW1, float* db1, float* dW3, float* db3,
-                      int B, int G, int C, int dgh_is_dz3, void* stream);
+                      int B, int G, int C, int dgh_is_dz3, float* dzg_out, void* stream);
+/* Weight gradients off the critical path: pb_global_pre_bwd with dW1 = dW3 = NULL and pb_global_post_bwd with dW4 = NULL
+ * skip their dW parts; the caller forms them as dW3 = dz3^T g, dW1 = dzg^T g (dzg_out [B,C] = dg2l * gelu'(zg), then
+ * required) and dW4 = dz4^T g1 (dz4 = scratch3 + 2*B*G) with pb_matmul_tn, e.g. on a second stream.
+ * out[n, k] = sum_m A[m, n] * B[m, k], all float, A [M,N], B [M,K], out [N,K]. */
+int pb_matmul_tn(const float* A, const float* B, float* out, int M, int N, int K, void* stream);
 int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const float* Wp, int Kdim,
                        const float* gamma1, const float* beta1, const float* W4, const float* b4, const float* gamma2,
                        const float* beta2, float* g1, float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2,

@@ -41,7 +41,8 @@ PROTOTYPES = {
     "pb_res_ln_rows_bwd": [_p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _p],
     "pb_global_fused_ok": [_i, _i, _i],
     "pb_global_pre_fwd": [_p] * 9 + [_i, _i, _i, _p],
-    "pb_global_pre_bwd": [_p] * 12 + [_i, _i, _i, _i, _p],
+    "pb_global_pre_bwd": [_p] * 12 + [_i, _i, _i, _i, _p, _p],
+    "pb_matmul_tn": [_p, _p, _p, _i, _i, _i, _p],
     "pb_global_post_fwd": [_p, _p, _p, _p, _i] + [_p] * 13 + [_i, _i, _p],
     "pb_global_post_bwd": [_p] * 12 + [_i] + [_p] * 12 + [_i, _i, _p],
     "pb_conv_pair_fwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],

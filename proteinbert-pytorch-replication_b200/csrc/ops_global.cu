@@ -224,6 +224,15 @@ int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float*
     return pb_check_launch("pb_linear_bwd");
 }
 
+// out[n, k] = sum_m A[m, n] * B[m, k]: the weight gradient dW = dZ^T X of a dense layer as a stand-alone product, for
+// callers that take it off the critical path (the fused global-track backward kernels can skip their dW part).
+int pb_matmul_tn(const float* A, const float* B, float* out, int M, int N, int K, void* stream) {
+    PB_REQUIRE(M > 0 && N > 0 && K > 0 && A && B && out, PB_ERR_SHAPE, "matmul_tn: bad arguments M=%d N=%d K=%d", M, N, K);
+    launch_gemm_simt<64, 64, 16, 4, 4>(ColMajorA<float>{A, N}, MatKN<float>{B, K}, EpStore{out, K}, N, K, M, 1, 1, (cudaStream_t)stream);
+    pb_count_launch(1);
+    return pb_check_launch("pb_matmul_tn");
+}
+
 int pb_res_ln_rows_fwd(const float* a, const float* b, const float* c, const float* w_param, int Kdim, const float* gamma,
                        const float* beta, float* xhat, float* rstd, float* y, int B, int G, void* stream) {
     PB_REQUIRE(B > 0 && G > 0 && G <= 12288, PB_ERR_SHAPE, "res_ln_rows_fwd: bad shape B=%d G=%d", B, G);

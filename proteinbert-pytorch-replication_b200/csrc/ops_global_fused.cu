@@ -231,6 +231,8 @@ struct PreBwd {
     float *dg, *dW1, *db1, *dW3, *db3;
     int B, G, C;
     int dgh_is_dz3;                // dgh already holds dgh * gelu'(z3) (written by the post backward kernel)
+    float* dzg_out;                // optional [B, C]: dg2l * gelu'(zg), for a caller that forms dW1 itself
+    int skip_dw;                   // leave dW3 / dW1 to the caller (pb_matmul_tn on another stream)
     unsigned long long* dbg;
 };
 
@@ -269,7 +271,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
         fill_tile<2, false>(A_s + G, lda, MT, mt, C, p.dg2l, p.zg, C, row0, MulGeluGrad4());
         __syncthreads();
         stamp(p.dbg, 17);
-        if (has_dg) fill_x_slice(D_s, p.g, G, row0, mt, MT, n0);         // g[:, n0 .. n0+7]
+        if (p.dzg_out != nullptr && blockIdx.x == 0)       // one CTA publishes dzg (columns G .. G+C of the staged tile)
+            for (int i = threadIdx.x; i < mt * C; i += kThreads) p.dzg_out[(size_t)(row0 + i / C) * C + i % C] = A_s[(size_t)(i / C) * lda + G + i % C];
+        if (has_dg && !p.skip_dw) fill_x_slice(D_s, p.g, G, row0, mt, MT, n0);         // g[:, n0 .. n0+7]
         if (threadIdx.x < 32) {                        // db of columns n0 .. n0+7 of [dz3 | dzg] (n0 + j < KA always)
             float a = 0.f;
             for (int m = threadIdx.x >> 3; m < mt; m += 4) a += A_s[(size_t)m * lda + n0 + (threadIdx.x & 7)];
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
         }
         __syncthreads();
         stamp(p.dbg, 18);
-        if (has_dg) dw_from_tile(accw, A_s, lda, D_s, mt, KA);          // [dW3 ; dW1][:, n0 .. n0+7]
+        if (has_dg && !p.skip_dw) dw_from_tile(accw, A_s, lda, D_s, mt, KA);          // [dW3 ; dW1][:, n0 .. n0+7]
         stamp(p.dbg, 19);
         if (has_dg) {
             float out[kNT];
@@ -291,7 +295,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
         }
     }
     stamp(p.dbg, 20);
-    if (has_dg) {
+    if (has_dg && !p.skip_dw) {
 #pragma unroll
         for (int q = 0; q < kQ; ++q) {
             const int n = threadIdx.x + q * kThreads;
@@ -399,6 +403,7 @@ struct PostBwd {
     const float *dg2, *gamma2, *xhat2, *rstd2, *z4, *g1, *W4, *gamma1, *xhat1, *rstd1, *pool, *Wp;
     const float* z3;               // optional: pre-activation of gh, to emit dz3 = dx1 * gelu'(z3) for the pre backward kernel
     float* dz3;
+    int skip_dw;                   // leave dW4 to the caller (dz4 is scratch3[2], pb_matmul_tn on another stream)
     float *dg1, *dx2, *dz4, *dx1, *dpool, *dWp, *dgamma1, *dbeta1, *dW4, *db4, *dgamma2, *dbeta2;
     int B, G, Kdim;
     unsigned long long* dbg;
@@ -458,7 +463,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
         fill_tile<1, true>(A_s, lda, MT, mt, G, p.dz4, nullptr, G, row0, Copy4());
         __syncthreads();
         stamp(p.dbg, 35);
-        fill_x_slice(D_s, p.g1, G, row0, mt, MT, n0);                   // g1[:, n0 .. n0+7]
+        if (!p.skip_dw) fill_x_slice(D_s, p.g1, G, row0, mt, MT, n0);   // g1[:, n0 .. n0+7]
         if (threadIdx.x < 32) {          // one warp: 8 columns x 4 row lanes, folded with two shuffles
             const int j = threadIdx.x & 7, c = n0 + j;
             float a = 0.f, b = 0.f, e = 0.f;
@@ -477,7 +482,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
         }
         __syncthreads();
         stamp(p.dbg, 36);
-        dw_from_tile(accw, A_s, lda, D_s, mt, G);                       // dW4[:, n0 .. n0+7] = dz4^T g1[:, n0 ..]
+        if (!p.skip_dw) dw_from_tile(accw, A_s, lda, D_s, mt, G);       // dW4[:, n0 .. n0+7] = dz4^T g1[:, n0 ..]
         stamp(p.dbg, 37);
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);                   // dz4 W4[:, n0..]
@@ -489,10 +494,12 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
             *reinterpret_cast<float4*>(p.dg1 + o + 4) = make_float4(out[4] + x1.x, out[5] + x1.y, out[6] + x1.z, out[7] + x1.w);
         }
     }
+    if (!p.skip_dw) {
 #pragma unroll
-    for (int q = 0; q < kQ; ++q) {
-        const int n = threadIdx.x + q * kThreads;
-        if (n < G) store8(p.dW4 + (size_t)n * G + n0, accw[q]);
+        for (int q = 0; q < kQ; ++q) {
+            const int n = threadIdx.x + q * kThreads;
+            if (n < G) store8(p.dW4 + (size_t)n * G + n0, accw[q]);
+        }
     }
     if (threadIdx.x < kNT) {
         p.db4[n0 + threadIdx.x] = c_db4;
@@ -594,12 +601,16 @@ int pb_global_pre_fwd(const float* g, const float* W1, const float* b1, const fl
 
 int pb_global_pre_bwd(const float* dg2l, const float* dgh, const float* zg, const float* z3, const float* g, const float* W1,
                       const float* W3, float* dg, float* dW1, float* db1, float* dW3, float* db3, int B, int G, int C,
-                      int dgh_is_dz3, void* stream) {
+                      int dgh_is_dz3, float* dzg_out, void* stream) {
     PB_REQUIRE(pb_global_fused_ok(B, G, C), PB_ERR_UNSUPPORTED, "global_pre_bwd: shape B=%d G=%d C=%d not covered", B, G, C);
     const size_t smem = smem_bytes(row_tile_of(G + C), G + C, true);
     int rc = dgh_is_dz3 ? set_smem(global_pre_bwd_kernel<true>, smem) : set_smem(global_pre_bwd_kernel<false>, smem);
     if (rc) return rc;
-    PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C, dgh_is_dz3, (unsigned long long*)pb_debug_ptr()};
+    // dW1 == NULL (with dW3 == NULL): the weight gradients are left to the caller, who needs dzg_out for dW1 = dzg^T g
+    PB_REQUIRE((dW1 == nullptr) == (dW3 == nullptr), PB_ERR_SHAPE, "global_pre_bwd: dW1 and dW3 go together");
+    PB_REQUIRE(dW1 != nullptr || dzg_out != nullptr, PB_ERR_SHAPE, "global_pre_bwd: without dW1/dW3 the caller needs dzg_out");
+    PreBwd p{dg2l, dgh, zg, z3, g, W1, W3, dg, dW1, db1, dW3, db3, B, G, C, dgh_is_dz3, dzg_out, dW1 == nullptr ? 1 : 0,
+             (unsigned long long*)pb_debug_ptr()};
     if (dgh_is_dz3) PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel<true>, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
     else PB_CUDA(pb_launch_pdl(global_pre_bwd_kernel<false>, dim3((G + C) / kNT), dim3(kThreads), smem, (cudaStream_t)stream, p));
     pb_count_launch(1);
@@ -635,7 +646,7 @@ int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2
     if (rc) return rc;
     const size_t n = (size_t)B * G;
     PB_REQUIRE((z3 == nullptr) == (dz3 == nullptr), PB_ERR_SHAPE, "global_post_bwd: z3 and dz3 go together");
-    PostBwd p{dg2, gamma2, xhat2, rstd2, z4, g1, W4, gamma1, xhat1, rstd1, pool, Wp, z3, dz3,
+    PostBwd p{dg2, gamma2, xhat2, rstd2, z4, g1, W4, gamma1, xhat1, rstd1, pool, Wp, z3, dz3, dW4 == nullptr ? 1 : 0,
               scratch3, scratch3 + n, scratch3 + 2 * n, dx1, dpool, dWp, dgamma1, dbeta1, dW4, db4, dgamma2, dbeta2, B, G, Kdim, (unsigned long long*)pb_debug_ptr()};
     void* args[] = {&p};
     PB_CUDA(cudaLaunchCooperativeKernel((const void*)global_post_bwd_kernel, dim3(G / kNT), dim3(kThreads), args, smem,

@@ -321,8 +321,16 @@ class GlobalPreFn(torch.autograd.Function):
         dg = torch.empty_like(g)
         dW1, db1 = torch.empty_like(W1), torch.empty((C,), dtype=torch.float32, device=dev)
         dW3, db3 = torch.empty_like(W3), torch.empty((G,), dtype=torch.float32, device=dev)
-        _call("pb_global_pre_bwd", _p(dg2l), _p(dgh), _p(zg[0]), _p(z3[0]), _p(g), _p(W1), _p(W3), _p(dg), _p(dW1), _p(db1),
-              _p(dW3), _p(db3), B, G, C, ready, _st())
+        if ready and WGRAD_STREAM:
+            # the two weight gradients leave the critical path: the kernel publishes dzg, the products run on the side stream
+            dzg = torch.empty((B, C), dtype=torch.float32, device=dev)
+            _call("pb_global_pre_bwd", _p(dg2l), _p(dgh), _p(zg[0]), _p(z3[0]), _p(g), _p(W1), _p(W3), _p(dg), None, _p(db1),
+                  None, _p(db3), B, G, C, ready, _p(dzg), _st())
+            run_on_side(dev, lambda: (_call("pb_matmul_tn", _p(dgh), _p(g), _p(dW3), B, G, G, _st()),
+                                      _call("pb_matmul_tn", _p(dzg), _p(g), _p(dW1), B, C, G, _st())), dgh, dzg, g, dW3, dW1)
+        else:
+            _call("pb_global_pre_bwd", _p(dg2l), _p(dgh), _p(zg[0]), _p(z3[0]), _p(g), _p(W1), _p(W3), _p(dg), _p(dW1), _p(db1),
+                  _p(dW3), _p(db3), B, G, C, ready, None, _st())
         return dg, dW1, db1, dW3, db3, None
 
 
@@ -357,9 +365,12 @@ class GlobalPostFn(torch.autograd.Function):
         vec = torch.empty((5, G), dtype=torch.float32, device=dev)         # dgamma1, dbeta1, db4, dgamma2, dbeta2
         dW4 = torch.empty_like(W4)
         dz3 = out[5] if z3 is not None else None
+        side = WGRAD_STREAM
         _call("pb_global_post_bwd", _p(dg2), _p(gamma2), _p(buf[3]), _p(rstd[1]), _p(buf[2]), _p(buf[0]), _p(W4), _p(gamma1),
               _p(buf[1]), _p(rstd[0]), _p(pool), _p(Wp), Wp.numel(), _p(out[0]), _p(out[3]), _p(out[4]), _p(dWp), _p(vec[0]),
-              _p(vec[1]), _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), _p(z3), _p(dz3), B, G, _st())
+              _p(vec[1]), None if side else _p(dW4), _p(vec[2]), _p(vec[3]), _p(vec[4]), _p(z3), _p(dz3), B, G, _st())
+        if side:        # dW4 = dz4^T g1 off the critical path (dz4 is the third scratch slab)
+            run_on_side(dev, lambda: _call("pb_matmul_tn", _p(out[2]), _p(buf[0]), _p(dW4), B, G, G, _st()), out, buf, dW4)
         if dz3 is not None:
             link.dz3, link.dgh_ptr = dz3, out[3].data_ptr()
         return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4], None
@@ -389,6 +400,21 @@ def _side_stream(dev):
         s = torch.cuda.Stream(device=dev, priority=0)          # the main stream of a step may be high priority; this is not
         _SIDE[dev] = s
     return s
+
+
+def run_on_side(dev, fn, *used):
+    """Run fn (which launches on the then-current stream) on the side stream, after everything issued so far on the current
+    stream; joined at once unless a step function defers the join to the end of backward."""
+    side, main = _side_stream(dev), torch.cuda.current_stream(dev)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        fn()
+    for t in used:
+        if t is not None:
+            t.record_stream(side)
+    _SIDE_PENDING.add(dev)
+    if not DEFER_WGRAD_JOIN:
+        join_side_streams()
 
 
 def join_side_streams():
