@@ -29,3 +29,22 @@ e0.record()
 for _ in range(20): fwd()
 e1.record(); torch.cuda.synchronize()
 print("fwd avg us", e0.elapsed_time(e1) / 20 * 1000)
+
+# ---- data-gradient variant ----
+du = torch.randn(B, L, C, generator=g).cuda().bfloat16()
+dzn, dzw = torch.randn(B, L, C, generator=g).cuda().bfloat16(), torch.randn(B, L, C, generator=g).cuda().bfloat16()
+dx = torch.empty_like(x)
+def dgrad():
+    ops._call("pb_conv_pair_bwd", du.data_ptr(), None, None, x.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(), dzn.data_ptr(), dzw.data_ptr(),
+              dx.data_ptr(), None, None, None, None, None, B, L, C, KS, DIL, 1, None, 0, st)
+for _ in range(3): dgrad()
+dbg.zero_()
+lib.pb_debug_buffer(dbg.data_ptr())
+dgrad(); torch.cuda.synchronize()
+d = dbg.cpu().tolist()
+print("dgrad: mma issue loop %d cyc (wait weights %d, wait halo %d), all MMAs done at %d; epilogue waited %d, epilogue work %d" % tuple(d[:6]))
+lib.pb_debug_buffer(None)
+e0.record()
+for _ in range(20): dgrad()
+e1.record(); torch.cuda.synchronize()
+print("dgrad avg us", e0.elapsed_time(e1) / 20 * 1000)
