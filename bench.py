@@ -162,7 +162,6 @@ def main():
     import torch
     import torch.distributed as dist
     import proteinbert_b200 as pb
-    from oracle import model_oracle          # synthetic_batch only (input generation); the oracle is not on the timed path
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -184,7 +183,7 @@ def main():
         for t in model.head_tensors().values():        # unregistered in the reference: broadcast once by hand
             dist.broadcast(t.data, 0)
     B = PER_GPU_BATCH
-    host = model_oracle.synthetic_batch(B, CFG["sequences_length"], CFG["num_annotations"], seed=100 + rank)
+    host = pb.data_processing.synthetic_batch(B, CFG["sequences_length"], CFG["num_annotations"], seed=100 + rank)
     host = [t.pin_memory() for t in host]
     devb = [t.to(dev) for t in host]
     h2d_bytes = sum(t.numel() * t.element_size() for t in host)

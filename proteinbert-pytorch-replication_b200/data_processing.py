@@ -151,3 +151,27 @@ class UniRefGO_PretrainingDataset(torch.utils.data.Dataset):
     def collate(self, samples):
         seqs, anns, draws = zip(*samples)
         return corrupt_pad(pack_batch(seqs, anns, draws, self.seq_max_length), self.device)
+
+
+def synthetic_batch(B: int, L: int, A: int, seed: int = 0, vocab_size: int = 26):
+    """Synthetic (X, Y, W) tensors of the shapes/dtypes the reference dataset yields (data_processing.py:159-180) without the
+    string path, for benchmarks and probes: random lengths (padded and full-length rows), 5 %-corrupted X tokens,
+    Bernoulli(0.005) annotations, half of the samples with all annotations hidden.  CPU tensors."""
+    gen = torch.Generator().manual_seed(seed)
+    lengths = torch.randint(2, 2 * L, (B,), generator=gen).clamp(max=L)
+    pos = torch.arange(L).unsqueeze(0)
+    valid = pos < lengths.unsqueeze(1)
+    y_local = torch.randint(4, vocab_size, (B, L), generator=gen)
+    y_local[:, 0] = 1
+    y_local[torch.arange(B), lengths - 1] = 2
+    y_local = torch.where(valid, y_local, torch.zeros_like(y_local))
+    corrupt = (torch.rand(B, L, generator=gen) < 0.05) & (y_local > 2)
+    x_local = torch.where(corrupt, torch.randint(3, vocab_size, (B, L), generator=gen), y_local)
+    y_global = (torch.rand(B, A, generator=gen) < 0.005).float()
+    keep = (torch.rand(B, A, generator=gen) < 0.75).float()
+    add = (torch.rand(B, A, generator=gen) < 1e-4).float()
+    shown = (torch.rand(B, 1, generator=gen) > 0.5).float()
+    x_global = (y_global + add) * keep * shown
+    w_local = (y_local != 0).double()
+    w_global = y_global.bool().any(dim=1, keepdim=True).double().expand(B, A).contiguous()
+    return x_local, x_global, y_local, y_global, w_local, w_global

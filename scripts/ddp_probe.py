@@ -6,7 +6,6 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import proteinbert_b200 as pb
-from oracle import model_oracle
 
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
@@ -17,7 +16,7 @@ dist.init_process_group("nccl", device_id=dev, pg_options=_opts)
 CFG = dict(sequences_length=512, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=6)
 torch.manual_seed(0)
 model = pb.ProteinBERT(device=dev, precision="bf16", **CFG)
-b = [t.to(dev) for t in model_oracle.synthetic_batch(64, 512, 8943, seed=rank)]
+b = [t.to(dev) for t in pb.data_processing.synthetic_batch(64, 512, 8943, seed=rank)]
 X, Y, W = {"local": b[0], "global": b[1]}, {"local": b[2], "global": b[3]}, {"local": b[4], "global": b[5]}
 t = torch.ones(1, device=dev); dist.all_reduce(t)
 

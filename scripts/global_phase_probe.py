@@ -8,12 +8,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import proteinbert_b200 as pb
 from bench import CFG
-from oracle import model_oracle          # synthetic inputs only
 
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
 model = pb.ProteinBERT(device=dev, precision="bf16", **CFG)
-b = [t.to(dev) for t in model_oracle.synthetic_batch(64, CFG["sequences_length"], CFG["num_annotations"], seed=100)]
+b = [t.to(dev) for t in pb.data_processing.synthetic_batch(64, CFG["sequences_length"], CFG["num_annotations"], seed=100)]
 X, Y, W = {"local": b[0], "global": b[1]}, {"local": b[2], "global": b[3]}, {"local": b[4], "global": b[5]}
 for _ in range(3):
     pb.pretraining_step(model, X, Y, W, None)

@@ -29,12 +29,11 @@ def main():
     import proteinbert_b200 as pb
     from proteinbert_b200 import ops
     from bench import CFG
-    from oracle import model_oracle          # synthetic inputs only
-
+    
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
     model = pb.ProteinBERT(device=dev, precision="bf16", **CFG)
-    b = [t.to(dev) for t in model_oracle.synthetic_batch(args.batch, CFG["sequences_length"], CFG["num_annotations"], seed=100)]
+    b = [t.to(dev) for t in pb.data_processing.synthetic_batch(args.batch, CFG["sequences_length"], CFG["num_annotations"], seed=100)]
     X, Y, W = {"local": b[0], "global": b[1]}, {"local": b[2], "global": b[3]}, {"local": b[4], "global": b[5]}
     for _ in range(3):
         pb.pretraining_step(model, X, Y, W, None)
