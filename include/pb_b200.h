@@ -288,6 +288,14 @@ int pb_corrupt_pad(const uint8_t* seq_bytes, const int64_t* seq_off, const int64
                    int64_t* y_local, double* w_local, float* x_global, float* y_global, double* w_global, int B,
                    int L, int A, void* stream);
 
+/* ---- which engine a shape takes ------------------------------------------------------------------
+ * op = "conv" (pb_conv_pair_*), "local_linear" (pb_local_linear_*), "attn_pool" (pb_attn_pool_*), all for PB_BF16
+ * activations: 0 = the fp32-accumulating SIMT engine, 1 = the general tcgen05 kernels, 2 = the shape-specialised
+ * tcgen05 kernels (halo-resident convolution / persistent pooling).  ksize/dil are read for "conv", G for "attn_pool".
+ * Tests assert this before comparing engines, so a silent fall-back to SIMT cannot pass as a tensor-core result.
+ * No counterpart in the reference (torch picks cuDNN / cuBLAS algorithms internally, modules.py:124-160). */
+int pb_tc_path(const char* op, int B, int L, int C, int G, int ksize, int dil);
+
 /* ---- sizing ------------------------------------------------------------------------------------ */
 size_t pb_workspace_bytes(const char* op, int M, int N, int K);
 

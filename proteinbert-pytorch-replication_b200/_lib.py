@@ -65,6 +65,7 @@ PROTOTYPES = {
     "pb_sigmoid_bwd": [_p, _p, _p, _p, _ll, _p],
     "pb_corrupt_pad": [_p] * 16 + [_i, _i, _i, _p],
     "pb_workspace_bytes": [C.c_char_p, _i, _i, _i],
+    "pb_tc_path": [C.c_char_p, _i, _i, _i, _i, _i, _i],
 }
 _RESTYPES = {"pb_last_error": C.c_char_p, "pb_launch_count": _ll, "pb_workspace_bytes": _sz, "pb_linear_tc_workspace": _sz}
 

@@ -3,6 +3,7 @@
 // the shape qualifies (see pb_tc_*); everything here stays as the parity engine and as the engine for
 // shapes the tensor-core tiling does not cover.
 // Reference call sites: modules.py:124-164 (layers), :205-217 (block forward), :49-60,:87-92 (attention).
+#include <string.h>
 #include "gemm_simt.cuh"
 #include "../../include/pb_b200.h"
 #include "tc_api.cuh"
@@ -883,6 +884,20 @@ int pb_attn_pool_bwd(const void* h, const void* wvT, const void* wv, const float
         }
     });
     return pb_check_launch("pb_attn_pool_bwd");
+}
+
+int pb_tc_path(const char* op, int B, int L, int C, int G, int ksize, int dil) {
+    if (op == nullptr) return 0;
+    if (!strcmp(op, "conv")) {
+        if (!pb_tc_conv_ok(B, L, C, ksize, dil)) return 0;
+        return (pb_tc_mode() != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil)) ? 2 : 1;
+    }
+    if (!strcmp(op, "local_linear")) return pb_tc_linear_ok(B, L, C) ? 1 : 0;
+    if (!strcmp(op, "attn_pool")) {
+        if (!pb_tc_attn_ok(B, L, C, G)) return 0;
+        return pb_tc_pool_ok(B, L, C, G) ? 2 : 1;
+    }
+    return 0;
 }
 
 }  // extern "C"

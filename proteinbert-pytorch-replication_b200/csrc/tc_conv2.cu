@@ -127,8 +127,10 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc_bf16(128, kC, 0, 0);
+#ifdef PB_CONV2_PROBE
             long long t_wait_full = 0, t_wait_a = 0;
             const long long t_begin = clock64();
+#endif
             for (int i = 0; i < n_iter; ++i) {
                 const int s = i % kStages;
                 const int conv = i / (p.ksize * 2), kc = (i / p.ksize) & 1, t = i % p.ksize;
@@ -137,12 +139,17 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 // row of the halo tile at which this tap's window starts
                 int row_off = kFwd ? half * (p.dil - d) + t * d : (2 * half - t) * d;
                 if (p.debug & 1) row_off &= ~7;
+#ifdef PB_CONV2_PROBE
                 long long c0 = clock64();
+#endif
                 if (t == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * 2 + kc], 0);
+#ifdef PB_CONV2_PROBE
                 long long c1 = clock64();
+#endif
                 mbar_wait(&full_bar[s], (i / kStages) & 1);
-                long long c2 = clock64();
-                t_wait_a += c1 - c0; t_wait_full += c2 - c1;
+#ifdef PB_CONV2_PROBE
+                t_wait_a += c1 - c0; t_wait_full += clock64() - c1;
+#endif
                 tc_fence_after();
                 // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start address
                 // field (bits 0..13), so they are formed by adding constants -- the issuing thread is the bottleneck
@@ -162,16 +169,21 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 if (kFwd && i == p.ksize * 2 - 1) umma_commit(&tmem_full_bar[0]);       // narrow conv: both sub-tiles complete
             }
             umma_commit(&tmem_full_bar[1]);
+#ifdef PB_CONV2_PROBE
             if (p.dbg && blockIdx.x == 0) {
                 const long long t_issue_end = clock64();
                 mbar_wait(&tmem_full_bar[1], 0);
                 const long long t_done = clock64();
                 p.dbg[0] = t_issue_end - t_begin; p.dbg[1] = t_wait_full; p.dbg[2] = t_wait_a; p.dbg[3] = t_done - t_begin;
             }
+#endif
         }
     } else {
         // ===== epilogue: warps 2..9; sub-tile = (warp-2)/4, TMEM lane quarter = warp % 4 =====
+#ifdef PB_CONV2_PROBE
         const long long e0 = clock64();
+        long long e1 = e0;
+#endif
         const int tile = (warp - 2) >> 2, q = warp & 3;
         const int row = tile * 128 + q * 32 + lane;                     // position inside the CTA's 256
         const size_t grow = ((size_t)b * p.L + l0 + row) * kC;
@@ -182,14 +194,15 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
         const int sw = (lane >> 1) & 3;                                 // 64B swizzle: 16-byte chunk ^= (row / 2) & 3
         const int lrow = l0 + tile * 128 + q * 32;
         float s_sum = 0.f, s_sq = 0.f;
-        long long e1 = e0;
         if (kFwd) {
             // ---- first half, under the MMAs of the dilated convolution: zn = acc + bn (stored), and the partial sum
             //      x + gelu(zn) + g2l goes back into the accumulator's TMEM columns (tcgen05.st) for the second half.
             //      x comes from the halo tile that feeds the MMAs.
             const int hrow = half * p.dil + row;
             mbar_wait(&tmem_full_bar[0], 0);
+#ifdef PB_CONV2_PROBE
             e1 = clock64();
+#endif
             tc_fence_after();
 #pragma unroll 1
             for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
@@ -260,7 +273,9 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             }
         } else {
             mbar_wait(&tmem_full_bar[1], 0);
+#ifdef PB_CONV2_PROBE
             e1 = clock64();
+#endif
             tc_fence_after();
 #pragma unroll 1
             for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
@@ -294,7 +309,9 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             if (lane == 0) { atomicAdd(&p.stats[2 * b], ds); atomicAdd(&p.stats[2 * b + 1], dq); }
         }
         tc_fence_before();
+#ifdef PB_CONV2_PROBE
         if (p.dbg && blockIdx.x == 0 && threadIdx.x == 64) { p.dbg[4] = e1 - e0; p.dbg[5] = clock64() - e1; }
+#endif
     }
     __syncthreads();
     if (warp == 1) {
@@ -319,7 +336,8 @@ int w_map(CUtensorMap* m, const void* base, int ksize) {
 template <bool kFwd, int kStages>
 int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv2Params p, int B, int L, cudaStream_t st) {
     const int half = p.ksize / 2;
-    { const char* e = getenv("PB_CONV2_DEBUG"); p.debug = e ? atoi(e) : 0; }
+    static const int debug_env = [] { const char* e = getenv("PB_CONV2_DEBUG"); return e ? atoi(e) : 0; }();   // read once
+    p.debug = debug_env;
     p.dbg = (unsigned long long*)pb_debug_ptr();
     p.hr[0] = kRows + 2 * half;
     p.hr[1] = kRows + 2 * half * p.dil;
@@ -346,7 +364,11 @@ int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv
     const size_t a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
     const size_t smem = 2 * a_buf + (size_t)kStages * kBTile + (kFwd ? 8 * 3 * 2048 : 0) + 1024 + 256;
     PB_REQUIRE(smem <= 232448, PB_ERR_UNSUPPORTED, "conv2: %zu bytes of shared memory needed", smem);
-    PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static size_t smem_set = 0;
+    if (smem_set != smem) {
+        PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
     PB_CUDA(pb_launch_pdl(tc_conv2_kernel<kFwd, kStages>, dim3(B * (L / kRows)), dim3(kThreads), smem, st, mA0m, mA0t, mA1m, mA1t,
                           mB0, mB1, mS0, mS1, mS2, p));
     pb_count_launch(1);

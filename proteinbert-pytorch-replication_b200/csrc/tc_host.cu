@@ -1,6 +1,8 @@
 // Host side of the tensor-core engine: CUtensorMap construction through the driver entry point, the
 // engine switch, and the vectorised bf16 LayerNorm-apply.
 #include <atomic>
+#include <stdlib.h>
+#include <string.h>
 #include <cudaTypedefs.h>
 #include "tc_common.cuh"
 #include "tc_api.cuh"
@@ -17,6 +19,20 @@ int pb_tc_mode() { return g_tc_enabled.load(std::memory_order_relaxed); }
 
 extern "C" int pb_set_tensor_cores(int enabled) { return g_tc_enabled.exchange(enabled < 0 ? 0 : enabled); }
 
+// Encoded maps are kept in a small per-thread direct-mapped cache keyed by every argument of the encode call: an eager
+// step re-creates the same ~200 maps per step (the conv kernels alone take nine each), and cuTensorMapEncodeTiled costs
+// about a microsecond of host time per map.  Per thread because forward runs on the caller's thread and backward on
+// autograd's worker: no lock on the launch path.  A map depends only on (address, shape, strides, box, swizzle), never on
+// the tensor's contents, so a cached copy stays valid when the allocator hands the same address out again.
+namespace {
+struct TmapKey {
+    const void* base; int rank, swizzle; uint64_t dims[3], strides[2]; uint32_t box[3];
+    bool operator==(const TmapKey& o) const { return memcmp(this, &o, sizeof(TmapKey)) == 0; }
+};
+struct TmapSlot { TmapKey key; CUtensorMap map; bool valid; };
+constexpr int kTmapSlots = 512;
+}  // namespace
+
 int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                       const uint32_t* box, int swizzle_bytes) {
     static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
@@ -27,7 +43,19 @@ int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64
         PB_REQUIRE(fn != nullptr && qres == cudaDriverEntryPointSuccess, PB_ERR_CUDA, "cuTensorMapEncodeTiled not available");
         encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
     }
+    PB_REQUIRE(rank >= 2 && rank <= 3, PB_ERR_SHAPE, "tensor maps of rank 2 or 3 only");
     PB_REQUIRE(((uintptr_t)base % 16) == 0, PB_ERR_SHAPE, "tensor map base address must be 16-byte aligned");
+    static thread_local TmapSlot* cache = nullptr;
+    if (cache == nullptr) cache = (TmapSlot*)calloc(kTmapSlots, sizeof(TmapSlot));
+    TmapKey key;
+    memset(&key, 0, sizeof(key));
+    key.base = base; key.rank = rank; key.swizzle = swizzle_bytes;
+    for (int i = 0; i < rank; ++i) { key.dims[i] = dims[i]; key.box[i] = box[i]; }
+    for (int i = 0; i + 1 < rank; ++i) key.strides[i] = strides_bytes[i];
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(key) / 8; ++i) { h ^= reinterpret_cast<const uint64_t*>(&key)[i]; h *= 1099511628211ull; }
+    TmapSlot* slot = cache ? &cache[(h ^ (h >> 29)) % kTmapSlots] : nullptr;
+    if (slot && slot->valid && slot->key == key) { *out = slot->map; return PB_OK; }
     cuuint64_t gdim[5];
     cuuint64_t gstr[4];
     cuuint32_t bdim[5], estr[5];
@@ -43,6 +71,7 @@ int pb_make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     PB_REQUIRE(r == CUDA_SUCCESS, PB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    if (slot) { slot->key = key; slot->map = *out; slot->valid = true; }
     return PB_OK;
 }
 

@@ -1,0 +1,237 @@
+"""GPU parity at the shapes that carry the performance claims (BASELINE.json configs 1, 2 and 4).
+
+Every number bench.py prints is measured at L = 512 (two 256-position convolution tiles per sample) or L = 2048 (eight);
+the tests here compare exactly those code paths -- a second tile whose left halo is real data, the tail tensor map
+crossing into the next tile, weight-gradient chunks past row 256 -- with the fp64 CPU oracle and with torch's conv1d,
+element-wise, and assert that the tcgen05 path (not the SIMT engine) produced the result.
+
+Tolerances are the ones of tests/test_gpu_parity.py; the bf16 bound for the cancellation-prone
+global-track tensors is absolute, relative to the largest global-track gradient -- stated at BF16_ABS.
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import assert_close_rel, rel_fro
+from oracle import model_oracle
+from test_gpu_parity import CANCELLATION_PRONE, MATH_ZERO, build_model, check_bf16, check_fp32, run_step
+
+pytestmark = pytest.mark.gpu
+
+CONFIG1 = dict(sequences_length=512, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=6)
+CONFIG4 = dict(sequences_length=2048, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=2)
+
+# bf16 precision, tensors whose gradient is a cancelling sum (global-track weights, W_parameter, the heads' Wv):
+# |g - g_ref|_F <= BF16_REL * |g_ref|_F + BF16_ABS * gscale * sqrt(numel), gscale = largest |gradient entry| of the model.
+BF16_REL, BF16_ABS = 1e-1, 2e-3
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import proteinbert_b200
+    proteinbert_b200._lib.check(proteinbert_b200._lib.lib().pb_device_ok(0), "pb_device_ok")
+    return proteinbert_b200
+
+
+def oracle_case(cfg, B, seed):
+    params = model_oracle.init_params(seed=seed, **cfg)
+    g = torch.Generator().manual_seed(seed + 1)
+    for k in params:          # LayerNorm affines away from (1, 0) so that dgamma/dbeta and the affine itself are exercised
+        if "norm" in k:
+            params[k] = params[k] + (0.2 if k.endswith("weight") else 0.1) * torch.randn(params[k].shape, generator=g)
+    batch = model_oracle.synthetic_batch(B, cfg["sequences_length"], cfg["num_annotations"], seed=seed + 2)
+    p64 = {k: v.double() for k, v in params.items()}
+    b64 = (batch[0], batch[1].double(), batch[2], batch[3].double(), batch[4], batch[5])
+    return params, batch, model_oracle.loss_and_grads(p64, b64, attention="closed_form")
+
+
+@pytest.fixture(scope="module")
+def config1_ref():
+    return oracle_case(CONFIG1, 8, 21)
+
+
+@pytest.fixture(scope="module")
+def config4_ref():
+    return oracle_case(CONFIG4, 2, 31)
+
+
+def assert_tensor_core_paths(pb, B, cfg):
+    lib = pb._lib.lib()
+    L, C, G = cfg["sequences_length"], cfg["local_dim"], cfg["global_dim"]
+    assert lib.pb_tc_path(b"conv", B, L, C, G, 9, 5) == 2, "conv pair did not take the halo-resident tcgen05 kernel"
+    assert lib.pb_tc_path(b"local_linear", B, L, C, G, 0, 0) >= 1, "local linear fell back to SIMT"
+    assert lib.pb_tc_path(b"attn_pool", B, L, C, G, 0, 0) >= 1, "attention pooling fell back to SIMT"
+
+
+def check_bf16_cancellation_prone(grads, ref_grads, what=""):
+    """the set check_bf16 leaves to a finiteness test, held to an absolute bound against the fp64 oracle."""
+    gscale = max(float(v.abs().max()) for v in ref_grads.values())
+    worst = []
+    for k, ref in ref_grads.items():
+        if any(s in k for s in MATH_ZERO):
+            continue
+        if not (any(s in k for s in CANCELLATION_PRONE) or "heads" in k):
+            continue
+        err = float((grads[k].double().cpu() - ref.double()).norm())
+        bound = BF16_REL * float(ref.double().norm()) + BF16_ABS * gscale * np.sqrt(ref.numel())
+        worst.append((err / bound, k, err, float(ref.double().norm())))
+    worst.sort(reverse=True)
+    for r, k, err, nrm in worst[:6]:
+        print(f"  {what}{k}: |diff| {err:.3e} |ref| {nrm:.3e} ({r:.2f} of bound)")
+    assert worst and worst[0][0] <= 1.0, worst[0]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config1_full_step_against_fp64_oracle(pb, config1_ref, precision):
+    """BASELINE.json configs[0]: batch 8, seq 512, 6 blocks, 128/512, 8943 annotations."""
+    params, batch, ref = config1_ref
+    model = build_model(pb, CONFIG1, params, precision)
+    p_local, p_global, loss, grads = run_step(pb, model, batch)
+    if precision == "fp32":
+        assert_close_rel(p_local, ref[0], 1e-4, what="p_local")
+        assert_close_rel(p_global, ref[1], 1e-4, what="p_global")
+        assert abs(float(loss) - float(ref[2])) <= 1e-4 * abs(float(ref[2]))
+        check_fp32(grads, ref[3], "config1/")
+    else:
+        assert_tensor_core_paths(pb, 8, CONFIG1)
+        check_bf16(p_local, p_global, loss, grads, ref)
+        check_bf16_cancellation_prone(grads, ref[3], "config1/")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config4_shape_full_step_against_fp64_oracle(pb, config4_ref, precision):
+    """The long-sequence shape of BASELINE.json configs[3] (L = 2048: eight convolution tiles per sample), 2 blocks."""
+    params, batch, ref = config4_ref
+    model = build_model(pb, CONFIG4, params, precision)
+    p_local, p_global, loss, grads = run_step(pb, model, batch)
+    if precision == "fp32":
+        assert_close_rel(p_local, ref[0], 1e-4, what="p_local")
+        assert_close_rel(p_global, ref[1], 1e-4, what="p_global")
+        assert abs(float(loss) - float(ref[2])) <= 1e-4 * abs(float(ref[2]))
+        check_fp32(grads, ref[3], "config4/")
+    else:
+        assert_tensor_core_paths(pb, 2, CONFIG4)
+        check_bf16(p_local, p_global, loss, grads, ref)
+        check_bf16_cancellation_prone(grads, ref[3], "config4/")
+
+
+def test_config2_batch64_graphed_step_matches_eager_and_oracle_sample(pb):
+    """configs[1] itself (batch 64, seq 512, bf16) through GraphedPretrainStep, the object bench.py times: the loss and
+    every gradient of the replayed graph agree with the eager step, and the loss agrees with the CPU oracle's forward
+    on the same weights and batch within the bf16 bound."""
+    torch.manual_seed(0)
+    model = pb.ProteinBERT(device="cuda", precision="bf16", **CONFIG1)
+    b = [t.cuda() for t in pb.data_processing.synthetic_batch(64, 512, 8943, seed=5)]
+    X, Y, W = {"local": b[0], "global": b[1]}, {"local": b[2], "global": b[3]}, {"local": b[4], "global": b[5]}
+    assert_tensor_core_paths(pb, 64, CONFIG1)
+    loss_e = float(pb.pretraining_step(model, X, Y, W))
+    ref = {n: p.grad.clone() for n, p in model.named_parameters()}
+    step = pb.GraphedPretrainStep(model, X, Y, W, warmup=1)
+    loss_g = float(step(X, Y, W))
+    torch.cuda.synchronize()
+    assert abs(loss_g - loss_e) <= 1e-6 * abs(loss_e)
+    for n, p in model.named_parameters():
+        assert rel_fro(p.grad, ref[n]) < 2e-3 or float(ref[n].abs().max()) < 1e-6, n
+    # the same weights through the fp32 CPU oracle (fp64 would take a minute at batch 64): loss within the bf16 bound
+    params = {k: v.detach().cpu() for k, v in model.state_dict().items()}
+    params.update({k: v.detach().cpu() for k, v in model.head_tensors().items()})
+    cb = [t.cpu() for t in b]
+    with torch.no_grad():
+        pl, pg = model_oracle.forward(params, cb[0], cb[1], attention="closed_form")
+        ref_loss = float(model_oracle.pretraining_loss(pl, pg, cb[2], cb[3], cb[4], cb[5]))
+    assert abs(loss_e - ref_loss) <= 2e-3 * abs(ref_loss), (loss_e, ref_loss)
+
+
+def _conv_case(B, L, seed):
+    g = torch.Generator().manual_seed(seed)
+    C, KS = 128, 9
+    x = torch.randn(B, L, C, generator=g).bfloat16()
+    wn = (torch.randn(C, C, KS, generator=g) * 0.05)
+    ww = (torch.randn(C, C, KS, generator=g) * 0.05)
+    bn, bw, g2l = torch.randn(C, generator=g), torch.randn(C, generator=g), torch.randn(B, C, generator=g)
+    return x, wn, ww, bn, bw, g2l
+
+
+def _row_windows(L):
+    """Row ranges asserted separately: both sequence ends and every 256-row tile seam (+-20 rows: the dilated halo)."""
+    wins = [("first rows", slice(0, 20)), ("last rows", slice(L - 20, L))]
+    for seam in range(256, L, 256):
+        wins.append((f"seam {seam}", slice(seam - 20, seam + 20)))
+    return wins
+
+
+@pytest.mark.parametrize("B,L", [(3, 512), (2, 2048)])
+def test_conv_pair_forward_bf16_across_tile_seams(pb, B, L):
+    """pb_conv_pair_fwd (tcgen05 halo kernel) against conv1d in fp64 on the bf16-rounded operands, element-wise."""
+    from proteinbert_b200 import ops
+    lib = pb._lib.lib()
+    C, KS, DIL = 128, 9, 5
+    assert lib.pb_tc_path(b"conv", B, L, C, 0, KS, DIL) == 2
+    x, wn, ww, bn, bw, g2l = _conv_case(B, L, 40 + L)
+    xd = x.cuda()
+    wn_f, _ = ops.conv_pack(wn.cuda(), 1)
+    ww_f, _ = ops.conv_pack(ww.cuda(), 1)
+    bnd, bwd, gd = bn.cuda(), bw.cuda(), g2l.cuda()
+    zn, zw, u = torch.empty_like(xd), torch.empty_like(xd), torch.empty_like(xd)
+    stats = torch.zeros(B, 2, dtype=torch.float64, device="cuda")
+    ops._call("pb_conv_pair_fwd", xd.data_ptr(), wn_f.data_ptr(), ww_f.data_ptr(), bnd.data_ptr(), bwd.data_ptr(), gd.data_ptr(),
+              zn.data_ptr(), zw.data_ptr(), u.data_ptr(), stats.data_ptr(), B, L, C, KS, DIL, 1, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    xr = x.double().permute(0, 2, 1)
+    rn = torch.nn.functional.conv1d(xr, wn.bfloat16().double(), bn.double(), padding="same").permute(0, 2, 1)
+    rw = torch.nn.functional.conv1d(xr, ww.bfloat16().double(), bw.double(), padding="same", dilation=DIL).permute(0, 2, 1)
+    # u is formed from the STORED (bf16) pre-activations, as the kernel does
+    ru = x.double() + model_oracle.gelu(zn.double().cpu()) + model_oracle.gelu(zw.double().cpu()) + g2l.double().unsqueeze(1)
+    for name, got, ref in (("zn", zn, rn), ("zw", zw, rw), ("u", u, ru)):
+        got = got.double().cpu()
+        assert rel_fro(got, ref) < 4e-3, (name, rel_fro(got, ref))
+        for wname, rows in _row_windows(L):
+            assert rel_fro(got[:, rows], ref[:, rows]) < 4e-3, (name, wname, rel_fro(got[:, rows], ref[:, rows]))
+        # element-wise: a wrong halo row shows up as an O(1) error in single positions, far above bf16 rounding
+        assert float((got - ref).abs().max()) <= 2e-2 * max(1.0, float(ref.abs().max())), name
+    us = u.double().cpu()
+    assert_close_rel(stats[:, 0], us.sum((1, 2)), 1e-5, floor=1e-2, what="sum u")
+    assert_close_rel(stats[:, 1], (us * us).sum((1, 2)), 1e-5, what="sum u^2")
+
+
+@pytest.mark.parametrize("B,L", [(3, 512), (2, 2048)])
+def test_conv_pair_backward_bf16_across_tile_seams(pb, B, L):
+    """pb_conv_pair_bwd (tcgen05 data gradient + three-tap weight-gradient kernel) against torch autograd of conv1d in
+    fp64 on the bf16-rounded operands: dx element-wise incl. the tile seams, dWn, dWw."""
+    from proteinbert_b200 import ops
+    lib = pb._lib.lib()
+    C, KS, DIL = 128, 9, 5
+    assert lib.pb_tc_path(b"conv", B, L, C, 0, KS, DIL) == 2
+    x, wn, ww, _, _, _ = _conv_case(B, L, 50 + L)
+    g = torch.Generator().manual_seed(60 + L)
+    du = (torch.randn(B, L, C, generator=g) * 0.1).bfloat16()
+    dzn = (torch.randn(B, L, C, generator=g) * 0.1).bfloat16()
+    dzw = (torch.randn(B, L, C, generator=g) * 0.1).bfloat16()
+    xd, dud, dznd, dzwd = x.cuda(), du.cuda(), dzn.cuda(), dzw.cuda()
+    _, wn_b = ops.conv_pack(wn.cuda(), 1)
+    _, ww_b = ops.conv_pack(ww.cuda(), 1)
+    dx = torch.empty_like(xd)
+    dWn, dWw = torch.empty(C, C, KS, device="cuda"), torch.empty(C, C, KS, device="cuda")
+    dev = torch.device("cuda", torch.cuda.current_device())
+    # zn = zw = NULL: the GELU gradients dzn / dzw are inputs (the fused LayerNorm-backward kernel produces them)
+    ops._call("pb_conv_pair_bwd", dud.data_ptr(), None, None, xd.data_ptr(), wn_b.data_ptr(), ww_b.data_ptr(), dznd.data_ptr(),
+              dzwd.data_ptr(), dx.data_ptr(), dWn.data_ptr(), dWw.data_ptr(), None, None, None, B, L, C, KS, DIL, 1,
+              *ops._wgrad_ws(dev), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    xr = x.double().permute(0, 2, 1).requires_grad_(True)
+    wnr, wwr = wn.bfloat16().double().requires_grad_(True), ww.bfloat16().double().requires_grad_(True)
+    yn = torch.nn.functional.conv1d(xr, wnr, None, padding="same")
+    yw = torch.nn.functional.conv1d(xr, wwr, None, padding="same", dilation=DIL)
+    ((yn * dzn.double().permute(0, 2, 1)).sum() + (yw * dzw.double().permute(0, 2, 1)).sum()).backward()
+    dx_ref = du.double() + xr.grad.permute(0, 2, 1)
+    got = dx.double().cpu()
+    assert rel_fro(got, dx_ref) < 4e-3, rel_fro(got, dx_ref)
+    for wname, rows in _row_windows(L):
+        assert rel_fro(got[:, rows], dx_ref[:, rows]) < 4e-3, (wname, rel_fro(got[:, rows], dx_ref[:, rows]))
+    assert float((got - dx_ref).abs().max()) <= 2e-2 * max(1.0, float(dx_ref.abs().max()))
+    # weight gradients: wnr is bf16-rounded but its gradient does not depend on its value
+    assert rel_fro(dWn, wnr.grad) < 2e-3, rel_fro(dWn, wnr.grad)
+    assert rel_fro(dWw, wwr.grad) < 2e-3, rel_fro(dWw, wwr.grad)
+    for t in range(KS):        # every tap separately: a shifted halo row corrupts single taps, not the whole tensor
+        assert rel_fro(dWn[:, :, t], wnr.grad[:, :, t]) < 3e-3, ("dWn tap", t)
+        assert rel_fro(dWw[:, :, t], wwr.grad[:, :, t]) < 3e-3, ("dWw tap", t)

@@ -18,8 +18,19 @@ def pb():
     return proteinbert_b200
 
 
-def both_engines(pb, fn, modes=(0, 1)):
+def both_engines(pb, fn, modes=(0, 1), op=None):
+    """Run fn on the SIMT engine and on the tensor-core engine.  `op` names the C-ABI op family whose engine choice is
+    asserted first (pb_tc_path), so that a shape which silently fell back to SIMT cannot compare SIMT with SIMT."""
     lib = pb._lib.lib()
+    if op is not None:
+        for mode in modes:
+            lib.pb_set_tensor_cores(mode)
+            try:
+                path = lib.pb_tc_path(op.encode(), B, L, C, G, KS, DIL)
+            finally:
+                lib.pb_set_tensor_cores(1)
+            want = {0: 0, 1: 2 if op != "local_linear" else 1, 4: 1}[mode]
+            assert path == want, f"{op}: engine switch {mode} takes path {path}, expected {want}"
     outs = []
     for enabled in modes:
         lib.pb_set_tensor_cores(enabled)
@@ -66,7 +77,7 @@ def test_conv_pair_forward(pb):
                   zn.data_ptr(), zw.data_ptr(), u.data_ptr(), stats.data_ptr(), B, L, C, KS, DIL, 1, torch.cuda.current_stream().cuda_stream)
         return zn, zw, u, stats
 
-    simt, tc = both_engines(pb, run)
+    simt, tc = both_engines(pb, run, op="conv")
     compare(["zn", "zw", "u", "stats"], simt, tc)
     # and against torch conv1d in fp64 on the bf16-rounded operands (edge rows exercise the zero padding)
     xr = x.double().cpu().permute(0, 2, 1)
@@ -93,7 +104,7 @@ def test_conv_pair_backward(pb):
                   dg2l.data_ptr(), B, L, C, KS, DIL, 1, *wsargs(pb), torch.cuda.current_stream().cuda_stream)
         return dx, dWn, dWw, dbn, dbw, dg2l
 
-    simt, tc = both_engines(pb, run)
+    simt, tc = both_engines(pb, run, op="conv")
     compare(["dx", "dWn", "dWw", "dbn", "dbw", "dg2l"], simt, tc)
 
 
@@ -116,7 +127,7 @@ def test_local_linear(pb):
                   dh.data_ptr(), dW.data_ptr(), db.data_ptr(), B, L, C, 1, *wsargs(pb), st)
         return z, u2, stats, dh, dW, db
 
-    simt, tc = both_engines(pb, run)
+    simt, tc = both_engines(pb, run, op="local_linear")
     compare(["z", "u2", "stats", "dh", "dW", "db"], simt, tc)
 
 
@@ -139,7 +150,7 @@ def test_attention_pool(pb):
                   dh.data_ptr(), dWvT.data_ptr(), 0, B, L, C, G, 1, *wsargs(pb), st)
         return pool, dzv, dh, dWvT
 
-    simt, tc = both_engines(pb, run)
+    simt, tc = both_engines(pb, run, op="attn_pool")
     compare(["pool", "dzv", "dh", "dWvT"], simt, tc)
     ref = (torch.nn.functional.gelu(h.double().cpu() @ wvw.double().cpu())).sum(1)
     assert rel_fro(tc[0], ref) < 2e-3
@@ -183,7 +194,7 @@ def test_conv_pair_both_kernel_generations(pb, mode):
                   dg2l.data_ptr(), B, L, C, KS, DIL, 1, *wsargs(pb), st)
         return zn, zw, u, stats, dx
 
-    simt, tc = both_engines(pb, run, modes=(0, mode))
+    simt, tc = both_engines(pb, run, modes=(0, mode), op="conv")
     compare(["zn", "zw", "u", "stats", "dx"], simt, tc)
 
 
