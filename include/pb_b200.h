@@ -116,8 +116,10 @@ int pb_linear_fwd(const float* X, const float* W, const float* bias, float* Z, f
  * counterpart in the reference.  The split-K partial sums live in a 4 MiB device array that is part of the
  * library image (held by every GPU that loads the library, until exit), so the call allocates nothing.
  * Limit: M*N <= 32768 output elements per call (larger -> PB_ERR_UNSUPPORTED; use pb_linear_fwd).  The first
- * call on each device looks the array's address up (cudaGetSymbolAddress): make it before any stream capture
- * on that device.  All calls on a device share the array: calls that overlap on the GPU race -- serialise them.
+ * call on each device looks the array's address up (cudaGetSymbolAddress; under lazy module loading this may also load
+ * the library's device code): make it before any stream capture on that device, with that device current -- `stream`
+ * must belong to the current device.  All calls on a device share the array: calls that overlap on the GPU race --
+ * serialise them.
  * Nothing in the array needs clearing between calls (every partial is rewritten before it is read).           */
 int pb_linear_fwd_noalloc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N,
                           int K, int act, void* stream);

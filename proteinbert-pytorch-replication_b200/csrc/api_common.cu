@@ -167,6 +167,7 @@ int pb_adam_step(const pb_adam_desc* descs_dev, int n, float lr, double beta1, d
                  void* stream) {
     if (n <= 0) return PB_OK;
     PB_REQUIRE(descs_dev != nullptr && step >= 1, PB_ERR_SHAPE, "adam_step: null table or step < 1");
+    PB_REQUIRE(n <= 65535, PB_ERR_SHAPE, "adam_step: %d table rows exceed the 65535 one launch covers (gridDim.y); split the table", n);
     const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
     adam_kernel<<<dim3(32, n), 256, 0, (cudaStream_t)stream>>>(descs_dev, (float)(lr / bc1), (float)beta1, (float)beta2, (float)(1.0 / sqrt(bc2)), eps,
                                                               weight_decay, (float)(1.0 - beta1), (float)(1.0 - beta2));
@@ -177,6 +178,7 @@ int pb_adam_step(const pb_adam_desc* descs_dev, int n, float lr, double beta1, d
 int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream) {
     if (n <= 0) return PB_OK;
     PB_REQUIRE(chunks_dev != nullptr && flat != nullptr, PB_ERR_SHAPE, "flat_copy: null argument");
+    PB_REQUIRE(n <= 65535, PB_ERR_SHAPE, "flat_copy: %d table rows exceed the 65535 one launch covers (gridDim.y); split the table", n);
     flat_copy_kernel<<<dim3(8, n), 256, 0, (cudaStream_t)stream>>>(chunks_dev, flat, to_flat, scale);
     pb_count_launch(1);
     return pb_check_launch("pb_flat_copy");
@@ -185,6 +187,7 @@ int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_fla
 int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream) {
     if (n <= 0) return PB_OK;
     PB_REQUIRE(jobs_dev != nullptr, PB_ERR_SHAPE, "stage_weights: null job table");
+    PB_REQUIRE(n <= 65535, PB_ERR_SHAPE, "stage_weights: %d jobs exceed the 65535 one launch covers (gridDim.y); split the table", n);
     dim3 grid(96, n);
     if (dt == PB_F32) stage_weights_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);
     else if (dt == PB_BF16) stage_weights_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>(jobs_dev);

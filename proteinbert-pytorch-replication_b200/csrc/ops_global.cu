@@ -1,5 +1,6 @@
 // Global-track operators (all float, M = batch rows): dense layers with split-K, and the
 // residual + LayerNorm over G.  Reference call sites: modules.py:166-199,208,221-229,255-262,286-293.
+#include <atomic>
 #include "gemm_simt.cuh"
 #include "../../include/pb_b200.h"
 
@@ -280,14 +281,17 @@ int pb_res_ln_rows_bwd(const float* dy, const float* gamma, const float* xhat, c
 //
 // Set-up: the array's device address is looked up once per device with cudaGetSymbolAddress, by the first
 // call made while that device is current (the array's name is only a host-side handle, it is not usable as
-// a pointer in a launch).  Make that first call before starting any stream capture on that device.
+// a pointer in a launch).  Make that first call before starting any stream capture on that device: with lazy module
+// loading the look-up may load this library's device code onto the GPU, which is not permitted during capture.  The
+// address is cached per device index of the CURRENT device, so `stream` must belong to the current device, and the
+// cache does not survive a cudaDeviceReset.
 // =================================================================================================
 #define PB_NOALLOC_MAX_MN 32768
 #define PB_NOALLOC_SCRATCH_FLOATS (kMaxSplit * PB_NOALLOC_MAX_MN)          /* 32 splits x 32768 floats = 4 MiB */
 #define PB_NOALLOC_MAX_DEVICES 64
 
 static __device__ __align__(256) float g_linear_scratch[PB_NOALLOC_SCRATCH_FLOATS];
-static float* g_linear_scratch_addr[PB_NOALLOC_MAX_DEVICES] = {nullptr};
+static std::atomic<float*> g_linear_scratch_addr[PB_NOALLOC_MAX_DEVICES];      // zero-initialised; filled once per device
 
 extern "C" int pb_linear_fwd_noalloc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
                                      int act, void* stream) {
@@ -298,13 +302,14 @@ extern "C" int pb_linear_fwd_noalloc(const float* X, const float* W, const float
     int dev = -1;
     PB_CUDA(cudaGetDevice(&dev));
     PB_REQUIRE(dev >= 0 && dev < PB_NOALLOC_MAX_DEVICES, PB_ERR_UNSUPPORTED, "linear_fwd_noalloc: device index %d not supported", dev);
-    if (g_linear_scratch_addr[dev] == nullptr) {            // once per device, with that device current
+    float* ws = g_linear_scratch_addr[dev].load(std::memory_order_acquire);
+    if (ws == nullptr) {                                    // once per device, with that device current
         float* ptr = nullptr;
         PB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_linear_scratch));
         PB_REQUIRE(ptr != nullptr, PB_ERR_CUDA, "linear_fwd_noalloc: cudaGetSymbolAddress returned a null address");
-        g_linear_scratch_addr[dev] = ptr;
+        g_linear_scratch_addr[dev].store(ptr, std::memory_order_release);   // racing threads store the same value
+        ws = ptr;                                           // a real device address; never the symbol name itself
     }
-    float* ws = g_linear_scratch_addr[dev];                 // a real device address; never the symbol name itself
     cudaStream_t st = (cudaStream_t)stream;
     const int tiles = ceil_div(N, 64) * ceil_div(M, 64);
     const int nsplit = pick_split(tiles, K);                // <= kMaxSplit, so nsplit*M*N floats always fit

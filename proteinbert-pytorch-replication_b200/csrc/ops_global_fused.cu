@@ -14,8 +14,18 @@
 //                 ([rows x K] fp32) and contracts it against its [K x 8] weight slice.
 // Phases are separated by a cooperative grid barrier (the grids are <= 148 CTAs of one wave, launched with
 // cudaLaunchCooperativeKernel), so the row-wise results never have to be recomputed per column slice.
+//
+// Two things bound these kernels in round 1 (profiles/r01_global_phases.md): staging the shared A operand with
+// LDG + scalar STS (3.8 us for 128 KB per CTA) and the scalar-FMA 64 x 8 x K product (1.7 - 5 us).  Now
+//   * operands that are plain copies arrive by TMA bulk copies (cp.async.bulk, one per row into a row pitch of K + 4
+//     floats, completion on an mbarrier): no register round trip, no store-side bank conflicts, and the copies of
+//     weights that do not depend on the previous kernel are issued before griddepcontrol.wait;
+//   * the product runs on the tensor cores through warp-level mma.sync.m16n8k8 TF32 with the error-compensated
+//     three-product split (a = hi + lo, b = hi + lo; hi*hi + hi*lo + lo*hi), which keeps fp32-level accuracy
+//     (relative error ~2^-22 per product): 16 warps = (row tiles of 16) x (K groups), partials reduced through shared
+//     memory.  The pitch K + 4 makes the A-fragment reads (8 rows x 4 consecutive floats) bank-conflict free.
 #include <cooperative_groups.h>
-#include "common.cuh"
+#include "tc_common.cuh"
 #include "../../include/pb_b200.h"
 
 namespace cg = cooperative_groups;
@@ -29,11 +39,39 @@ constexpr int kThreads = 512;
 constexpr float kEps = 1e-5f;
 constexpr int kQ = 2;             // row phases / dW row sweep: up to kQ * 512 = 1024 columns
 
+constexpr int kPad = 4;           // A tile row pitch = K + kPad floats: 16-byte aligned rows, conflict-free mma fragment reads
+
+#ifdef PB_GLOBAL_PROBE            // phase timestamps for scripts/global_phase_probe.py: compile-time only
 __device__ __forceinline__ void stamp(unsigned long long* dbg, int slot) {
     if (dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
         dbg[slot] = t;
+    }
+}
+#else
+__device__ __forceinline__ void stamp(unsigned long long*, int) {}
+#endif
+
+// ---- TMA bulk row copies: rows [row0, row0 + mt) of a row-major [*, ld] fp32 tensor -> A_s rows of pitch lda ----------
+// Called by ONE warp.  K * 4 bytes per row (K % 4 == 0), source rows 16-byte aligned (ld % 4 == 0).  Completion: `bar`
+// receives mt * K * 4 bytes; the caller waits on it with the barrier's current parity.
+__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tma_rows(float* A_s, int lda, const float* src, size_t ld, int row0, int mt, int K, uint64_t* bar) {
+    const int lane = threadIdx.x & 31;
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)mt * (uint32_t)K * 4u);
+    __syncwarp();
+    for (int r = lane; r < mt; r += 32) bulk_copy_g2s(A_s + (size_t)r * lda, src + (size_t)(row0 + r) * ld, (uint32_t)K * 4u, bar);
+}
+__device__ __forceinline__ void zero_rows(float* A_s, int lda, int mt, int MT, int K) {      // rows mt .. MT-1 (ragged last tile)
+    const int kv = K / 4;
+    for (int i = threadIdx.x; i < (MT - mt) * kv; i += blockDim.x) {
+        const int r = mt + i / kv, k = (i % kv) * 4;
+        *reinterpret_cast<float4*>(A_s + (size_t)r * lda + k) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 }
 
@@ -42,35 +80,57 @@ __host__ __device__ __forceinline__ int row_tile_of(int K) { return K <= 704 ? 6
 __device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ float4 ld4cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
-// ---- CTA-level product: out[r][j] = sum_k A_s[r*lda + k] * Bt_s[k*8 + j],  r < MT, j < 8, k < Kd ---------
-// thread (r = tid % MT, ks = tid / MT) accumulates the k = ks, ks + nks, ... slice; partials are combined through
-// red_s [nks][MT][8].  The result is returned in out[] for threads with ks == 0 (tid < MT).
+// ---- CTA-level product: out[r][j] = sum_k A_s[r*lda + k] * Bt_s[k*8 + j],  r < MT, j < 8, k < Kd -----------------
+// Tensor cores, warp-level: mma.sync.m16n8k8 TF32 x 3 (error-compensated split, see the file header).  Warp w owns row
+// tile w % (MT/16) and K group w / (MT/16); the K groups' partial tiles are combined through red_s [groups][MT][8].
+// The result is returned in out[] for threads tid < MT (row tid).  MT in {16, 32, 64}, Kd % 8 == 0, lda % 32 == 4.
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
 __device__ __forceinline__ void cta_gemm8(const float* A_s, int lda, const float* Bt_s, int Kd, int MT, float* red_s,
                                           float (&out)[kNT]) {
-    const int r = threadIdx.x % MT, ks = threadIdx.x / MT, nks = kThreads / MT;
-    float acc[kNT];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int nmt = MT >> 4, nkg = (kThreads / 32) / nmt;
+    const int mtile = warp % nmt, kg = warp / nmt;
+    const int steps = Kd >> 3, s0 = kg * steps / nkg, s1 = (kg + 1) * steps / nkg;
+    float c[4] = {0.f, 0.f, 0.f, 0.f};
+    const float* a0p = A_s + (size_t)(mtile * 16 + g) * lda + t;
+    const float* a1p = a0p + 8 * lda;
+#pragma unroll 2
+    for (int s = s0; s < s1; ++s) {
+        const int k = s << 3;
+        const float af[4] = {a0p[k], a1p[k], a0p[k + 4], a1p[k + 4]};
+        const float bf[2] = {Bt_s[(k + t) * kNT + g], Bt_s[(k + t + 4) * kNT + g]};
+        uint32_t ah[4], al[4], bh[2], bl[2];
 #pragma unroll
-    for (int j = 0; j < kNT; ++j) acc[j] = 0.f;
-    const float* a = A_s + (size_t)r * lda;
-#pragma unroll 8
-    for (int k = ks; k < Kd; k += nks) {
-        const float av = a[k];
-        const float4 b0 = *reinterpret_cast<const float4*>(Bt_s + k * kNT);
-        const float4 b1 = *reinterpret_cast<const float4*>(Bt_s + k * kNT + 4);
-        acc[0] = fmaf(av, b0.x, acc[0]); acc[1] = fmaf(av, b0.y, acc[1]);
-        acc[2] = fmaf(av, b0.z, acc[2]); acc[3] = fmaf(av, b0.w, acc[3]);
-        acc[4] = fmaf(av, b1.x, acc[4]); acc[5] = fmaf(av, b1.y, acc[5]);
-        acc[6] = fmaf(av, b1.z, acc[6]); acc[7] = fmaf(av, b1.w, acc[7]);
+        for (int i = 0; i < 4; ++i) { ah[i] = to_tf32(af[i]); al[i] = to_tf32(af[i] - __uint_as_float(ah[i])); }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) { bh[i] = to_tf32(bf[i]); bl[i] = to_tf32(bf[i] - __uint_as_float(bh[i])); }
+        mma_tf32(c, al, bh);                   // small terms first
+        mma_tf32(c, ah, bl);
+        mma_tf32(c, ah, bh);
     }
-#pragma unroll
-    for (int j = 0; j < kNT; ++j) red_s[((size_t)ks * MT + r) * kNT + j] = acc[j];
+    {
+        float* r0 = red_s + ((size_t)kg * MT + mtile * 16 + g) * kNT + 2 * t;
+        r0[0] = c[0]; r0[1] = c[1];
+        r0[8 * kNT] = c[2]; r0[8 * kNT + 1] = c[3];
+    }
     __syncthreads();
-    if (ks == 0) {
+    if (threadIdx.x < MT) {
 #pragma unroll
-        for (int j = 0; j < kNT; ++j) {
-            float s = 0.f;
-            for (int q = 0; q < nks; ++q) s += red_s[((size_t)q * MT + r) * kNT + j];
-            out[j] = s;
+        for (int j = 0; j < kNT; ++j) out[j] = 0.f;
+        for (int q = 0; q < nkg; ++q) {
+            const float4 v0 = *reinterpret_cast<const float4*>(red_s + ((size_t)q * MT + threadIdx.x) * kNT);
+            const float4 v1 = *reinterpret_cast<const float4*>(red_s + ((size_t)q * MT + threadIdx.x) * kNT + 4);
+            out[0] += v0.x; out[1] += v0.y; out[2] += v0.z; out[3] += v0.w;
+            out[4] += v1.x; out[5] += v1.y; out[6] += v1.z; out[7] += v1.w;
         }
     }
     __syncthreads();
@@ -124,8 +184,7 @@ __device__ __forceinline__ void fill_tile(float* A_s, int lda, int MT, int mt, i
                 const int r = i / kv, k = (i - r * kv) * 4;
                 float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (r < mt) o = combine(v[u][0], v[u][1]);
-                float* d = A_s + (size_t)r * lda + k;
-                d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w;
+                *reinterpret_cast<float4*>(A_s + (size_t)r * lda + k) = o;
             }
         }
     }
@@ -188,22 +247,29 @@ struct PreFwd {
 
 __global__ void __launch_bounds__(kThreads, 1) global_pre_fwd_kernel(PreFwd p) {
     extern __shared__ __align__(16) float sm[];
-    const int K = p.G, MT = row_tile_of(K), lda = K + 1;
+    __shared__ __align__(8) uint64_t bar;
+    const int K = p.G, MT = row_tile_of(K), lda = K + kPad;
     float* A_s = sm;                                   // [MT][lda]
     float* Bt_s = A_s + (size_t)MT * lda;              // [K][8]
-    float* red_s = Bt_s + (size_t)K * kNT;             // [512/MT][MT][8] = [512*8]
-    pdl_wait();
+    float* red_s = Bt_s + (size_t)K * kNT;             // [16 warps' partial tiles] <= [512*8]
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
     const int n0 = blockIdx.x * kNT;                   // column in the concatenated [C + G] output
     const bool is_g2l = n0 < p.C;                      // slices never straddle (C % 8 == 0)
     const float* W = is_g2l ? p.W1 : p.W3;
     const float* bias = is_g2l ? p.b1 : p.b3;
     const int c0 = is_g2l ? n0 : n0 - p.C;
     const int ncols = is_g2l ? p.C : p.G;
-    load_bt_rows(Bt_s, W, K, c0, K);
+    load_bt_rows(Bt_s, W, K, c0, K);                   // weights do not depend on the previous kernel: before the wait
+    __syncthreads();
+    pdl_wait();
+    uint32_t phase = 0;
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
-        __syncthreads();
-        fill_tile<1, false>(A_s, lda, MT, mt, K, p.g, nullptr, K, row0, Copy4());
+        __syncthreads();                               // the previous tile's product has finished reading A_s
+        if (threadIdx.x < 32) tma_rows(A_s, lda, p.g, K, row0, mt, K, &bar);
+        zero_rows(A_s, lda, mt, MT, K);
+        mbar_wait(&bar, phase);
+        phase ^= 1;
         __syncthreads();
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, K, MT, red_s, out);
@@ -239,20 +305,24 @@ struct PreBwd {
 template <bool kDz3Ready>
 __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     extern __shared__ __align__(16) float sm[];
-    const int G = p.G, C = p.C, KA = G + C, MT = row_tile_of(KA), lda = KA + 1;
+    const int G = p.G, C = p.C, KA = G + C, MT = row_tile_of(KA), lda = KA + kPad;
     float* A_s = sm;                                   // [MT][lda] = [dz3 | dzg]
     float* Bt_s = A_s + (size_t)MT * lda;              // [KA][8]
     float* red_s = Bt_s + (size_t)KA * kNT;            // [512*8]
     float* D_s = red_s + kThreads * kNT;               // [MT][8] slice g[:, n0 .. n0+7] for the dW product
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+    uint32_t phase = 0;
     // CTA i owns columns [8i, 8i+8) of dg and of the stacked [dW3 ; dW1] matrix (if 8i < G), and db entries [8i, 8i+8).
-    pdl_wait();
     const int n0 = blockIdx.x * kNT;                   // 0 .. G + C
     const bool has_dg = n0 < G;
     stamp(p.dbg, 16);
     if (has_dg) {                                      // Bt = [W3[:, n0..] ; W1[:, n0..]]  (rows = contraction index)
-        load_bt_cols(Bt_s, p.W3, G, n0, G);
+        load_bt_cols(Bt_s, p.W3, G, n0, G);            // weights: before the wait on the previous kernel
         load_bt_cols(Bt_s + (size_t)G * kNT, p.W1, G, n0, C);
     }
+    __syncthreads();
+    pdl_wait();
     stamp(p.dbg, 22);
     const bool w_is_3 = n0 < G;
     const int wrow0 = w_is_3 ? n0 : n0 - G;
@@ -265,10 +335,15 @@ __global__ void __launch_bounds__(kThreads, 1) global_pre_bwd_kernel(PreBwd p) {
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        if (kDz3Ready) fill_tile<1, false>(A_s, lda, MT, mt, G, p.dgh, nullptr, G, row0, Copy4());
-        else fill_tile<2, false>(A_s, lda, MT, mt, G, p.dgh, p.z3, G, row0, MulGeluGrad4());
+        if (kDz3Ready) {                               // dz3 is a plain copy: TMA rows, zero the ragged tail
+            if (threadIdx.x < 32) tma_rows(A_s, lda, p.dgh, G, row0, mt, G, &bar);
+            zero_rows(A_s, lda, mt, MT, G);
+        } else {
+            fill_tile<2, false>(A_s, lda, MT, mt, G, p.dgh, p.z3, G, row0, MulGeluGrad4());
+        }
         stamp(p.dbg, 23);
         fill_tile<2, false>(A_s + G, lda, MT, mt, C, p.dg2l, p.zg, C, row0, MulGeluGrad4());
+        if (kDz3Ready) { mbar_wait(&bar, phase); phase ^= 1; }
         __syncthreads();
         stamp(p.dbg, 17);
         if (p.dzg_out != nullptr && blockIdx.x == 0)       // one CTA publishes dzg (columns G .. G+C of the staged tile)
@@ -346,10 +421,13 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
     extern __shared__ __align__(16) float sm[];
     __shared__ float red[32];
     cg::grid_group grid = cg::this_grid();
-    const int G = p.G, MT = row_tile_of(G), lda = G + 1;
+    const int G = p.G, MT = row_tile_of(G), lda = G + kPad;
     float* A_s = sm;                                   // [MT][lda]  g1 rows
     float* Bt_s = A_s + (size_t)MT * lda;              // [G][8]
     float* red_s = Bt_s + (size_t)G * kNT;             // [512*8]
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+    uint32_t phase = 0;
     const int n0 = blockIdx.x * kNT;
     load_bt_rows(Bt_s, p.W4, G, n0, G);
     // ---- row phase: LayerNorm 1
@@ -369,7 +447,11 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<1, true>(A_s, lda, MT, mt, G, p.g1, nullptr, G, row0, Copy4());
+        // g1 was written by other CTAs before the grid barrier (generic proxy); the TMA unit reads it through the async proxy
+        if (threadIdx.x < 32) { asm volatile("fence.proxy.async;" ::: "memory"); tma_rows(A_s, lda, p.g1, G, row0, mt, G, &bar); }
+        zero_rows(A_s, lda, mt, MT, G);
+        mbar_wait(&bar, phase);
+        phase ^= 1;
         __syncthreads();
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);
@@ -413,11 +495,14 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
     extern __shared__ __align__(16) float sm[];
     __shared__ float red[32];
     cg::grid_group grid = cg::this_grid();
-    const int G = p.G, MT = row_tile_of(G), lda = G + 1;
+    const int G = p.G, MT = row_tile_of(G), lda = G + kPad;
     float* A_s = sm;                                   // [MT][lda]  dz4 rows
     float* Bt_s = A_s + (size_t)MT * lda;              // [G][8]     W4[:, n0..n0+7]
     float* red_s = Bt_s + (size_t)G * kNT;             // [512*8]
     float* D_s = red_s + kThreads * kNT;               // [MT][8] dz4 slice
+    __shared__ __align__(8) uint64_t bar;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+    uint32_t phase = 0;
     const int n0 = blockIdx.x * kNT;
     stamp(p.dbg, 32);
     load_bt_cols(Bt_s, p.W4, G, n0, G);
@@ -460,7 +545,11 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
         __syncthreads();
-        fill_tile<1, true>(A_s, lda, MT, mt, G, p.dz4, nullptr, G, row0, Copy4());
+        // dz4 was written by other CTAs before the grid barrier (generic proxy); the TMA unit reads it through the async proxy
+        if (threadIdx.x < 32) { asm volatile("fence.proxy.async;" ::: "memory"); tma_rows(A_s, lda, p.dz4, G, row0, mt, G, &bar); }
+        zero_rows(A_s, lda, mt, MT, G);
+        mbar_wait(&bar, phase);
+        phase ^= 1;
         __syncthreads();
         stamp(p.dbg, 35);
         if (!p.skip_dw) fill_x_slice(D_s, p.g1, G, row0, mt, MT, n0);   // g1[:, n0 .. n0+7]
@@ -564,7 +653,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_bwd_kernel(PostBwd p)
 }
 
 size_t smem_bytes(int MT, int KA, bool with_slice) {
-    size_t f = (size_t)MT * (KA + 1) + (size_t)KA * kNT + (size_t)kThreads * kNT;
+    size_t f = (size_t)MT * (KA + kPad) + (size_t)KA * kNT + (size_t)kThreads * kNT;
     if (with_slice) f += (size_t)MT * kNT;
     return f * sizeof(float) + 64;
 }

@@ -121,7 +121,7 @@ class GraphedPretrainStep:
         dev = next(model.parameters()).device
         self.model = model
         self.device = dev
-        self._staging = self._copy_stream = self._staged_key = None
+        self._staging = self._copy_stream = self._staged_src = None
         self.static = [t.to(dev).clone() for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])]
         sx, sy, sw = self._dicts()
         distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
@@ -225,18 +225,19 @@ class GraphedPretrainStep:
             for dst, t in zip(self._staging, src):
                 dst.copy_(t, non_blocking=True)
             self._staged_done.record(self._copy_stream)
-        self._staged_key = tuple(id(t) for t in src)
+        self._staged_src = src          # strong references: an id() could be reused by a new tensor once these are freed
 
     def __call__(self, X, Y, W, prefetch=None):
         """One step on the batch (X, Y, W).  ``prefetch=(Xn, Yn, Wn)`` starts copying the NEXT batch while this one runs."""
         src = self._flat(X, Y, W)
         cur = torch.cuda.current_stream(self.device)
-        if self._staged_key is not None and self._staged_key == tuple(id(t) for t in src):
+        staged = self._staged_src
+        if staged is not None and len(staged) == len(src) and all(a is b for a, b in zip(staged, src)):
             cur.wait_event(self._staged_done)
             for dst, t in zip(self.static, self._staging):
                 dst.copy_(t, non_blocking=True)
             self._staging_free.record(cur)
-            self._staged_key = None
+            self._staged_src = None
         else:
             for dst, t in zip(self.static, src):
                 if t is not dst:
@@ -296,10 +297,17 @@ class GradAllReducer:
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self._armed = False
 
-    def broadcast_parameters(self, src: int = 0):
+    def broadcast_parameters(self, src: int = 0, extra_tensors=None):
+        """Make every rank start from rank ``src``'s weights.  ``extra_tensors``: tensors that take part in the forward
+        pass without being registered parameters -- pass ``model.head_tensors().values()``: the reference keeps the
+        attention heads' Wq/Wk/Wv in a plain list (modules.py:73-81), so ``model.parameters()`` does not reach them, yet
+        Wv enters every block's pooling.  Ranks that are not seeded identically would otherwise train different models
+        and average their gradients without any error."""
         if self.world > 1:
             for p in self.params:
                 dist.broadcast(p.data, src, group=self.group)
+            for t in (extra_tensors or ()):
+                dist.broadcast(t.data, src, group=self.group)
 
     def prepare(self):
         self._pending = [len(b) for b in self.buckets]
@@ -376,7 +384,12 @@ class FusedAdam(torch.optim.Adam):
             ps = [p for p in group["params"] if p.grad is not None]
             if not ps:
                 continue
-            gkey = tuple(p.grad.data_ptr() for p in ps)           # gradients are re-allocated by eager autograd, static under a graph
+            # the device job table holds raw pointers: it is valid only while every parameter, gradient and moment tensor
+            # stays where it was (gradients are re-allocated by eager autograd, static under a graph; load_state_dict
+            # replaces the moments)
+            gkey = tuple((p.data_ptr(), p.grad.data_ptr(),
+                          self.state[p]["exp_avg"].data_ptr() if "exp_avg" in self.state[p] else 0,
+                          self.state[p]["exp_avg_sq"].data_ptr() if "exp_avg_sq" in self.state[p] else 0) for p in ps)
             tab = self._tables.get(gi)
             if tab is None or tab["gkey"] != gkey or tab["n"] != len(ps):
                 self._sync_step_counters()                        # the counters are read below
@@ -399,6 +412,8 @@ class FusedAdam(torch.optim.Adam):
                         rows.append((p.data_ptr() + 4 * s0, p.grad.data_ptr() + 4 * s0, m.data_ptr() + 4 * s0, v.data_ptr() + 4 * s0,
                                      min(piece, p.numel() - s0)))
                 arr = np.array(rows, dtype=[("p", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), ("numel", "<i8")])
+                gkey = tuple((p.data_ptr(), p.grad.data_ptr(), self.state[p]["exp_avg"].data_ptr(),
+                              self.state[p]["exp_avg_sq"].data_ptr()) for p in ps)
                 tab = {"gkey": gkey, "n": len(ps), "table": torch.from_numpy(arr.view(np.uint8).copy()).to(ps[0].device),
                        "rows": len(rows), "t": steps.pop(), "steps": [self.state[p]["step"] for p in ps],
                        "stream_dev": ps[0].device}
@@ -418,6 +433,20 @@ class FusedAdam(torch.optim.Adam):
     def state_dict(self):
         self._sync_step_counters()
         return super().state_dict()
+
+    def load_state_dict(self, state_dict):
+        """torch replaces the ``exp_avg`` / ``exp_avg_sq`` / ``step`` tensors here: the cached device tables (raw pointers
+        to the old moments and the old step count) must not survive it."""
+        self._tables = {}
+        super().load_state_dict(state_dict)
+        for st in self.state.values():          # torch moves `step` to the parameter's device for non-capturable Adam or not,
+            if "step" in st and torch.is_tensor(st["step"]):     # depending on version: keep it a CPU scalar tensor as step() expects
+                st["step"] = st["step"].detach().to("cpu", torch.float32)
+
+    def add_param_group(self, param_group):
+        if hasattr(self, "_tables"):
+            self._tables = {}
+        super().add_param_group(param_group)
 
 
 def _lib_error(msg):

@@ -491,3 +491,39 @@ def test_fused_adam_matches_torch_adam(pb):
     ref2.load_state_dict(new.state_dict())                      # same keys / layout as the torch optimizer
     for a in p_ref:
         assert float(ref2.state[a]["step"]) == float(ref.state[a]["step"]) == 4
+
+
+def test_fused_adam_survives_load_state_dict_after_stepping(pb):
+    """step, save, step, load, step: torch replaces the moment tensors in load_state_dict, so the cached device table of
+    raw pointers must be rebuilt and the loaded step count honoured -- compared with torch.optim.Adam doing the same."""
+    g = torch.Generator().manual_seed(1)
+    shapes = [(9,), (70, 130), (128, 128, 9)]
+    p_ref = [torch.randn(s, generator=g).cuda().requires_grad_(True) for s in shapes]
+    p_new = [p.detach().clone().requires_grad_(True) for p in p_ref]
+    ref = torch.optim.Adam(p_ref, lr=1e-3, foreach=False, fused=False)
+    new = pb.FusedAdam(p_new, lr=1e-3)
+    grads = [[torch.randn(s, generator=g).cuda() for s in shapes] for _ in range(3)]
+
+    def give(i):
+        for a, b_, gr in zip(p_ref, p_new, grads[i]):      # the SAME gradient tensors every time: their addresses stay put
+            if a.grad is None:
+                a.grad, b_.grad = gr.clone(), gr.clone()
+            else:
+                a.grad.copy_(gr); b_.grad.copy_(gr)
+
+    give(0); ref.step(); new.step()
+    saved_ref, saved_new = ref.state_dict(), new.state_dict()
+    import copy
+    saved_ref, saved_new = copy.deepcopy(saved_ref), copy.deepcopy(saved_new)
+    saved_p = [p.detach().clone() for p in p_ref]
+    give(1); ref.step(); new.step()
+    with torch.no_grad():                                   # back to the checkpoint: weights and optimizer state
+        for a, b_, s in zip(p_ref, p_new, saved_p):
+            a.copy_(s); b_.copy_(s)
+    ref.load_state_dict(saved_ref); new.load_state_dict(saved_new)
+    give(2); ref.step(); new.step()
+    for a, b_ in zip(p_ref, p_new):
+        assert_close_rel(b_.detach(), a.detach(), 1e-6, what="param after load")
+        assert_close_rel(new.state[b_]["exp_avg"], ref.state[a]["exp_avg"], 1e-6)
+        assert_close_rel(new.state[b_]["exp_avg_sq"], ref.state[a]["exp_avg_sq"], 1e-6)
+    assert all(float(v["step"]) == 2 for v in new.state_dict()["state"].values())
