@@ -184,6 +184,40 @@ int pb_global_post_bwd(const float* dg2, const float* gamma2, const float* xhat2
                        float* dWp, float* dgamma1, float* dbeta1, float* dW4, float* db4, float* dgamma2,
                        float* dbeta2, const float* z3, float* dz3, int B, int G, void* stream);
 
+/* ---- a7/a13/a14 as one 16-CTA cluster launch per block boundary (csrc/gtrack.cu) --------------------------------
+ * Forward unit = [post half of block i ; pre half of block i+1]:
+ *   g1 = LN1(g + gh + (sum(Wp)/Kdim) pool), z4 = g1 W4^T + b4, g2 = LN2(g1 + gelu(z4))      (modules.py:92,223-229)
+ *   zg = g2 W1^T + b1, g2l = gelu(zg), z3 = g2 W3^T + b3, gh_out = gelu(z3)                 (modules.py:208,221, next block)
+ * W4 == NULL skips the post half (first block: the pre half then reads g_in); W1 == NULL skips the pre half (last
+ * block).  All tensors float32; B <= 128, C <= G <= 512 (pb_gtrack_ok also asks the driver whether a 16-CTA cluster with
+ * ~212 KB of shared memory per CTA can be scheduled); otherwise use pb_global_{pre,post}_*.
+ * Backward unit = the mirror image [pre half of block i+1 ; post half of block i]:
+ *   dzg = dg2l gelu'(zg); dg_total = dg_direct + dz3 W3 + dzg W1; db1, db3   (dz3_in given, or formed as dgh gelu'(z3n)
+ *   into dz3_buf; dg_direct may be NULL)
+ *   then with dg2 = dg_total (or dg_in when there is no pre half): LayerNorm-2 backward -> dv2, dz4 = dv2 gelu'(z4),
+ *   dg1 = dv2 + dz4 W4, db4, dgamma2, dbeta2, LayerNorm-1 backward -> dv1 (gradient of g and of gh), dpool, dWp,
+ *   dgamma1, dbeta1, and -- when z3 (this block's) is given -- dz3_out = dv1 gelu'(z3) for the next unit's dz3_in.
+ * Weight gradients are left to the caller: dW4 = dz4^T g1, dW3 = dz3^T g, dW1 = dzg^T g (pb_matmul_tn).
+ * dv2, dz4, dg1 are [B,G] scratch/outputs.  The batch is processed in groups of 16 rows, one cluster each; the groups
+ * meet in the column sums, so db1, db3, db4, dgamma1, dbeta1, dgamma2, dbeta2 and dWp are ACCUMULATED: zero on entry. */
+int pb_gtrack_ok(int B, int G, int C);
+/* up to three weight-gradient products in one launch: out_j [N_j, K_j] = A_j^T X_j with A_j [M, N_j], X_j [M, K_j], M <= 128
+ * (the batch); out_j == NULL skips product j.  Same results as three pb_matmul_tn calls. */
+int pb_matmul_tn3(const float* A0, const float* X0, float* out0, int N0, int K0, const float* A1, const float* X1, float* out1,
+                  int N1, int K1, const float* A2, const float* X2, float* out2, int N2, int K2, int M, void* stream);
+int pb_gtrack_fwd(const float* g, const float* gh, const float* pool, const float* Wp, int Kdim, const float* gamma1,
+                  const float* beta1, const float* W4, const float* b4, const float* gamma2, const float* beta2, float* g1,
+                  float* xhat1, float* rstd1, float* z4, float* xhat2, float* rstd2, float* g2, const float* g_in,
+                  const float* W1, const float* b1, const float* W3, const float* b3, float* zg, float* g2l, float* z3,
+                  float* gh_out, int B, int G, int C, void* stream);
+int pb_gtrack_bwd(const float* dg2l, const float* zg, const float* dz3_in, const float* dgh, const float* z3n,
+                  const float* dg_direct, const float* W1, const float* W3, float* dz3_buf, float* dzg, float* db1, float* db3,
+                  float* dg_total, const float* dg_in, const float* gamma2, const float* xhat2, const float* rstd2,
+                  const float* z4, const float* W4, const float* gamma1, const float* xhat1, const float* rstd1,
+                  const float* pool, const float* Wp, int Kdim, const float* z3, float* dv2, float* dz4, float* dg1, float* dv1,
+                  float* dz3_out, float* dpool, float* dWp, float* dgamma1, float* dbeta1, float* db4, float* dgamma2,
+                  float* dbeta2, int B, int G, int C, void* stream);
+
 /* ---- a5/a6/a7: narrow + dilated Conv1d, GELU, 4-way add with the global broadcast ---------------
  * zn = conv(x, Wn, d=1)+bn, zw = conv(x, Ww, d=dil)+bw, u = x + gelu(zn) + gelu(zw) + g2l[b,:]
  * (modules.py:205-211), and stats[b] += (sum u, sum u^2) over (L,C) for the joint LayerNorm that

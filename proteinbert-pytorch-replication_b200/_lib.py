@@ -45,6 +45,10 @@ PROTOTYPES = {
     "pb_matmul_tn": [_p, _p, _p, _i, _i, _i, _p],
     "pb_global_post_fwd": [_p, _p, _p, _p, _i] + [_p] * 13 + [_i, _i, _p],
     "pb_global_post_bwd": [_p] * 12 + [_i] + [_p] * 12 + [_i, _i, _p],
+    "pb_gtrack_ok": [_i, _i, _i],
+    "pb_matmul_tn3": [_p, _p, _p, _i, _i, _p, _p, _p, _i, _i, _p, _p, _p, _i, _i, _i, _p],
+    "pb_gtrack_fwd": [_p, _p, _p, _p, _i] + [_p] * 22 + [_i, _i, _i, _p],
+    "pb_gtrack_bwd": [_p] * 24 + [_i] + [_p] * 13 + [_i, _i, _i, _p],
     "pb_conv_pair_fwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p],
     "pb_conv_pair_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p],
     "pb_ln_joint_stats": [_p, _p, _i, _i, _i, _i, _p],

@@ -13,7 +13,8 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libpb_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-FLAGS = [*ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+# PB_NVCC_DEFINES="-DPB_GLOBAL_PROBE -DPB_CONV2_PROBE": probe builds (phase timestamps / cycle counters), never the shipped library
+FLAGS = [*ARCH, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC", *os.environ.get("PB_NVCC_DEFINES", "").split()]
 
 
 def _stale(target: str, deps) -> bool:

@@ -388,6 +388,7 @@ struct PostFwd {
     const float *g, *gh, *pool, *Wp, *gamma1, *beta1, *W4, *b4, *gamma2, *beta2;
     float *g1, *xhat1, *rstd1, *z4, *xhat2, *rstd2, *g2;
     int B, G, Kdim;
+    unsigned long long* dbg;
 };
 
 // LayerNorm of one row held as one value per (thread, i): v[i] is column threadIdx.x + i*512
@@ -429,7 +430,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
     if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
     uint32_t phase = 0;
     const int n0 = blockIdx.x * kNT;
+    stamp(p.dbg, 48);
     load_bt_rows(Bt_s, p.W4, G, n0, G);
+    stamp(p.dbg, 49);
     // ---- row phase: LayerNorm 1
     const float coef = coef_of(p.Wp, p.Kdim, red);
     for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
@@ -442,7 +445,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
         }
         ln_row(v, G, p.gamma1, p.beta1, p.xhat1 + off, p.g1 + off, p.rstd1 + r, red);
     }
+    stamp(p.dbg, 50);
     grid.sync();
+    stamp(p.dbg, 51);
     // ---- column phase: z4[:, n0..n0+7]
     for (int row0 = 0; row0 < p.B; row0 += MT) {
         const int mt = min(MT, p.B - row0);
@@ -453,8 +458,10 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
         mbar_wait(&bar, phase);
         phase ^= 1;
         __syncthreads();
+        stamp(p.dbg, 52);
         float out[kNT];
         cta_gemm8(A_s, lda, Bt_s, G, MT, red_s, out);
+        stamp(p.dbg, 53);
         if (threadIdx.x < mt) {
             float* o = p.z4 + (size_t)(row0 + threadIdx.x) * G + n0;
             const float4 b0 = ld4(p.b4 + n0), b1 = ld4(p.b4 + n0 + 4);
@@ -462,7 +469,9 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
             *reinterpret_cast<float4*>(o + 4) = make_float4(out[4] + b1.x, out[5] + b1.y, out[6] + b1.z, out[7] + b1.w);
         }
     }
+    stamp(p.dbg, 54);
     grid.sync();
+    stamp(p.dbg, 55);
     // ---- row phase: LayerNorm 2
     for (int r = blockIdx.x; r < p.B; r += gridDim.x) {
         const size_t off = (size_t)r * G;
@@ -474,6 +483,7 @@ __global__ void __launch_bounds__(kThreads, 1) global_post_fwd_kernel(PostFwd p)
         }
         ln_row(v, G, p.gamma2, p.beta2, p.xhat2 + off, p.g2 + off, p.rstd2 + r, red);
     }
+    stamp(p.dbg, 56);
 }
 
 // ============================================================================================================
@@ -715,7 +725,8 @@ int pb_global_post_fwd(const float* g, const float* gh, const float* pool, const
     const size_t smem = smem_bytes(row_tile_of(G), G, false);
     int rc = set_smem(global_post_fwd_kernel, smem);
     if (rc) return rc;
-    PostFwd p{g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, g1, xhat1, rstd1, z4, xhat2, rstd2, g2, B, G, Kdim};
+    PostFwd p{g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, g1, xhat1, rstd1, z4, xhat2, rstd2, g2, B, G, Kdim,
+              (unsigned long long*)pb_debug_ptr()};
     void* args[] = {&p};
     PB_CUDA(cudaLaunchCooperativeKernel((const void*)global_post_fwd_kernel, dim3(G / kNT), dim3(kThreads), args, smem,
                                         (cudaStream_t)stream));

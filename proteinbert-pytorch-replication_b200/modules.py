@@ -118,6 +118,37 @@ class ProteinBERTBlock(nn.Module):
         self.global_linear_layer_2 = nn.Sequential(nn.Linear(global_dim, global_dim, device=device), nn.GELU())
         self.global_norm_2 = nn.LayerNorm(normalized_shape=global_dim, device=device)
 
+    def local_track(self, xl: torch.Tensor, g2l: torch.Tensor, arena=None):
+        """modules.py:205-219 without the global side: xl [B,L,C], g2l [B,C] -> (h [B,L,C], pool [B,G] = sum_l gelu(h Wv_all))."""
+        if xl.shape[1] != self.sequences_length:
+            raise ValueError(f"sequence length {xl.shape[1]} != sequences_length {self.sequences_length} "
+                             "(the (L,C) LayerNorm fixes it, modules.py:148-151)")
+        nconv, wconv = self.local_narrow_conv_layer[0], self.local_wide_conv_layer[0]
+        lin = self.local_linear_layer[0]
+        att = self.global_attention_layer
+        dt = ops.dt_of(xl)
+        if getattr(self, "_prestaged", None) == dt:          # ProteinBERT.forward staged all blocks in one launch
+            staged, self._prestaged = self._staged, None
+        else:
+            staged = ops.stage_blocks(self, [self], dt)[0]
+        return ops.LocalTrackFn.apply(                                                         # :205-219
+            xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
+            self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
+            self.local_norm_2.weight, self.local_norm_2.bias, staged,
+            self.conv_kernel_size, self.wide_conv_dilation, self.head_grads, arena,
+            *[hd.Wv_parameter for hd in att.global_attention_heads])
+
+    def global_post_params(self):
+        """(W_parameter, LN1 weight/bias, W4, b4, LN2 weight/bias): the post half of this block's global track (:92,:223-229)."""
+        gl2 = self.global_linear_layer_2[0]
+        return (self.global_attention_layer.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias, gl2.weight, gl2.bias,
+                self.global_norm_2.weight, self.global_norm_2.bias)
+
+    def global_pre_params(self):
+        """(W1, b1, W3, b3): global-to-local linear (:208) and global linear 1 (:221), both read the block's input g."""
+        a, b = self.global_to_local_linear_layer[0], self.global_linear_layer_1[0]
+        return (a.weight, a.bias, b.weight, b.bias)
+
     def forward_channels_last(self, xl: torch.Tensor, g: torch.Tensor, arena=None):
         """xl [B,L,C] in the activation dtype, g [B,G] float -> (h [B,L,C], g_out [B,G])."""
         if xl.shape[1] != self.sequences_length:
@@ -198,6 +229,13 @@ class ProteinBERT(nn.Module):
             blk.head_grads = bool(flag)
         return self
 
+    def uses_cluster_units(self, batch: int) -> bool:
+        """Whether forward runs the global track as one cluster launch per block boundary (ops.GTrackFn) at this batch size."""
+        blocks = list(self.proteinBERT_blocks)
+        G = self.global_linear_layer[0].weight.shape[0]
+        return (all(b.fuse_global for b in blocks) and os.environ.get("PB_B200_GTRACK", "1") == "1"
+                and ops.gtrack_ok(batch, G, blocks[0].local_dim))
+
     def head_tensors(self):
         """The unregistered Wq/Wk/Wv tensors, keyed like oracle/model_oracle.py."""
         out = {}
@@ -221,11 +259,26 @@ class ProteinBERT(nn.Module):
         cut = getattr(self, "_boundary_at", None)        # training.GraphedPretrainStep: where backward is split in two
         Bsz, Lseq, Cloc = h.shape
         arena = ops.ZeroArena(len(blocks) * ops.ZeroArena.block_bytes(Bsz, Lseq, Cloc, g.shape[1]), h.device)   # one fill per step
-        for i, blk in enumerate(blocks):
-            if cut is not None and i == cut:
-                self._boundary = (h, g)
-            blk._prestaged = dt
-            h, g = blk.forward_channels_last(h, g, arena)
+        Cdim = blocks[0].local_dim
+        use_units = self.uses_cluster_units(Bsz)
+        if use_units:
+            # the global track runs as one cluster launch per block boundary: [post of block i ; pre of block i+1]
+            links = [ops.GTrackLink() for _ in range(len(blocks) + 1)]
+            none7 = (None,) * 7
+            _, g2l, gh = ops.GTrackFn.apply(g, None, None, *none7, *blocks[0].global_pre_params(), Cdim, None, links[0])
+            for i, blk in enumerate(blocks):
+                if cut is not None and i == cut:
+                    self._boundary = (h, g, g2l, gh)
+                blk._prestaged = dt
+                h, pool = blk.local_track(h, g2l, arena)
+                nxt = blocks[i + 1].global_pre_params() if i + 1 < len(blocks) else (None,) * 4
+                g, g2l, gh = ops.GTrackFn.apply(g, gh, pool, *blk.global_post_params(), *nxt, Cdim, links[i], links[i + 1])
+        else:
+            for i, blk in enumerate(blocks):
+                if cut is not None and i == cut:
+                    self._boundary = (h, g)
+                blk._prestaged = dt
+                h, g = blk.forward_channels_last(h, g, arena)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
         p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284
         p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID, tc)                       # :286-293

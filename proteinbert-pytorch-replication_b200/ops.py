@@ -376,6 +376,142 @@ class GlobalPostFn(torch.autograd.Function):
         return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4], None
 
 
+def gtrack_ok(B, G, C) -> bool:
+    return bool(lib().pb_gtrack_ok(B, G, C))
+
+
+class GTrackLink:
+    """Side channel between consecutive GTrackFn units.  Unit i's pre half produces z3 of block i+1; unit i+1's backward holds
+    every row of dv1 (the gradient of gh) anyway and emits dz3 = dv1 * gelu'(z3) beside it, which unit i's backward then
+    stages as a plain copy instead of forming it in a row phase of its own.  Used only when the gradient autograd hands to
+    unit i for gh is the very tensor unit i+1 returned."""
+    __slots__ = ("z3", "dz3", "dgh_ptr")
+
+    def __init__(self):
+        self.z3 = self.dz3 = self.dgh_ptr = None
+
+
+class GTrackFn(torch.autograd.Function):
+    """The global track across one block boundary as ONE 16-CTA cluster launch (csrc/gtrack.cu): the post half of block i
+    (modules.py:92,223-229: g1 = LN(g + gh + att), g2 = LN(g1 + gelu(g1 W4^T + b4))) followed by the pre half of block i+1
+    (:208,:221: g2l = gelu(g2 W1^T + b1), gh = gelu(g2 W3^T + b3)).  W4 is None for the first unit (pre half of block 0
+    only), W1 is None for the last (post half only).  Returns (g2, g2l, gh) with None for an absent half."""
+
+    @staticmethod
+    def forward(ctx, g, gh, pool, Wp, gamma1, beta1, W4, b4, gamma2, beta2, W1, b1, W3, b3, C, link_in, link_out):
+        _need_cuda(g)
+        has_post, has_pre = W4 is not None, W1 is not None
+        g = g.contiguous()
+        B, G = g.shape
+        dev = g.device
+        buf = rstd = zg2 = z32 = None
+        if has_post:
+            gh, pool = gh.contiguous(), pool.contiguous()
+            buf = torch.empty((5, B, G), dtype=torch.float32, device=dev)          # g1, xhat1, z4, xhat2, g2
+            rstd = torch.empty((2, B), dtype=torch.float32, device=dev)
+        if has_pre:
+            zg2 = torch.empty((2, B, C), dtype=torch.float32, device=dev)          # zg, g2l
+            z32 = torch.empty((2, B, G), dtype=torch.float32, device=dev)          # z3, gh
+        b = lambda t, i: None if t is None else t[i].data_ptr()
+        _call("pb_gtrack_fwd", _p(g) if has_post else None, _p(gh) if has_post else None, _p(pool) if has_post else None,
+              _p(Wp) if has_post else None, Wp.numel() if has_post else 0, _p(gamma1), _p(beta1), _p(W4), _p(b4), _p(gamma2), _p(beta2),
+              b(buf, 0), b(buf, 1), b(rstd, 0), b(buf, 2), b(buf, 3), b(rstd, 1), b(buf, 4),
+              None if has_post else _p(g), _p(W1), _p(b1), _p(W3), _p(b3), b(zg2, 0), b(zg2, 1), b(z32, 0), b(z32, 1), B, G, C, _st())
+        ctx.save_for_backward(g, pool, Wp, gamma1, W4, gamma2, buf, rstd, W1, W3, zg2, z32)
+        ctx.cfg = (B, G, C, has_post, has_pre)
+        ctx.link_in, ctx.link_out = link_in, link_out
+        if has_pre and link_out is not None:
+            link_out.z3 = z32[0]
+        return (buf[4] if has_post else None, zg2[1] if has_pre else None, z32[1] if has_pre else None)
+
+    @staticmethod
+    def backward(ctx, dg2, dg2l, dghn):
+        g, pool, Wp, gamma1, W4, gamma2, buf, rstd, W1, W3, zg2, z32 = ctx.saved_tensors
+        B, G, C, has_post, has_pre = ctx.cfg
+        dev = g.device
+        link_in, link_out = ctx.link_in, ctx.link_out
+        f32 = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
+        dg2 = None if dg2 is None else dg2.contiguous()
+        # ---- pre half (block i+1): needs dg2l, dgh of the next block and the direct-path gradient of g2
+        dz3_in = dz3_buf = dzg = db1 = db3 = dg_total = None
+        if has_pre:
+            dg2l = torch.zeros((B, C), dtype=torch.float32, device=dev) if dg2l is None else dg2l.contiguous()
+            dghn = torch.zeros((B, G), dtype=torch.float32, device=dev) if dghn is None else dghn.contiguous()
+            if link_out is not None and link_out.dz3 is not None and link_out.dgh_ptr == dghn.data_ptr():
+                dz3_in = link_out.dz3
+            else:
+                dz3_buf = f32(B, G)
+            if link_out is not None:
+                link_out.z3 = link_out.dz3 = link_out.dgh_ptr = None
+            dzg, dg_total = f32(B, C), f32(B, G)
+        # ---- post half (block i)
+        out = vec = dWp = None
+        z3_here = link_in.z3 if (has_post and link_in is not None) else None
+        if has_post:
+            out = f32(6 if z3_here is not None else 5, B, G)                      # dv2, dz4, dg1, dv1, dpool[, dz3 of this block]
+            if not has_pre and dg2 is None:
+                dg2 = torch.zeros((B, G), dtype=torch.float32, device=dev)
+        # the 16-row groups of the batch (one cluster each) meet in the column sums: those outputs are accumulated into one
+        # zero-filled buffer  [dgamma1, dbeta1, db4, dgamma2, dbeta2 | db3 | db1 | dWp]
+        Kd = Wp.numel() if has_post else 0
+        acc = torch.zeros(((5 * G if has_post else 0) + (G + C if has_pre else 0) + Kd,), dtype=torch.float32, device=dev)
+        pos = 0
+        if has_post:
+            vec = acc[:5 * G].view(5, G)
+            pos = 5 * G
+        if has_pre:
+            db3, db1 = acc[pos:pos + G], acc[pos + G:pos + G + C]
+            pos += G + C
+        if has_post:
+            dWp = acc[pos:pos + Kd]
+        o = lambda i: None if out is None else out[i].data_ptr()
+        v = lambda i: None if vec is None else vec[i].data_ptr()
+        _call("pb_gtrack_bwd", _p(dg2l) if has_pre else None, None if zg2 is None else zg2[0].data_ptr(), _p(dz3_in),
+              _p(dghn) if (has_pre and dz3_in is None) else None, (z32[0].data_ptr() if (has_pre and dz3_in is None) else None),
+              _p(dg2) if has_pre else None, _p(W1), _p(W3), _p(dz3_buf), _p(dzg), _p(db1), _p(db3), _p(dg_total),
+              None if has_pre else _p(dg2), _p(gamma2), (buf[3].data_ptr() if has_post else None), (rstd[1].data_ptr() if has_post else None),
+              (buf[2].data_ptr() if has_post else None), _p(W4), _p(gamma1), (buf[1].data_ptr() if has_post else None),
+              (rstd[0].data_ptr() if has_post else None), _p(pool) if has_post else None, _p(Wp) if has_post else None,
+              Wp.numel() if has_post else 0, _p(z3_here), o(0), o(1), o(2), o(3), (out[5].data_ptr() if z3_here is not None else None),
+              o(4), _p(dWp), v(0), v(1), v(2), v(3), v(4), B, G, C, _st())
+        if has_post and link_in is not None:
+            if z3_here is not None:
+                link_in.dz3, link_in.dgh_ptr = out[5], out[3].data_ptr()
+        # ---- weight gradients dW = dZ^T X, off the critical path
+        dW4 = dW1 = dW3 = None
+        jobs = []
+        if has_post:
+            dW4 = torch.empty_like(W4)
+            jobs.append((out[1], buf[0], dW4, G, G))                               # dz4^T g1
+        if has_pre:
+            gp = buf[4] if has_post else g                                         # the pre half's input
+            dz3 = dz3_in if dz3_in is not None else dz3_buf
+            dW3, dW1 = torch.empty_like(W3), torch.empty_like(W1)
+            jobs.append((dz3, gp, dW3, G, G))
+            jobs.append((dzg, gp, dW1, C, G))
+
+        def products():          # one launch for the unit's two or three products
+            args = []
+            for (a, x, dw, n, k) in jobs + [(None, None, None, 0, 0)] * (3 - len(jobs)):
+                args += [_p(a), _p(x), _p(dw), n, k]
+            _call("pb_matmul_tn3", *args, B, _st())
+
+        if WGRAD_STREAM:
+            run_on_side(dev, products, *[t for j in jobs for t in j[:3]])
+        else:
+            products()
+        if has_post:
+            ret_g, ret_gh, ret_pool = out[3], out[3], out[4]          # dv1 is the gradient of g and of gh; dpool = coef * dv1
+        else:
+            ret_g, ret_gh, ret_pool = dg_total, None, None
+        return (ret_g, ret_gh, ret_pool, dWp, v_t(vec, 0), v_t(vec, 1), dW4, v_t(vec, 2), v_t(vec, 3), v_t(vec, 4),
+                dW1, db1, dW3, db3, None, None, None)
+
+
+def v_t(vec, i):
+    return None if vec is None else vec[i]
+
+
 def global_fused_ok(B, G, C) -> bool:
     return bool(lib().pb_global_fused_ok(B, G, C))
 
@@ -729,4 +865,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "GTrackFn", "GTrackLink", "gtrack_ok", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]

@@ -133,8 +133,13 @@ class GraphedPretrainStep:
 
         # ---- two-stage backward (data-parallel): stage A = forward + loss + backward down to the input of block
         # `cut`; stage B = the rest.  The gradients of stage A are all-reduced while stage B runs.
+        # with cluster units (ops.GTrackFn) the pre half of block `cut` (its global-to-local and first global linear) is
+        # computed -- and differentiated -- together with the post half of block cut-1, i.e. below the cut
+        straddle = (f"proteinBERT_blocks.{cut}.global_to_local_linear_layer.", f"proteinBERT_blocks.{cut}.global_linear_layer_1.") \
+            if model.uses_cluster_units(self.static[0].shape[0]) else ()
         upper = [p for n, p in model.named_parameters()
-                 if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut)]
+                 if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut
+                                                     and not n.startswith(straddle))]
         upper_ids = {id(p) for p in upper}
         lower = [p for p in model.parameters() if id(p) not in upper_ids]
         upper_heads = [h.Wv_parameter for blk in list(model.proteinBERT_blocks)[cut:]
@@ -148,22 +153,22 @@ class GraphedPretrainStep:
             finally:
                 model._boundary_at = None
             loss = pretraining_loss(p_local, p_global, sy, sw)
-            hb, gb = model._boundary
+            bnd = list(model._boundary)          # the tensors that cross the cut: (h, g) or, with cluster units, (h, g, g2l, gh)
             model._boundary = None
             ops.DEFER_WGRAD_JOIN = True
             try:
-                grads = torch.autograd.grad(loss, upper + upper_heads + [hb, gb], retain_graph=True)
+                grads = torch.autograd.grad(loss, upper + upper_heads + bnd, retain_graph=True)
             finally:
                 ops.DEFER_WGRAD_JOIN = False
                 ops.join_side_streams()
             for p, g in zip(upper + upper_heads, grads):
                 p.grad = g
-            return loss.detach(), hb, gb, grads[-2], grads[-1]
+            return loss.detach(), bnd, list(grads[len(grads) - len(bnd):])
 
-        def stage_b(hb, gb, dhb, dgb):
+        def stage_b(bnd, dbnd):
             ops.DEFER_WGRAD_JOIN = True
             try:
-                torch.autograd.backward([hb, gb], [dhb, dgb])
+                torch.autograd.backward(bnd, dbnd)
             finally:
                 ops.DEFER_WGRAD_JOIN = False
                 ops.join_side_streams()

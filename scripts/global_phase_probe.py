@@ -7,7 +7,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import proteinbert_b200 as pb
-from bench import CFG
+from bench import BASE_CFG as CFG
 
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
@@ -33,3 +33,8 @@ names = {16: "start", 17: "A tile [dz3|dzg] staged (gelu')", 18: "D slice + colu
 print(f"pre_bwd: weight slices loaded +{t[22] - t[16]}, dz3 tile staged +{t[23] - t[22]}, dzg tile (gelu') +{t[17] - t[23]}")
 for i in range(17, 22):
     print(f"  {names[i]:40s} +{t[i] - t[i - 1]:6d}   (t = {t[i] - t[16]})")
+
+print("post_fwd (last launch of the step):")
+for a, b_, what in ((48, 49, "W4 slice loaded"), (49, 50, "LN1 rows"), (50, 51, "grid.sync"), (51, 52, "g1 tile staged (TMA)"), (52, 53, "mma product"),
+                    (53, 54, "z4 stores"), (54, 55, "grid.sync"), (55, 56, "LN2 rows")):
+    print(f"  {what:40s} +{t[b_] - t[a]:6d}   (t = {t[b_] - t[48]})")
