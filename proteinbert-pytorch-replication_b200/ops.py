@@ -525,6 +525,7 @@ def global_fused_ok(B, G, C) -> bool:
 import os as _os
 
 WGRAD_STREAM = _os.environ.get("PB_B200_WGRAD_STREAM", "1") != "0"
+CONV_WGRAD_EARLY = _os.environ.get("PB_B200_CONV_WGRAD_EARLY", "1") == "1"
 DEFER_WGRAD_JOIN = False
 _SIDE = {}
 _SIDE_PENDING = set()
@@ -732,10 +733,17 @@ class LocalTrackFn(torch.autograd.Function):
                                       _p(dzw), _p(dx), _p(dWn), _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt,
                                       *_wgrad_ws(dev), st)
         else:
+            wgrad = lambda: _call("pb_conv_pair_bwd", None, None, None, _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), None, _p(dWn), _p(dWw),
+                                  None, None, None, B, L, C, ksize, dil, dt, *_wgrad_ws(dev), _st())
+            # with the fused LayerNorm-backward kernel dzn / dzw exist before the data gradient is issued: the weight gradient then
+            # depends on that kernel only, not on the data gradient behind it
+            early = fused and CONV_WGRAD_EARLY
+            if early:
+                on_side(wgrad, x, dzn, dzw, dWn, dWw)
             _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
                                       _p(dzw), _p(dx), None, None, _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt, None, 0, st)
-            on_side(lambda: _call("pb_conv_pair_bwd", None, None, None, _p(x), _p(wn_b), _p(ww_b), _p(dzn), _p(dzw), None, _p(dWn), _p(dWw),
-                                  None, None, None, B, L, C, ksize, dil, dt, *_wgrad_ws(dev), _st()), x, dzn, dzw, dWn, dWw)
+            if not early:
+                on_side(wgrad, x, dzn, dzw, dWn, dWw)
             if not DEFER_WGRAD_JOIN:
                 join_side_streams()
         if head_grads:
