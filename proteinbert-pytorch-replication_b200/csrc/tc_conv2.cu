@@ -12,6 +12,15 @@
 //     two: the narrow convolution's half (zn out, x + gelu(zn) + g2l written back into its TMEM columns with
 //     tcgen05.st) runs while the dilated convolution's MMAs are still being issued; only the second half is exposed.
 // L2 -> smem traffic drops to ~0.65 MB per 256 positions (3.5x less per position).
+//
+// Round 2: operand roles swapped.  With positions as the MMA's M (two 128 x 128 x 16 MMAs per weight k-step) the tensor pipe
+// waited on shared memory: each MMA read 4 KB of activations + 4 KB of weights, 128 B per cycle at the 64-cycle rate, and
+// issued at ~107 cycles (profiles/r01_conv2_fwd_ncu.md).  Now the WEIGHT tile is the A operand (M = 128 output channels)
+// and all 256 positions of the CTA are the B operand (N = 256, the same row-shifted halo descriptor): one 128 x 256 x 16
+// MMA per k-step reads 4 KB + 8 KB for twice the work -- 25 % less shared-memory traffic per FLOP, half the instructions.
+// The accumulators come out transposed (TMEM lane = output channel, column = position), which makes bias and the global
+// broadcast per-lane constants; the epilogue transposes back on its way to the staging tiles (one shuffle per two values:
+// neighbouring lanes = neighbouring channels form the 32-bit words of a [position][channel] row).
 #include <stdlib.h>
 #include "tc_common.cuh"
 #include "tc_api.cuh"
@@ -126,7 +135,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(128, kC, 0, 0);
+            constexpr uint32_t idesc = make_idesc_bf16(kC, kRows, 0, 0);        // M = 128 output channels, N = 256 positions
 #ifdef PB_CONV2_PROBE
             long long t_wait_full = 0, t_wait_a = 0;
             const long long t_begin = clock64();
@@ -153,20 +162,18 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 tc_fence_after();
                 // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start address
                 // field (bits 0..13), so they are formed by adding constants -- the issuing thread is the bottleneck
-                const uint64_t da0 = desc_sw128_bo(smem_u32(smem + kc * a_buf) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
-                const uint64_t db0 = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
-                const uint32_t tm = tmem_base + conv * kC;
-                const uint32_t acc0 = (t == 0 && kc == 0) ? 0u : 1u;
+                const uint64_t dact = desc_sw128_bo(smem_u32(smem + kc * a_buf) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
+                const uint64_t dwgt = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
+                // forward: one accumulator per convolution (the narrow one is drained while the dilated one is still being
+                // formed); data gradient: both convolutions add into the same accumulator
+                const uint32_t tm = tmem_base + (kFwd ? conv * kRows : 0);
+                const uint32_t acc0 = kFwd ? ((t == 0 && kc == 0) ? 0u : 1u) : (i == 0 ? 0u : 1u);
 #pragma unroll
-                for (int tile = 0; tile < 2; ++tile) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16(tm + tile * 2 * kC, da0 + (uint64_t)(tile * 1024 + k * 2), db0 + (uint64_t)(k * 2), idesc,
-                                  k == 0 ? acc0 : 1u);
-                }
+                for (int k = 0; k < 4; ++k)
+                    umma_bf16(tm, dwgt + (uint64_t)(k * 2), dact + (uint64_t)(k * 2), idesc, k == 0 ? acc0 : 1u);
                 umma_commit(&empty_bar[s]);
                 if (!kFwd && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
-                if (kFwd && i == p.ksize * 2 - 1) umma_commit(&tmem_full_bar[0]);       // narrow conv: both sub-tiles complete
+                if (kFwd && i == p.ksize * 2 - 1) umma_commit(&tmem_full_bar[0]);       // narrow conv complete
             }
             umma_commit(&tmem_full_bar[1]);
 #ifdef PB_CONV2_PROBE
@@ -179,76 +186,91 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
 #endif
         }
     } else {
-        // ===== epilogue: warps 2..9; sub-tile = (warp-2)/4, TMEM lane quarter = warp % 4 =====
+        // ===== epilogue: warps 2..9.  TMEM lane = output channel: quarter q = warp % 4 -> channels 32q .. 32q+31 (one per
+        //       lane); position half = (warp-2)/4 -> columns 128*half .. +127 of each accumulator, in chunks of 32 =====
 #ifdef PB_CONV2_PROBE
         const long long e0 = clock64();
         long long e1 = e0;
 #endif
-        const int tile = (warp - 2) >> 2, q = warp & 3;
-        const int row = tile * 128 + q * 32 + lane;                     // position inside the CTA's 256
-        const size_t grow = ((size_t)b * p.L + l0 + row) * kC;
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + tile * 2 * kC;
-        // Output tiles leave through TMA: each warp stages its 32 x 32 bf16 sub-tile per tensor in shared memory
-        // (64-byte swizzle, conflict-free 16-byte stores), then one lane issues the bulk tensor store.
+        const int hpos = (warp - 2) >> 2, q = warp & 3;
+        const int co = q * 32 + lane;                                   // this thread's channel
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + hpos * 128;
+        // Output tiles leave through TMA: each warp stages a [32 positions x 32 channels] bf16 tile per tensor in shared
+        // memory (64-byte swizzle) and one lane issues the bulk tensor store.
         uint8_t* stage = stage_base + (warp - 2) * (kFwd ? 3 * 2048 : 2 * 3 * 2048);
-        const int sw = (lane >> 1) & 3;                                 // 64B swizzle: 16-byte chunk ^= (row / 2) & 3
-        const int lrow = l0 + tile * 128 + q * 32;
+        const int lrow = l0 + hpos * 128;                               // first position of this warp's half
+        const bool odd = lane & 1;
+        const int cw = lane >> 1;                                       // 32-bit word of the pair (co & ~1, co | 1) in a 64-byte row
+        // transposing store: v[j] = this lane's channel at position j.  Neighbouring lanes exchange one value per position
+        // pair, so that even lanes write the word (co, co+1) of row j and odd lanes the word (co-1, co) of row j+1: the two
+        // half-warps hit the two bank halves, conflict-free.
+        auto stage_transposed = [&](uint8_t* tile, const bf16 (&v)[32]) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const uint32_t mine = odd ? ((uint32_t)__bfloat16_as_ushort(v[j]) | ((uint32_t)__bfloat16_as_ushort(v[j + 2]) << 16))
+                                          : ((uint32_t)__bfloat16_as_ushort(v[j + 1]) | ((uint32_t)__bfloat16_as_ushort(v[j + 3]) << 16));
+                const uint32_t got = __shfl_xor_sync(0xffffffffu, mine, 1);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int r = j + 2 * h + (odd ? 1 : 0);
+                    const uint32_t other = (got >> (16 * h)) & 0xffffu;
+                    const uint32_t own = odd ? __bfloat16_as_ushort(v[j + 2 * h + 1]) : __bfloat16_as_ushort(v[j + 2 * h]);
+                    const uint32_t word = odd ? (other | (own << 16)) : (own | (other << 16));
+                    *reinterpret_cast<uint32_t*>(tile + r * 64 + ((((cw >> 2) ^ ((r >> 1) & 3))) << 4) + (cw & 3) * 4) = word;
+                }
+            }
+        };
         float s_sum = 0.f, s_sq = 0.f;
         if (kFwd) {
             // ---- first half, under the MMAs of the dilated convolution: zn = acc + bn (stored), and the partial sum
             //      x + gelu(zn) + g2l goes back into the accumulator's TMEM columns (tcgen05.st) for the second half.
             //      x comes from the halo tile that feeds the MMAs.
-            const int hrow = half * p.dil + row;
+            const float bnl = __ldg(p.bn + co), gl = __ldg(p.g2l + (size_t)b * kC + co);
+            const uint8_t* xbase = smem + (co >> 6) * a_buf;
+            const int xchunk = (co & 63) >> 3, xoff = (co & 7) * 2;
             mbar_wait(&tmem_full_bar[0], 0);
 #ifdef PB_CONV2_PROBE
             e1 = clock64();
 #endif
             tc_fence_after();
 #pragma unroll 1
-            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : 4); ++ch) {
                 float an[32];
                 tmem_ld32(taddr + ch * 32, an);
-                const int c0 = ch * 32;
                 uint8_t* sbuf = stage + (ch & 1) * 2048;
-                uint4 xv[4];
-                const uint8_t* xrow = smem + (ch >> 1) * a_buf + (size_t)hrow * 128;
-#pragma unroll
-                for (int v = 0; v < 4; ++v) xv[v] = *reinterpret_cast<const uint4*>(xrow + ((((ch & 1) * 4 + v) ^ (hrow & 7)) * 16));
-                const bf16* xb = reinterpret_cast<const bf16*>(xv);
-                const float bnl = __ldg(p.bn + c0 + lane), gl = __ldg(p.g2l + (size_t)b * kC + c0 + lane);
+                const int hrow0 = half * p.dil + hpos * 128 + ch * 32;     // halo row of the chunk's first position
                 __align__(16) bf16 on[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const bf16 zn = __float2bfloat16_rn(an[j] + __shfl_sync(0xffffffffu, bnl, j));
+                    const int hrow = hrow0 + j;
+                    const bf16 xv = *reinterpret_cast<const bf16*>(xbase + (size_t)hrow * 128 + ((xchunk ^ (hrow & 7)) << 4) + xoff);
+                    const bf16 zn = __float2bfloat16_rn(an[j] + bnl);
                     on[j] = zn;
-                    an[j] = (__bfloat162float(xb[j]) + gelu_fast(__bfloat162float(zn))) + __shfl_sync(0xffffffffu, gl, j);
+                    an[j] = (__bfloat162float(xv) + gelu_fast(__bfloat162float(zn))) + gl;
                 }
                 tmem_st32(taddr + ch * 32, an);
                 if (ch >= 2) {                                           // the buffer's previous store must have read it
                     if (lane == 0) tma_store_wait_read<1>();
                     __syncwarp();
                 }
-#pragma unroll
-                for (int v = 0; v < 4; ++v)
-                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(on)[v];
+                stage_transposed(sbuf, on);
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) { tma_store_3d(&mapS0, sbuf, c0, lrow, b); tma_store_commit(); }
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, q * 32, lrow + ch * 32, b); tma_store_commit(); }
             }
             // ---- second half, after the last MMA: zw = acc + bw, u = partial + gelu(zw), LayerNorm sums
+            const float bwl = __ldg(p.bw + co);
             mbar_wait(&tmem_full_bar[1], 0);
             tc_fence_after();
 #pragma unroll 1
-            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : 4); ++ch) {
                 float pa[32], aw[32];
                 tmem_ld32(taddr + ch * 32, pa);
-                tmem_ld32(taddr + kC + ch * 32, aw);
-                const int c0 = ch * 32;
-                const float bwl = __ldg(p.bw + c0 + lane);
+                tmem_ld32(taddr + kRows + ch * 32, aw);
                 __align__(16) bf16 ow[32], ou[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const bf16 zw = __float2bfloat16_rn(aw[j] + __shfl_sync(0xffffffffu, bwl, j));
+                    const bf16 zw = __float2bfloat16_rn(aw[j] + bwl);
                     ow[j] = zw;
                     const bf16 ub = __float2bfloat16_rn(pa[j] + gelu_fast(__bfloat162float(zw)));
                     ou[j] = ub;
@@ -257,17 +279,13 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 }
                 if (lane == 0) tma_store_wait_read<0>();                 // one pair of staging tiles: the previous stores have read them
                 __syncwarp();
-#pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    const int off = lane * 64 + ((v ^ sw) * 16);
-                    *reinterpret_cast<uint4*>(stage + off) = reinterpret_cast<const uint4*>(ow)[v];
-                    *reinterpret_cast<uint4*>(stage + 2048 + off) = reinterpret_cast<const uint4*>(ou)[v];
-                }
+                stage_transposed(stage, ow);
+                stage_transposed(stage + 2048, ou);
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
-                    tma_store_3d(&mapS1, stage, c0, lrow, b);
-                    tma_store_3d(&mapS2, stage + 2048, c0, lrow, b);
+                    tma_store_3d(&mapS1, stage, q * 32, lrow + ch * 32, b);
+                    tma_store_3d(&mapS2, stage + 2048, q * 32, lrow + ch * 32, b);
                     tma_store_commit();
                 }
             }
@@ -278,29 +296,26 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
 #endif
             tc_fence_after();
 #pragma unroll 1
-            for (int ch = 0; ch < ((p.debug & 2) ? 0 : kC / 32); ++ch) {
-                float an[32], aw[32];
+            for (int ch = 0; ch < ((p.debug & 2) ? 0 : 4); ++ch) {
+                // du[position][channel] for this lane's channel: 32 two-byte loads, 64 contiguous bytes per warp instruction
+                const bf16* dup = p.du + ((size_t)b * p.L + lrow + ch * 32) * kC + co;
+                bf16 dv[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) dv[j] = dup[(size_t)j * kC];
+                float an[32];
                 tmem_ld32(taddr + ch * 32, an);
-                tmem_ld32(taddr + kC + ch * 32, aw);
-                const int c0 = ch * 32;
                 uint8_t* sbuf = stage + (ch & 1) * (3 * 2048);
                 if (ch >= 2) {                                           // the buffer's previous store must have read it
                     if (lane == 0) tma_store_wait_read<1>();
                     __syncwarp();
                 }
-                uint4 dv[4];
-#pragma unroll
-                for (int v = 0; v < 4; ++v) dv[v] = *reinterpret_cast<const uint4*>(p.du + grow + c0 + v * 8);
-                const bf16* db_ = reinterpret_cast<const bf16*>(dv);
                 __align__(16) bf16 od[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__bfloat162float(db_[j]) + an[j] + aw[j]);
-#pragma unroll
-                for (int v = 0; v < 4; ++v)
-                    *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
+                for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__bfloat162float(dv[j]) + an[j]);
+                stage_transposed(sbuf, od);
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) { tma_store_3d(&mapS0, sbuf, c0, lrow, b); tma_store_commit(); }
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, q * 32, lrow + ch * 32, b); tma_store_commit(); }
             }
         }
         if (lane == 0) tma_store_wait<0>();
