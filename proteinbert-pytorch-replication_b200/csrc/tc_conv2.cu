@@ -226,8 +226,11 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             //      x + gelu(zn) + g2l goes back into the accumulator's TMEM columns (tcgen05.st) for the second half.
             //      x comes from the halo tile that feeds the MMAs.
             const float bnl = __ldg(p.bn + co), gl = __ldg(p.g2l + (size_t)b * kC + co);
-            const uint8_t* xbase = smem + (co >> 6) * a_buf;
-            const int xchunk = (co & 63) >> 3, xoff = (co & 7) * 2;
+            // x[position][co] sits in the 128-byte-swizzled halo tile: 16-byte chunk index ^ (row & 7).  The chunk's first halo
+            // row is a multiple of 4 ((2 * half * dil) % 8 == 0, positions in steps of 32), so (row0 + j) & 7 == (j & 7) ^ (row0 & 7):
+            // the per-position part of the swizzle is a compile-time constant
+            const int xsw = (((co & 63) >> 3) ^ ((half * p.dil) & 7)) << 4;
+            const uint8_t* xbase = smem + (co >> 6) * a_buf + (co & 7) * 2;
             mbar_wait(&tmem_full_bar[0], 0);
 #ifdef PB_CONV2_PROBE
             e1 = clock64();
@@ -238,12 +241,11 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 float an[32];
                 tmem_ld32(taddr + ch * 32, an);
                 uint8_t* sbuf = stage + (ch & 1) * 2048;
-                const int hrow0 = half * p.dil + hpos * 128 + ch * 32;     // halo row of the chunk's first position
+                const uint8_t* xrow = xbase + (size_t)(half * p.dil + hpos * 128 + ch * 32) * 128;     // halo row of the chunk's first position
                 __align__(16) bf16 on[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const int hrow = hrow0 + j;
-                    const bf16 xv = *reinterpret_cast<const bf16*>(xbase + (size_t)hrow * 128 + ((xchunk ^ (hrow & 7)) << 4) + xoff);
+                    const bf16 xv = *reinterpret_cast<const bf16*>(xrow + j * 128 + (xsw ^ ((j & 7) << 4)));
                     const bf16 zn = __float2bfloat16_rn(an[j] + bnl);
                     on[j] = zn;
                     an[j] = (__bfloat162float(xv) + gelu_fast(__bfloat162float(zn))) + gl;

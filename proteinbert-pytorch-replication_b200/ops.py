@@ -58,6 +58,38 @@ def dt_of(t: torch.Tensor) -> int:
     raise _lib.PBError(f"unsupported activation dtype {t.dtype}")
 
 
+# ---- gradient sink -------------------------------------------------------------------------------------------------
+# training.FlatGradBucket lays all registered gradients out in ONE flat buffer (what the data-parallel all-reduce sends).
+# While a sink is active, the backward functions below write each parameter's gradient straight into its slice of that
+# buffer (fresh views, so autograd adopts them as .grad without a copy) instead of a torch.empty tensor: no gather / scatter
+# pass around the collective.  Slices documented as accumulated ("zero on entry") are cleared by the bucket once per step.
+GRAD_SINK = None
+
+
+class GradSink:
+    def __init__(self, flat, table):
+        self.flat, self.table = flat, table            # table: parameter data_ptr -> (offset, shape)
+
+    def take(self, key, shape):
+        ent = self.table.get(key)
+        if ent is None or tuple(ent[1]) != tuple(shape):
+            return None
+        off, shp = ent
+        n = 1
+        for d in shp:
+            n *= int(d)
+        return self.flat[off:off + n].view(shp)
+
+
+def _gout(key, shape, device, zero=False):
+    """Gradient output for the parameter whose storage starts at `key` (data_ptr): its bucket slice when a sink is active."""
+    if GRAD_SINK is not None and key is not None:
+        v = GRAD_SINK.take(key, shape)
+        if v is not None:
+            return v
+    return (torch.zeros if zero else torch.empty)(shape, dtype=torch.float32, device=device)
+
+
 _WS = {}
 
 
@@ -174,6 +206,7 @@ class EmbeddingFn(torch.autograd.Function):
         _call("pb_embedding_fwd", _p(tok), _p(table.contiguous()), _p(out), B * L, C, V, dt, _st())
         ctx.save_for_backward(tok)
         ctx.shape = (V, C, dt)
+        ctx.key = table.data_ptr()
         return out
 
     @staticmethod
@@ -181,7 +214,7 @@ class EmbeddingFn(torch.autograd.Function):
         (tok,) = ctx.saved_tensors
         V, C, dt = ctx.shape
         dout = dout.contiguous()
-        dtable = torch.empty((V, C), dtype=torch.float32, device=dout.device)
+        dtable = _gout(ctx.key, (V, C), dout.device)
         _call("pb_embedding_bwd", _p(tok), _p(dout), _p(dtable), tok.numel(), C, V, dt, _st())
         return None, dtable, None
 
@@ -209,6 +242,7 @@ class LinearActFn(torch.autograd.Function):
             _call("pb_linear_fwd", _p(x), _p(W), _p(b), _p(z), _p(y), M, N, K, act, _p(ws), ws.numel(), _st())
         ctx.act = act
         ctx.tc = tc
+        ctx.keys = (W.data_ptr(), None if b is None else b.data_ptr())
         ctx.needs = (ctx.needs_input_grad[0], ctx.needs_input_grad[1])
         ctx.save_for_backward(x, W, z if act == ACT_GELU else (y if act == ACT_SIGMOID else None))
         return y
@@ -222,8 +256,8 @@ class LinearActFn(torch.autograd.Function):
         need_dx, need_dw = ctx.needs
         dz = torch.empty((M, N), dtype=torch.float32, device=dy.device)
         dx = torch.empty((M, K), dtype=torch.float32, device=dy.device) if need_dx else None
-        dW = torch.empty((N, K), dtype=torch.float32, device=dy.device) if need_dw else None
-        db = torch.empty((N,), dtype=torch.float32, device=dy.device)
+        dW = _gout(ctx.keys[0], (N, K), dy.device) if need_dw else None
+        db = _gout(ctx.keys[1], (N,), dy.device)
         if ctx.tc:
             ws = _workspace(lib().pb_linear_tc_workspace(M, N, K), dy.device)
             _call("pb_linear_bwd_tc", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
@@ -420,6 +454,9 @@ class GTrackFn(torch.autograd.Function):
         ctx.save_for_backward(g, pool, Wp, gamma1, W4, gamma2, buf, rstd, W1, W3, zg2, z32)
         ctx.cfg = (B, G, C, has_post, has_pre)
         ctx.link_in, ctx.link_out = link_in, link_out
+        kp = lambda t: None if t is None else t.data_ptr()
+        ctx.keys = {n: kp(t) for n, t in (("Wp", Wp), ("gamma1", gamma1), ("beta1", beta1), ("W4", W4), ("b4", b4), ("gamma2", gamma2),
+                                          ("beta2", beta2), ("W1", W1), ("b1", b1), ("W3", W3), ("b3", b3))}
         if has_pre and link_out is not None:
             link_out.z3 = z32[0]
         return (buf[4] if has_post else None, zg2[1] if has_pre else None, z32[1] if has_pre else None)
@@ -445,27 +482,44 @@ class GTrackFn(torch.autograd.Function):
                 link_out.z3 = link_out.dz3 = link_out.dgh_ptr = None
             dzg, dg_total = f32(B, C), f32(B, G)
         # ---- post half (block i)
-        out = vec = dWp = None
+        out = dWp = None
         z3_here = link_in.z3 if (has_post and link_in is not None) else None
         if has_post:
             out = f32(6 if z3_here is not None else 5, B, G)                      # dv2, dz4, dg1, dv1, dpool[, dz3 of this block]
             if not has_pre and dg2 is None:
                 dg2 = torch.zeros((B, G), dtype=torch.float32, device=dev)
-        # the 16-row groups of the batch (one cluster each) meet in the column sums: those outputs are accumulated into one
-        # zero-filled buffer  [dgamma1, dbeta1, db4, dgamma2, dbeta2 | db3 | db1 | dWp]
+        # the 16-row groups of the batch (one cluster each) meet in the column sums: those outputs are accumulated, zero on
+        # entry.  With a gradient sink they are the parameters' bucket slices (cleared once per step by the bucket); otherwise
+        # one zero-filled buffer  [dgamma1, dbeta1, db4, dgamma2, dbeta2 | db3 | db1 | dWp]
         Kd = Wp.numel() if has_post else 0
-        acc = torch.zeros(((5 * G if has_post else 0) + (G + C if has_pre else 0) + Kd,), dtype=torch.float32, device=dev)
-        pos = 0
-        if has_post:
-            vec = acc[:5 * G].view(5, G)
-            pos = 5 * G
-        if has_pre:
-            db3, db1 = acc[pos:pos + G], acc[pos + G:pos + G + C]
-            pos += G + C
-        if has_post:
-            dWp = acc[pos:pos + Kd]
+        keys = ctx.keys
+        vec_t = None
+        sunk = None
+        if GRAD_SINK is not None:
+            want = ([("gamma1", (G,)), ("beta1", (G,)), ("b4", (G,)), ("gamma2", (G,)), ("beta2", (G,)), ("Wp", (Kd,))] if has_post else []) + \
+                   ([("b3", (G,)), ("b1", (C,))] if has_pre else [])
+            got = {n: GRAD_SINK.take(keys[n], shp) for n, shp in want}
+            if all(t is not None for t in got.values()):
+                sunk = got
+        if sunk is not None:
+            if has_post:
+                vec_t = [sunk["gamma1"], sunk["beta1"], sunk["b4"], sunk["gamma2"], sunk["beta2"]]
+                dWp = sunk["Wp"]
+            if has_pre:
+                db3, db1 = sunk["b3"], sunk["b1"]
+        else:
+            acc = torch.zeros(((5 * G if has_post else 0) + (G + C if has_pre else 0) + Kd,), dtype=torch.float32, device=dev)
+            pos = 0
+            if has_post:
+                vec_t = [acc[i * G:(i + 1) * G] for i in range(5)]
+                pos = 5 * G
+            if has_pre:
+                db3, db1 = acc[pos:pos + G], acc[pos + G:pos + G + C]
+                pos += G + C
+            if has_post:
+                dWp = acc[pos:pos + Kd]
         o = lambda i: None if out is None else out[i].data_ptr()
-        v = lambda i: None if vec is None else vec[i].data_ptr()
+        v = lambda i: None if vec_t is None else vec_t[i].data_ptr()
         _call("pb_gtrack_bwd", _p(dg2l) if has_pre else None, None if zg2 is None else zg2[0].data_ptr(), _p(dz3_in),
               _p(dghn) if (has_pre and dz3_in is None) else None, (z32[0].data_ptr() if (has_pre and dz3_in is None) else None),
               _p(dg2) if has_pre else None, _p(W1), _p(W3), _p(dz3_buf), _p(dzg), _p(db1), _p(db3), _p(dg_total),
@@ -481,12 +535,12 @@ class GTrackFn(torch.autograd.Function):
         dW4 = dW1 = dW3 = None
         jobs = []
         if has_post:
-            dW4 = torch.empty_like(W4)
+            dW4 = _gout(keys["W4"], tuple(W4.shape), dev)
             jobs.append((out[1], buf[0], dW4, G, G))                               # dz4^T g1
         if has_pre:
             gp = buf[4] if has_post else g                                         # the pre half's input
             dz3 = dz3_in if dz3_in is not None else dz3_buf
-            dW3, dW1 = torch.empty_like(W3), torch.empty_like(W1)
+            dW3, dW1 = _gout(keys["W3"], tuple(W3.shape), dev), _gout(keys["W1"], tuple(W1.shape), dev)
             jobs.append((dz3, gp, dW3, G, G))
             jobs.append((dzg, gp, dW1, C, G))
 
@@ -504,12 +558,8 @@ class GTrackFn(torch.autograd.Function):
             ret_g, ret_gh, ret_pool = out[3], out[3], out[4]          # dv1 is the gradient of g and of gh; dpool = coef * dv1
         else:
             ret_g, ret_gh, ret_pool = dg_total, None, None
-        return (ret_g, ret_gh, ret_pool, dWp, v_t(vec, 0), v_t(vec, 1), dW4, v_t(vec, 2), v_t(vec, 3), v_t(vec, 4),
-                dW1, db1, dW3, db3, None, None, None)
-
-
-def v_t(vec, i):
-    return None if vec is None else vec[i]
+        vt = lambda i: None if vec_t is None else vec_t[i]
+        return (ret_g, ret_gh, ret_pool, dWp, vt(0), vt(1), dW4, vt(2), vt(3), vt(4), dW1, db1, dW3, db3, None, None, None)
 
 
 def global_fused_ok(B, G, C) -> bool:
@@ -633,6 +683,7 @@ class LocalTrackFn(torch.autograd.Function):
         ctx.bwd_zero = arena.take((ZeroArena._acc_floats(B, L, C),), torch.float32) if arena is not None else None
         ctx.staged = staged
         ctx.cfg = (B, L, C, G, ksize, dil, dt, bool(head_grads), len(head_wv))
+        ctx.keys = tuple(t.data_ptr() for t in (Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b))
         return h2, pool
 
     @staticmethod
@@ -662,6 +713,12 @@ class LocalTrackFn(torch.autograd.Function):
         dln2w, dln2b = arena[2 * L * C:3 * L * C].view(L, C), arena[3 * L * C:4 * L * C].view(L, C)
         o = 4 * L * C
         dbn, dbw, db2 = arena[o:o + C], arena[o + C:o + 2 * C], arena[o + 2 * C:o + 3 * C]
+        kWn, kbn, kWw, kbw, kl1w, kl1b, kW2, kb2, kl2w, kl2b = ctx.keys
+        if GRAD_SINK is not None:          # accumulated parameter gradients: the bucket's slices (cleared once per step) instead
+            got = [GRAD_SINK.take(k_, shp) for k_, shp in ((kl1w, (L, C)), (kl1b, (L, C)), (kl2w, (L, C)), (kl2b, (L, C)),
+                                                            (kbn, (C,)), (kbw, (C,)), (kb2, (C,)))]
+            if all(t is not None for t in got):
+                dln1w, dln1b, dln2w, dln2b, dbn, dbw, db2 = got
         dg2l = arena[o + 3 * C:o + 3 * C + B * C].view(B, C)
         sums_all = arena[n_acc:].view(torch.float64).view(2, B, 2)          # two [B,2] double scratch areas
 
@@ -694,7 +751,7 @@ class LocalTrackFn(torch.autograd.Function):
         fused = bool(L_.pb_ln_joint_bwd_gelu_ok(B, L, C))
         # LN2 (+ the linear layer's GELU gradient when the fused kernel takes the shape)
         du2 = torch.empty_like(x)
-        dW2 = f32(C, C)
+        dW2 = _gout(kW2, (C, C), dev)
         if fused:
             dz2 = torch.empty_like(x)
             _call("pb_ln_joint_bwd_gelu", _p(dh2t), _p(u2), _p(stats2), _p(ln2w), _p(z2), None, _p(du2), _p(dz2), None,
@@ -727,7 +784,7 @@ class LocalTrackFn(torch.autograd.Function):
             dzw = dh1                   # dead by now
         # conv pair
         dx = torch.empty_like(x)
-        dWn, dWw = f32(C, C, ksize), f32(C, C, ksize)
+        dWn, dWw = _gout(kWn, (C, C, ksize), dev), _gout(kWw, (C, C, ksize), dev)
         if side is None:
             _call("pb_conv_pair_bwd", _p(du1), None if fused else _p(zn), None if fused else _p(zw), _p(x), _p(wn_b), _p(ww_b), _p(dzn),
                                       _p(dzw), _p(dx), _p(dWn), _p(dWw), _p(dbn), _p(dbw), _p(dg2l), B, L, C, ksize, dil, dt,
@@ -801,6 +858,7 @@ class TokenHeadFn(torch.autograd.Function):
         p = torch.empty((B, L, V), dtype=torch.float32, device=dev)
         tc = dt == BF16 and bool(lib().pb_token_head_tc_ok(B, L, C, V))
         ctx.tc = tc
+        ctx.keys = (Wo.data_ptr(), bo.data_ptr())
         if tc:
             # Wo zero-padded to 128 vocabulary rows, and its transpose: the K-major operands of the two GEMMs
             pad = torch.zeros((2, 128, C), dtype=torch.bfloat16, device=dev) if C == 128 else None
@@ -829,12 +887,18 @@ class TokenHeadFn(torch.autograd.Function):
             woT_pad = ctx.saved_tensors[3]
             dlogit = torch.empty((B * L, 128), dtype=torch.bfloat16, device=dev)
             dWo_pad = torch.empty((128, C), dtype=torch.float32, device=dev)
-            dbo = torch.zeros((V,), dtype=torch.float32, device=dev)
+            dbo = _gout(ctx.keys[1], (V,), dev, zero=True)
             _call("pb_token_head_bwd_tc", _p(dP), _p(p), _p(h), _p(woT_pad), None, _p(dlogit), _p(dh), _p(dWo_pad), _p(dbo),
                   B, L, C, V, *_wgrad_ws(dev), _st())
-            return dh, dWo_pad[:V], dbo
-        dWo = torch.empty_like(Wo)
-        dbo = torch.empty((V,), dtype=torch.float32, device=dev)
+            dWo = dWo_pad[:V]
+            if GRAD_SINK is not None:
+                sl = GRAD_SINK.take(ctx.keys[0], (V, C))
+                if sl is not None:
+                    sl.copy_(dWo)               # 26 x 128 floats: the padded GEMM output cannot alias the bucket
+                    dWo = sl
+            return dh, dWo, dbo
+        dWo = _gout(ctx.keys[0], tuple(Wo.shape), dev)
+        dbo = _gout(ctx.keys[1], (V,), dev)
         _call("pb_token_head_bwd", _p(dP), _p(p), _p(h), _p(Wo.contiguous()), None, _p(dh), _p(dWo), _p(dbo), B, L, C, V,
               dt, _st())
         return dh, dWo, dbo

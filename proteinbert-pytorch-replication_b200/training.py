@@ -32,9 +32,11 @@ def _clear_grads(model):
             t.grad = None
 
 
-def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None) -> torch.Tensor:
+def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None, grad_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
     """forward + loss + backward (utils.py:291-299 without the optimizer).  Gradients are left in ``.grad``
-    (averaged over ranks when a reducer is given).  Returns the detached loss."""
+    (averaged over ranks when a reducer is given).  ``grad_scale``: a float64 scalar tensor on the model's device that
+    backward starts from instead of 1 (data-parallel steps fold 1/world in here, so the summed gradients are the mean).
+    Returns the detached loss."""
     _clear_grads(model)
     p_local, p_global = model(X)
     loss = pretraining_loss(p_local, p_global, Y, W)
@@ -42,7 +44,7 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None)
         reducer.prepare()
     ops.DEFER_WGRAD_JOIN = reducer is None          # the eager bucket hooks read gradients as they appear: join per block then
     try:
-        loss.backward()
+        loss.backward(gradient=grad_scale)
     finally:
         ops.DEFER_WGRAD_JOIN = False
         ops.join_side_streams()                     # weight gradients issued on the side stream (ops.LocalTrackFn)
@@ -51,73 +53,170 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None)
     return loss.detach()
 
 
-class FlatGradBucket:
-    """All registered gradients as ONE flat buffer: a gather kernel after backward, one NCCL all-reduce over
-    NVLink/NVSwitch, a scatter kernel that also applies 1/world.  Used by GraphedPretrainStep when the job is
-    data-parallel (the gradient tensors have fixed addresses once the step is captured)."""
+def _needs_zero(name: str) -> bool:
+    """Gradients the kernels ACCUMULATE into (LayerNorm affines, biases, W_parameter): their bucket slices are cleared once per step."""
+    return "_norm_" in name or name.endswith(".bias") or name.endswith("W_parameter")
 
-    def __init__(self, params, group=None):
-        import numpy as np
+
+def _is_block_pre_param(name: str) -> bool:
+    """A block's global-to-local linear and first global linear: with cluster units their gradients are produced together with
+    the block BELOW (ops.GTrackFn spans the boundary), so they close their block's group in the bucket."""
+    return ".global_to_local_linear_layer." in name or ".global_linear_layer_1." in name
+
+
+class FlatGradBucket:
+    """All registered gradients in ONE flat float32 buffer, laid out in the order backward produces them: output heads, blocks
+    last to first, then the embedding and the annotation-input layer.  While the step runs with the bucket's sink
+    (``ops.GRAD_SINK``), the backward kernels write every gradient straight into its slice and autograd adopts those slices as
+    ``.grad``: the data-parallel exchange is then NCCL all-reduces over contiguous ranges of this buffer, with no gather or
+    scatter pass and no separate scaling (1/world enters through the loss gradient).  Parameters whose ``.grad`` does not end
+    up aliasing its slice (a backward path that does not use the sink) are copied in and out by ``pb_flat_copy``."""
+
+    ALIGN = 128          # floats: every group starts 512-byte aligned (NCCL chunks), every tensor 16-byte aligned
+
+    def __init__(self, model, group=None):
         self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.params = [p for p in params if p.requires_grad]
-        if any(p.grad is None for p in self.params):
-            raise RuntimeError("FlatGradBucket needs materialised .grad tensors (run one step first)")
-        dev = self.params[0].device
-        rows, off = [], 0
-        for p in self.params:
-            g = p.grad
-            if not g.is_contiguous() or g.dtype != torch.float32:
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        nblk = len(model.proteinBERT_blocks)
+
+        def grp(n):
+            if n.startswith("pretraining_"):
+                return 0
+            if n.startswith("proteinBERT_blocks."):
+                return 1 + (nblk - 1 - int(n.split(".")[1]))
+            return 1 + nblk
+
+        def rank_in_group(n):            # accumulated tensors first (one clear per group), the block's pre-half parameters last
+            return (2 if _is_block_pre_param(n) else 0) + (0 if _needs_zero(n) else 1)
+
+        order = sorted(range(len(named)), key=lambda i: (grp(named[i][0]), rank_in_group(named[i][0]), i))
+        dev = named[0][1].device
+        self.table, self.slices, self.zero_ranges, self.group_ranges = {}, {}, [], []
+        self.pre_split = {}              # group -> offset where its pre-half parameters start
+        off, cur, gstart, zstart, zend = 0, None, 0, None, None
+        for i in order:
+            n, p = named[i]
+            g = grp(n)
+            if g != cur:
+                if cur is not None:
+                    self.group_ranges.append((cur, gstart, off))
+                    if zstart is not None:
+                        self.zero_ranges.append((zstart, zend))
+                off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+                cur, gstart, zstart, zend = g, off, None, None
+            if _is_block_pre_param(n) and g not in self.pre_split:
+                off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+                self.pre_split[g] = off
+            if not p.is_contiguous() or p.dtype != torch.float32:
+                raise RuntimeError("FlatGradBucket needs contiguous float32 parameters")
+            self.table[p.data_ptr()] = (off, tuple(p.shape))
+            self.slices[n] = (off, p.numel())
+            if _needs_zero(n) and not _is_block_pre_param(n):
+                zstart = off if zstart is None else zstart
+                zend = off + p.numel()
+            elif _needs_zero(n):
+                self.zero_ranges.append((off, off + p.numel()))
+            off += (p.numel() + 3) // 4 * 4
+        self.group_ranges.append((cur, gstart, off))
+        if zstart is not None:
+            self.zero_ranges.append((zstart, zend))
+        self.numel = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.flat = torch.zeros((self.numel,), dtype=torch.float32, device=dev)
+        self.params = dict(named)
+        self.loose, self._loose_table, self._loose_n = [], None, 0
+        self.nblk = nblk
+
+    def sink(self):
+        return ops.GradSink(self.flat, self.table)
+
+    def zero(self):
+        """Clear the accumulated slices (a handful of small memsets, ~1 MB per block)."""
+        for a, b in self.zero_ranges:
+            self.flat[a:b].zero_()
+
+    def view(self, name):
+        off, n = self.slices[name]
+        return self.flat[off:off + n].view(self.params[name].shape)
+
+    def adopt(self):
+        """After a step ran with the sink: note which parameters' .grad really alias their slice; the others ("loose") get
+        a pb_flat_copy table so that they still travel with the bucket."""
+        import numpy as np
+        rows, self.loose = [], []
+        base, piece = self.flat.data_ptr(), 1 << 16
+        for n, p in self.params.items():
+            off, numel = self.slices[n]
+            if p.grad is None:
+                raise RuntimeError(f"{n} has no gradient after the step")
+            if p.grad.data_ptr() == base + 4 * off and p.grad.is_contiguous():
+                continue
+            if not p.grad.is_contiguous() or p.grad.dtype != torch.float32:
                 raise RuntimeError("gradients must be contiguous float32")
-            # big tensors are cut into 64k-element pieces so the one-launch copy spreads over the whole GPU
-            piece = 1 << 16
-            for s0 in range(0, g.numel(), piece):
-                rows.append((g.data_ptr() + 4 * s0, off + s0, min(piece, g.numel() - s0)))
-            off += (g.numel() + 3) // 4 * 4                      # keep every tensor 16-byte aligned in the bucket
-        self.numel = off
-        self.flat = torch.zeros((off,), dtype=torch.float32, device=dev)
-        arr = np.array(rows, dtype=[("ptr", "<u8"), ("offset", "<i8"), ("numel", "<i8")])
-        self.table = torch.from_numpy(arr.view(np.uint8).copy()).to(dev)
-        self.n = len(rows)
-        self._ptrs = [p.grad.data_ptr() for p in self.params]
+            self.loose.append(n)
+            for s0 in range(0, numel, piece):
+                rows.append((p.grad.data_ptr() + 4 * s0, off + s0, min(piece, numel - s0)))
+        self._loose_n = len(rows)
+        if rows:
+            arr = np.array(rows, dtype=[("ptr", "<u8"), ("offset", "<i8"), ("numel", "<i8")])
+            self._loose_table = torch.from_numpy(arr.view(np.uint8).copy()).to(self.flat.device)
+        self._ptrs = {n: p.grad.data_ptr() for n, p in self.params.items()}
 
     def check(self):
-        if [p.grad.data_ptr() for p in self.params] != self._ptrs:
-            raise RuntimeError("gradient tensors moved since the bucket was built")
+        for n, p in self.params.items():
+            if p.grad is None or p.grad.data_ptr() != self._ptrs[n]:
+                raise RuntimeError(f"gradient tensor of {n} moved since the bucket was built")
 
-    def gather(self):
-        ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 1, 1.0,
-                  torch.cuda.current_stream().cuda_stream)
+    def gather_loose(self):
+        if self._loose_n:
+            ops._call("pb_flat_copy", self._loose_table.data_ptr(), self._loose_n, self.flat.data_ptr(), 1, 1.0,
+                      torch.cuda.current_stream().cuda_stream)
 
-    def all_reduce(self, async_op: bool = False):
+    def scatter_loose(self):
+        if self._loose_n:
+            ops._call("pb_flat_copy", self._loose_table.data_ptr(), self._loose_n, self.flat.data_ptr(), 0, 1.0,
+                      torch.cuda.current_stream().cuda_stream)
+
+    def split_offset(self, cut_block: int) -> int:
+        """Bucket offset that separates what backward has produced once it has gone down to the input of block `cut_block`
+        (heads, blocks above it, and the block itself without its pre-half parameters) from the rest."""
+        g = 1 + (self.nblk - 1 - cut_block)
+        if g in self.pre_split:
+            return self.pre_split[g]
+        for (gg, a, b) in self.group_ranges:
+            if gg == g:
+                return b
+        return self.numel
+
+    def all_reduce(self, a: int = 0, b: Optional[int] = None, async_op: bool = False):
         if self.world > 1:
-            return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+            b = self.numel if b is None else b
+            return dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
         return None
-
-    def scatter(self):
-        ops._call("pb_flat_copy", self.table.data_ptr(), self.n, self.flat.data_ptr(), 0, 1.0 / self.world,
-                  torch.cuda.current_stream().cuda_stream)
 
 
 class GraphedPretrainStep:
-    """forward + loss + backward captured once in a CUDA graph and replayed per step.
+    """forward + loss + backward captured once in CUDA graphs and replayed per step.
 
-    The step is ~170 short kernel launches; issued one by one from Python they cost more host time than the GPU
+    The step is ~160 short kernel launches; issued one by one from Python they cost more host time than the GPU
     needs to run them, so the public fast path is: copy the batch into static device buffers (one async H2D per
-    tensor, from pinned memory if the caller provides it), replay the graph, read the loss.  Gradients are
+    tensor, from pinned memory if the caller provides it), replay, read the loss.  Gradients are
     written to the parameters' static ``.grad`` tensors, ready for ``optimizer.step()``.  Shapes are fixed at
-    construction.  Under torch.distributed (world > 1) the registered gradients are then gathered into one flat bucket
-    (one kernel), all-reduced by NCCL over NVLink/NVSwitch and scattered back with 1/world applied (one kernel).
-    ``overlap=True`` captures backward as TWO graphs split at the middle block instead and all-reduces the first
-    half's bucket asynchronously while the second graph replays.  Measured on 2 x B200 (2.08 ms single-GPU step):
-    2.31 ms without, 2.39 ms with the split -- the NCCL kernel takes SMs from the one-wave persistent kernels of the
-    second graph, which costs more than the 0.07 ms of all-reduce it hides -- so the default is off.
+    construction.
+
+    Data-parallel (torch.distributed initialised with world > 1): every gradient is written by its kernel into ONE flat
+    bucket (``FlatGradBucket``; ``.grad`` are views of it, 1/world is folded into the loss gradient) and backward is captured
+    as TWO graphs split at the middle block.  Per step: replay A (forward, loss, backward of the heads and the upper
+    blocks) -> asynchronous NCCL all-reduce of the first part of the bucket on NCCL's stream -> replay B (the lower
+    blocks, embedding, annotation-input layer) while that all-reduce runs -> all-reduce of the rest -> join.  No gather,
+    scatter or scaling kernels.  ``overlap=False`` keeps one graph and one all-reduce after it.
 
         step = GraphedPretrainStep(model, X, Y, W)      # example batch fixes shapes / dtypes
         loss = step(X, Y, W)                            # host or device tensors
     """
 
-    def __init__(self, model, X, Y, W, warmup: int = 3, overlap: bool = False, force_split: bool = False):
+    def __init__(self, model, X, Y, W, warmup: int = 3, overlap: bool = True, force_split: bool = False, force_bucket: bool = False):
+        import os
         dev = next(model.parameters()).device
         self.model = model
         self.device = dev
@@ -125,28 +224,43 @@ class GraphedPretrainStep:
         self.static = [t.to(dev).clone() for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"])]
         sx, sy, sw = self._dicts()
         distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        self.world = dist.get_world_size() if distributed else 1
         nblk = len(model.proteinBERT_blocks)
         self.split = ((distributed and overlap) or force_split) and nblk >= 2
-        self.bucket = self.bucket_a = self.bucket_b = None
+        self.bucket = FlatGradBucket(model) if (distributed or force_bucket or force_split) else None
         self.graph_b = None
+        self.launches_outside_graph = 0
         cut = nblk // 2
+        self.cut_offset = self.bucket.split_offset(cut) if (self.bucket is not None and self.split) else None
+        scale = None
+        if self.world > 1:
+            scale = torch.tensor(1.0 / self.world, dtype=torch.float64, device=dev)      # sum over ranks -> mean
+        self._scale = scale
 
-        # ---- two-stage backward (data-parallel): stage A = forward + loss + backward down to the input of block
-        # `cut`; stage B = the rest.  The gradients of stage A are all-reduced while stage B runs.
-        # with cluster units (ops.GTrackFn) the pre half of block `cut` (its global-to-local and first global linear) is
-        # computed -- and differentiated -- together with the post half of block cut-1, i.e. below the cut
+        # ---- two-stage backward: stage A = forward + loss + backward down to the input of block `cut`; stage B = the rest.
+        # With cluster units (ops.GTrackFn) the pre half of block `cut` (its global-to-local and first global linear) is
+        # computed -- and differentiated -- together with the post half of block cut-1, i.e. below the cut.
         straddle = (f"proteinBERT_blocks.{cut}.global_to_local_linear_layer.", f"proteinBERT_blocks.{cut}.global_linear_layer_1.") \
             if model.uses_cluster_units(self.static[0].shape[0]) else ()
         upper = [p for n, p in model.named_parameters()
                  if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut
                                                      and not n.startswith(straddle))]
-        upper_ids = {id(p) for p in upper}
-        lower = [p for p in model.parameters() if id(p) not in upper_ids]
         upper_heads = [h.Wv_parameter for blk in list(model.proteinBERT_blocks)[cut:]
                        for h in blk.global_attention_layer.global_attention_heads if blk.head_grads]
 
+        def with_sink(fn):
+            if self.bucket is None:
+                return fn()
+            ops.GRAD_SINK = self.bucket.sink()
+            try:
+                return fn()
+            finally:
+                ops.GRAD_SINK = None
+
         def stage_a():
             _clear_grads(model)
+            if self.bucket is not None:
+                self.bucket.zero()
             model._boundary_at = cut
             try:
                 p_local, p_global = model(sx)
@@ -157,7 +271,7 @@ class GraphedPretrainStep:
             model._boundary = None
             ops.DEFER_WGRAD_JOIN = True
             try:
-                grads = torch.autograd.grad(loss, upper + upper_heads + bnd, retain_graph=True)
+                grads = torch.autograd.grad(loss, upper + upper_heads + bnd, grad_outputs=scale, retain_graph=True)
             finally:
                 ops.DEFER_WGRAD_JOIN = False
                 ops.join_side_streams()
@@ -173,14 +287,19 @@ class GraphedPretrainStep:
                 ops.DEFER_WGRAD_JOIN = False
                 ops.join_side_streams()
 
+        def one_graph_step():
+            if self.bucket is not None:
+                # _clear_grads happens inside pretraining_step; the accumulated bucket slices are cleared first
+                self.bucket.zero()
+            return pretraining_step(model, sx, sy, sw, grad_scale=scale)
+
         def full_step():
             if self.split:
-                out = stage_a()
-                stage_b(*out[1:])
+                out = with_sink(stage_a)
+                with_sink(lambda: stage_b(*out[1:]))
                 return out[0]
-            return pretraining_step(model, sx, sy, sw)
+            return with_sink(one_graph_step)
 
-        import os
         # the step is captured on a high-priority stream: when SMs free up, the critical path's CTAs are placed before the
         # weight-gradient CTAs waiting on the (default-priority) side stream.  Measured: 1.761 -> 1.750 ms per step.
         hipri = os.environ.get("PB_B200_CAPTURE_PRIORITY", "1") == "1"
@@ -196,19 +315,18 @@ class GraphedPretrainStep:
         cap = {"stream": side} if hipri else {}
         if self.split:
             with torch.cuda.graph(self.graph, **cap):
-                out = stage_a()
+                out = with_sink(stage_a)
             self.loss = out[0]
             self.graph_b = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self.graph_b, pool=self.graph.pool()):
-                stage_b(*out[1:])
+            with torch.cuda.graph(self.graph_b, pool=self.graph.pool(), **cap):
+                with_sink(lambda: stage_b(*out[1:]))
             del out
-            self.bucket_a = FlatGradBucket(upper)
-            self.bucket_b = FlatGradBucket(lower)
         else:
             with torch.cuda.graph(self.graph, **cap):
-                self.loss = pretraining_step(model, sx, sy, sw)
-            if distributed:        # the captured backward fixed the gradient addresses: build the flat bucket over them
-                self.bucket = FlatGradBucket(model.parameters())
+                self.loss = with_sink(one_graph_step)
+        if self.bucket is not None:         # the captured backward fixed the gradient addresses
+            self.bucket.adopt()
+            self.launches_outside_graph = 2 if self.bucket.loose else 0
 
     def _dicts(self):
         s = self.static
@@ -237,8 +355,7 @@ class GraphedPretrainStep:
             self._staged_done.record(self._copy_stream)
         self._staged_src = src          # strong references: an id() could be reused by a new tensor once these are freed
 
-    def __call__(self, X, Y, W, prefetch=None):
-        """One step on the batch (X, Y, W).  ``prefetch=(Xn, Yn, Wn)`` starts copying the NEXT batch while this one runs."""
+    def _load(self, X, Y, W):
         src = self._flat(X, Y, W)
         cur = torch.cuda.current_stream(self.device)
         staged = self._staged_src
@@ -252,24 +369,105 @@ class GraphedPretrainStep:
             for dst, t in zip(self.static, src):
                 if t is not dst:
                     dst.copy_(t, non_blocking=True)
+
+    def replay_local(self):
+        """The captured graphs alone: this rank's gradients (already scaled by 1/world), no exchange."""
+        self.graph.replay()
+        if self.graph_b is not None:
+            self.graph_b.replay()
+
+    def __call__(self, X, Y, W, prefetch=None):
+        """One step on the batch (X, Y, W).  ``prefetch=(Xn, Yn, Wn)`` starts copying the NEXT batch while this one runs."""
+        self._load(X, Y, W)
         self.graph.replay()
         if prefetch is not None:
             self.prefetch(*prefetch)
-        if self.split:
-            self.bucket_a.gather()
-            work = self.bucket_a.all_reduce(async_op=True)       # NCCL on its own stream ...
-            self.graph_b.replay()                                # ... while the second half of backward runs
-            self.bucket_b.gather()
-            self.bucket_b.all_reduce()
-            if work is not None:
-                work.wait()
-            self.bucket_a.scatter()
-            self.bucket_b.scatter()
-        elif self.bucket is not None:
-            self.bucket.gather()
-            self.bucket.all_reduce()
-            self.bucket.scatter()
+        bk = self.bucket
+        if bk is None or bk.world == 1:
+            if self.graph_b is not None:
+                self.graph_b.replay()
+            return self.loss
+        work = self._exchange_first()                  # NCCL on its own stream ...
+        if self.graph_b is not None:
+            self.graph_b.replay()                      # ... while the second half of backward runs
+        self._exchange_rest(work)
         return self.loss
+
+    def _exchange_first(self):
+        """After graph A: start the all-reduce of what it produced (the bucket up to the cut).  None when there is nothing to start early."""
+        bk = self.bucket
+        if self.split and not bk.loose:
+            return bk.all_reduce(0, self.cut_offset, async_op=True)
+        return None
+
+    def _exchange_rest(self, work):
+        bk = self.bucket
+        bk.gather_loose()
+        if work is None:
+            bk.all_reduce()
+        else:
+            bk.all_reduce(self.cut_offset, None)
+            work.wait()
+        bk.scatter_loose()
+
+    # ---- data-parallel diagnostics (bench.py, scripts/ddp_check.py) ---------------------------------------------------------
+    def ddp_check(self, X, Y, W) -> float:
+        """max over parameter groups of |grad after the exchange - sum over ranks of the rank-local gradients| / |that sum|.
+        The rank-local gradients carry the 1/world factor already, so their sum is the mean the reference recipe
+        ("the reference per shard, gradients averaged") asks for."""
+        bk = self.bucket
+        if bk is None:
+            return 0.0
+        self._load(X, Y, W)
+        self.replay_local()
+        bk.gather_loose()
+        local = bk.flat.clone()
+        if bk.world > 1:
+            parts = [torch.empty_like(local) for _ in range(bk.world)]
+            dist.all_gather(parts, local, group=bk.group)
+            expect = torch.stack(parts).double().sum(0)
+            # the very exchange __call__ performs (same ranges, same order), on the gradients that were just gathered:
+            # a second replay would differ from the first by the order of the kernels' float atomics
+            self._exchange_rest(self._exchange_first())
+        else:
+            expect = local.double()
+        torch.cuda.synchronize(self.device)
+        bk.gather_loose()
+        worst = 0.0
+        for (_, a, b) in bk.group_ranges:
+            den = float(expect[a:b].norm())
+            err = float((bk.flat[a:b].double() - expect[a:b]).norm())
+            worst = max(worst, err / den if den > 0 else err)
+        return worst
+
+    def comm_profile(self, X, Y, W, steps: int = 10):
+        """Per step, CUDA-event timed, max over ranks: the graphs alone, the whole step, and the all-reduce of the bucket alone."""
+        bk = self.bucket
+        if bk is None or bk.world == 1:
+            return {}
+        dev = self.device
+
+        def timed(fn):
+            for _ in range(2):
+                fn()
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(steps):
+                fn()
+            b.record()
+            torch.cuda.synchronize(dev)
+            t = torch.tensor([a.elapsed_time(b) / steps * 1e3], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t[0])
+
+        self._load(X, Y, W)
+        local_us = timed(self.replay_local)
+        full_us = timed(lambda: self(X, Y, W))
+        ar_us = timed(lambda: bk.all_reduce())
+        return {"exposed_comm_us": full_us - local_us, "step_us": full_us, "compute_only_us": local_us,
+                "allreduce_alone_us": ar_us, "allreduce_bytes": 4 * bk.numel, "bucket_loose_tensors": len(bk.loose)}
 
 
 class GradAllReducer:

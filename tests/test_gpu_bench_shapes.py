@@ -239,3 +239,25 @@ def test_conv_pair_backward_bf16_across_tile_seams(pb, B, L):
     for t in range(KS):        # every tap separately: a shifted halo row corrupts single taps, not the whole tensor
         assert rel_fro(dWn[:, :, t], wnr.grad[:, :, t]) < 3e-3, ("dWn tap", t)
         assert rel_fro(dWw[:, :, t], wwr.grad[:, :, t]) < 3e-3, ("dWw tap", t)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_rank_gradients_equal_mean_of_per_shard_gradients(pb, tmp_path):
+    """the multi-GPU oracle is 'the reference run per shard, gradients averaged'.  Two ranks, one process per
+    GPU over NCCL, each runs GraphedPretrainStep on its own shard (bucket views, two-graph backward, overlapped all-reduce);
+    checked against the sum of the rank-local gradients (exact to fp32 rounding) and against eager per-shard gradients
+    averaged on one GPU (fp32 engine, 1e-4)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "ddp.json"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29611", os.path.join(root, "scripts", "ddp_check.py"), "--out", str(out)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    res = json.load(open(out))
+    assert res["max_rel_err"] <= 1e-5, res
+    assert res["vs_eager_per_shard_mean"] <= 1e-4, res
+    assert res["loose_tensors"] == 0, res

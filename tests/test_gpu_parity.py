@@ -426,8 +426,13 @@ def test_graphed_step_and_two_stage_backward_match_eager(pb, wide_ref):
     X, Y, W = {"local": xl, "global": xg}, {"local": yl, "global": yg}, {"local": wl, "global": wg}
     loss_e = pb.pretraining_step(model, X, Y, W)
     ref = {n: p.grad.clone() for n, p in model.named_parameters()}
-    for kwargs in ({}, {"force_split": True}):
+    for kwargs in ({}, {"force_split": True}, {"force_bucket": True}):
         step = pb.GraphedPretrainStep(model, X, Y, W, warmup=1, **kwargs)
+        if kwargs:        # every gradient was written by its kernel straight into the flat bucket (no copies needed)
+            assert step.bucket is not None and step.bucket.loose == [], step.bucket.loose
+            for n, p in model.named_parameters():
+                assert p.grad.data_ptr() == step.bucket.view(n).data_ptr(), n
+            assert step.ddp_check(X, Y, W) == 0.0
         loss_g = step(X, Y, W)
         torch.cuda.synchronize()
         assert abs(float(loss_g) - float(loss_e)) <= 1e-6 * abs(float(loss_e))
