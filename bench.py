@@ -451,6 +451,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (e.g. configs[2]: global batch 512 -> 512 / N)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=1, help="capture the step in a CUDA graph for the `value` leg")
+    ap.add_argument("--ddp-overlap", type=int, default=1, help="N > 1: two-graph backward with the first all-reduce under the second graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-baseline", action="store_true")
     ap.add_argument("--no-kernel-table", action="store_true")
@@ -515,7 +516,7 @@ def main():
     if args.graph:
         try:
             n0 = pb.launch_count()
-            graph = pb.GraphedPretrainStep(model, X, Y, W, warmup=1)
+            graph = pb.GraphedPretrainStep(model, X, Y, W, warmup=1, overlap=bool(args.ddp_overlap))
             launches_per_step = (pb.launch_count() - n0) // 2          # one warm-up step + the captured step
             graph(X, Y, W)
             torch.cuda.synchronize()

@@ -75,7 +75,8 @@ typedef struct pb_stage_desc {
 int pb_stage_weights(const pb_stage_desc* jobs_dev, int n, int dt, void* stream);
 
 /* Gradient bucket of the data-parallel step: gather n float tensors into one flat
- * buffer (to_flat = 1) or scatter the buffer back, multiplied by `scale` (to_flat = 0), in one launch.  The
+ * buffer (to_flat = 1), scatter the buffer back, multiplied by `scale` (to_flat = 0), or clear the listed ranges of the
+ * buffer (to_flat = 2: the accumulated gradient slices, once per step; ptr is ignored), in one launch.  The
  * reference is single-process; this serves the one exchange step of the batch-sharded path (NCCL all-reduce). */
 typedef struct pb_chunk_desc {
     float* ptr;

@@ -125,7 +125,11 @@ __global__ void flat_copy_kernel(const pb_chunk_desc* __restrict__ chunks, float
     const long long n4 = ((((uintptr_t)t | (uintptr_t)f) & 15) == 0) ? c.numel / 4 : 0;
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (to_flat) {
+    if (to_flat == 2) {                      // clear the range (ptr is not read)
+        const long long z4 = (((uintptr_t)f & 15) == 0) ? c.numel / 4 : 0;
+        for (long long i = tid; i < z4; i += stride) reinterpret_cast<float4*>(f)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (long long i = z4 * 4 + tid; i < c.numel; i += stride) f[i] = 0.f;
+    } else if (to_flat) {
         for (long long i = tid; i < n4; i += stride) reinterpret_cast<float4*>(f)[i] = reinterpret_cast<const float4*>(t)[i];
         for (long long i = n4 * 4 + tid; i < c.numel; i += stride) f[i] = t[i];
     } else {

@@ -267,15 +267,19 @@ class ProteinBERT(nn.Module):
             none7 = (None,) * 7
             _, g2l, gh = ops.GTrackFn.apply(g, None, None, *none7, *blocks[0].global_pre_params(), Cdim, None, links[0])
             for i, blk in enumerate(blocks):
-                if cut is not None and i == cut:
-                    self._boundary = (h, g, g2l, gh)
                 blk._prestaged = dt
                 h, pool = blk.local_track(h, g2l, arena)
+                if cut is not None and i + 1 == cut:
+                    # a proper cut of the autograd graph: everything above consumes only these four tensors (the inputs of the
+                    # unit that spans the boundary and of block `cut`'s local track); h and pool come out of the same node
+                    h, pool, g, gh = ops.CutFn.apply(h, pool, g, gh)
+                    self._boundary = (h, pool, g, gh)
                 nxt = blocks[i + 1].global_pre_params() if i + 1 < len(blocks) else (None,) * 4
                 g, g2l, gh = ops.GTrackFn.apply(g, gh, pool, *blk.global_post_params(), *nxt, Cdim, links[i], links[i + 1])
         else:
             for i, blk in enumerate(blocks):
                 if cut is not None and i == cut:
+                    h, g = ops.CutFn.apply(h, g)
                     self._boundary = (h, g)
                 blk._prestaged = dt
                 h, g = blk.forward_channels_last(h, g, arena)

@@ -410,6 +410,22 @@ class GlobalPostFn(torch.autograd.Function):
         return out[3], out[3], out[4], dWp, vec[0], vec[1], dW4, vec[2], vec[3], vec[4], None
 
 
+class CutFn(torch.autograd.Function):
+    """Identity on a group of tensors, used to mark where GraphedPretrainStep splits backward in two.  torch.autograd.grad
+    with respect to non-leaf tensors captures the gradient at the node that PRODUCED them and still executes every node with
+    an edge into such a node -- with several producers on the cut (a block's local track and the global-track unit below it)
+    one of them would run in both halves.  Behind this node all crossing tensors have ONE producer, and nothing below it
+    runs before the second half asks for it."""
+
+    @staticmethod
+    def forward(ctx, *ts):
+        return tuple(t.view_as(t) for t in ts)
+
+    @staticmethod
+    def backward(ctx, *gs):
+        return gs
+
+
 def gtrack_ok(B, G, C) -> bool:
     return bool(lib().pb_gtrack_ok(B, G, C))
 
@@ -937,4 +953,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "GTrackFn", "GTrackLink", "gtrack_ok", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "CutFn", "GTrackFn", "GTrackLink", "gtrack_ok", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]

@@ -59,9 +59,16 @@ def _needs_zero(name: str) -> bool:
 
 
 def _is_block_pre_param(name: str) -> bool:
-    """A block's global-to-local linear and first global linear: with cluster units their gradients are produced together with
-    the block BELOW (ops.GTrackFn spans the boundary), so they close their block's group in the bucket."""
+    """A block's global-to-local linear and first global linear (modules.py:208,221: they read the block's INPUT g): the last
+    gradients its backward produces."""
     return ".global_to_local_linear_layer." in name or ".global_linear_layer_1." in name
+
+
+def _is_block_post_param(name: str) -> bool:
+    """The post half of a block's global track (modules.py:92,223-229): W_parameter, both global LayerNorms, global linear 2 --
+    the first gradients its backward produces (with cluster units: together with the block ABOVE, ops.GTrackFn spans the boundary)."""
+    return (name.endswith("global_attention_layer.W_parameter") or ".global_norm_1." in name or ".global_norm_2." in name
+            or ".global_linear_layer_2." in name)
 
 
 class FlatGradBucket:
@@ -87,53 +94,64 @@ class FlatGradBucket:
                 return 1 + (nblk - 1 - int(n.split(".")[1]))
             return 1 + nblk
 
-        def rank_in_group(n):            # accumulated tensors first (one clear per group), the block's pre-half parameters last
-            return (2 if _is_block_pre_param(n) else 0) + (0 if _needs_zero(n) else 1)
+        def rank_in_group(n):            # production order inside a block: post half, local track, pre half; accumulated tensors first in each
+            part = 0 if _is_block_post_param(n) else (2 if _is_block_pre_param(n) else 1)
+            return 2 * part + (0 if _needs_zero(n) else 1)
 
         order = sorted(range(len(named)), key=lambda i: (grp(named[i][0]), rank_in_group(named[i][0]), i))
         dev = named[0][1].device
         self.table, self.slices, self.zero_ranges, self.group_ranges = {}, {}, [], []
-        self.pre_split = {}              # group -> offset where its pre-half parameters start
-        off, cur, gstart, zstart, zend = 0, None, 0, None, None
+        self.post_end = {}               # group -> offset where the block's post-half parameters end
+        off, cur, cur_rank, gstart = 0, None, None, 0
         for i in order:
             n, p = named[i]
-            g = grp(n)
+            g, r = grp(n), rank_in_group(n)
             if g != cur:
                 if cur is not None:
                     self.group_ranges.append((cur, gstart, off))
-                    if zstart is not None:
-                        self.zero_ranges.append((zstart, zend))
                 off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
-                cur, gstart, zstart, zend = g, off, None, None
-            if _is_block_pre_param(n) and g not in self.pre_split:
-                off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
-                self.pre_split[g] = off
+                cur, gstart, cur_rank = g, off, None
+            if r != cur_rank:
+                if cur_rank is not None and cur_rank < 2 <= r:
+                    off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+                    self.post_end[g] = off
+                cur_rank = r
             if not p.is_contiguous() or p.dtype != torch.float32:
                 raise RuntimeError("FlatGradBucket needs contiguous float32 parameters")
             self.table[p.data_ptr()] = (off, tuple(p.shape))
             self.slices[n] = (off, p.numel())
-            if _needs_zero(n) and not _is_block_pre_param(n):
-                zstart = off if zstart is None else zstart
-                zend = off + p.numel()
-            elif _needs_zero(n):
-                self.zero_ranges.append((off, off + p.numel()))
+            if _needs_zero(n):
+                if self.zero_ranges and self.zero_ranges[-1][1] == off:
+                    self.zero_ranges[-1] = (self.zero_ranges[-1][0], off + (p.numel() + 3) // 4 * 4)
+                else:
+                    self.zero_ranges.append((off, off + (p.numel() + 3) // 4 * 4))
             off += (p.numel() + 3) // 4 * 4
         self.group_ranges.append((cur, gstart, off))
-        if zstart is not None:
-            self.zero_ranges.append((zstart, zend))
         self.numel = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
         self.flat = torch.zeros((self.numel,), dtype=torch.float32, device=dev)
         self.params = dict(named)
         self.loose, self._loose_table, self._loose_n = [], None, 0
         self.nblk = nblk
+        import numpy as np
+        rows = []
+        for a, b in self.zero_ranges:            # pieces of <= 64k floats so that the one clearing launch spreads over the GPU
+            for s0 in range(a, b, 1 << 16):
+                rows.append((0, s0, min(1 << 16, b - s0)))
+        arr = np.array(rows, dtype=[("ptr", "<u8"), ("offset", "<i8"), ("numel", "<i8")])
+        self._zero_table = torch.from_numpy(arr.view(np.uint8).copy()).to(dev)
+        self._zero_n = len(rows)
 
     def sink(self):
         return ops.GradSink(self.flat, self.table)
 
     def zero(self):
-        """Clear the accumulated slices (a handful of small memsets, ~1 MB per block)."""
-        for a, b in self.zero_ranges:
-            self.flat[a:b].zero_()
+        """Clear the accumulated slices (~1 MB per block) with one launch."""
+        if self.flat.is_cuda:
+            ops._call("pb_flat_copy", self._zero_table.data_ptr(), self._zero_n, self.flat.data_ptr(), 2, 0.0,
+                      torch.cuda.current_stream().cuda_stream)
+        else:
+            for a, b in self.zero_ranges:
+                self.flat[a:b].zero_()
 
     def view(self, name):
         off, n = self.slices[name]
@@ -177,12 +195,13 @@ class FlatGradBucket:
             ops._call("pb_flat_copy", self._loose_table.data_ptr(), self._loose_n, self.flat.data_ptr(), 0, 1.0,
                       torch.cuda.current_stream().cuda_stream)
 
-    def split_offset(self, cut_block: int) -> int:
-        """Bucket offset that separates what backward has produced once it has gone down to the input of block `cut_block`
-        (heads, blocks above it, and the block itself without its pre-half parameters) from the rest."""
-        g = 1 + (self.nblk - 1 - cut_block)
-        if g in self.pre_split:
-            return self.pre_split[g]
+    def split_offset(self, cut_block: int, units: bool) -> int:
+        """Bucket offset below which everything has been produced once backward has come down to the input of block `cut_block`:
+        the heads and the blocks from the top down to it -- and, with cluster units, the post half of the block below, whose
+        gradients come out of the unit that spans the boundary."""
+        g = 1 + (self.nblk - 1 - cut_block)             # the group of block cut_block; the block below is group g + 1
+        if units and (g + 1) in self.post_end:
+            return self.post_end[g + 1]
         for (gg, a, b) in self.group_ranges:
             if gg == g:
                 return b
@@ -231,20 +250,20 @@ class GraphedPretrainStep:
         self.graph_b = None
         self.launches_outside_graph = 0
         cut = nblk // 2
-        self.cut_offset = self.bucket.split_offset(cut) if (self.bucket is not None and self.split) else None
+        units = model.uses_cluster_units(self.static[0].shape[0])
+        self.cut_offset = self.bucket.split_offset(cut, units) if (self.bucket is not None and self.split) else None
         scale = None
         if self.world > 1:
             scale = torch.tensor(1.0 / self.world, dtype=torch.float64, device=dev)      # sum over ranks -> mean
         self._scale = scale
 
         # ---- two-stage backward: stage A = forward + loss + backward down to the input of block `cut`; stage B = the rest.
-        # With cluster units (ops.GTrackFn) the pre half of block `cut` (its global-to-local and first global linear) is
-        # computed -- and differentiated -- together with the post half of block cut-1, i.e. below the cut.
-        straddle = (f"proteinBERT_blocks.{cut}.global_to_local_linear_layer.", f"proteinBERT_blocks.{cut}.global_linear_layer_1.") \
-            if model.uses_cluster_units(self.static[0].shape[0]) else ()
+        # With cluster units (ops.GTrackFn) the unit that spans the boundary -- post half of block cut-1, pre half of block cut --
+        # runs in stage A (its inputs are the cut), so the post-half parameters of block cut-1 are produced above the cut.
+        below = f"proteinBERT_blocks.{cut - 1}."
         upper = [p for n, p in model.named_parameters()
-                 if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut
-                                                     and not n.startswith(straddle))]
+                 if n.startswith("pretraining_") or (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= cut)
+                 or (units and n.startswith(below) and _is_block_post_param(n))]
         upper_heads = [h.Wv_parameter for blk in list(model.proteinBERT_blocks)[cut:]
                        for h in blk.global_attention_layer.global_attention_heads if blk.head_grads]
 

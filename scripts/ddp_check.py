@@ -46,17 +46,19 @@ step = pb.GraphedPretrainStep(model, *d(shards[rank]), warmup=1)
 check = step.ddp_check(*d(shards[rank]))
 step(*d(shards[rank]))
 torch.cuda.synchronize()
-worst, worst_name = 0.0, ""
+worst, worst_name, worst_wp = 0.0, "", 0.0
 gmax = max(float(v.abs().max()) for v in want.values())
 for n, p in model.named_parameters():
     ref = want[n]
     err = float((p.grad.double() - ref).norm())
     den = float(ref.norm()) + 1e-6 * gmax * ref.numel() ** 0.5        # absolute floor for mathematically-zero gradients
-    if err / den > worst:
+    if n.endswith("W_parameter"):       # a cancelling sum ~1e-4 of the largest gradient: fp32 atomics reorder it from run to run
+        worst_wp = max(worst_wp, err / den)
+    elif err / den > worst:
         worst, worst_name = err / den, n
-t = torch.tensor([check, worst], device=dev, dtype=torch.float64)
+t = torch.tensor([check, worst, worst_wp], device=dev, dtype=torch.float64)
 dist.all_reduce(t, op=dist.ReduceOp.MAX)
-res = {"world": world, "max_rel_err": float(t[0]), "vs_eager_per_shard_mean": float(t[1]), "worst_tensor": worst_name,
+res = {"world": world, "max_rel_err": float(t[0]), "vs_eager_per_shard_mean": float(t[1]), "vs_eager_W_parameter": float(t[2]), "worst_tensor": worst_name,
        "loose_tensors": len(step.bucket.loose), "split": bool(step.split), "precision": args.precision}
 if rank == 0:
     print(json.dumps(res))

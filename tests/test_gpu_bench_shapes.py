@@ -260,4 +260,5 @@ def test_two_rank_gradients_equal_mean_of_per_shard_gradients(pb, tmp_path):
     res = json.load(open(out))
     assert res["max_rel_err"] <= 1e-5, res
     assert res["vs_eager_per_shard_mean"] <= 1e-4, res
+    assert res["vs_eager_W_parameter"] <= 5e-2, res            # association-order sensitive (fp32 tests: 2e-3 + floor on one GPU)
     assert res["loose_tensors"] == 0, res

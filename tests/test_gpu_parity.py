@@ -432,12 +432,14 @@ def test_graphed_step_and_two_stage_backward_match_eager(pb, wide_ref):
             assert step.bucket is not None and step.bucket.loose == [], step.bucket.loose
             for n, p in model.named_parameters():
                 assert p.grad.data_ptr() == step.bucket.view(n).data_ptr(), n
-            assert step.ddp_check(X, Y, W) == 0.0
+
         loss_g = step(X, Y, W)
         torch.cuda.synchronize()
         assert abs(float(loss_g) - float(loss_e)) <= 1e-6 * abs(float(loss_e))
         for n, p in model.named_parameters():
-            assert rel_fro(p.grad, ref[n]) < 2e-3 or float(ref[n].abs().max()) < 1e-6, (kwargs, n)
+            assert rel_fro(p.grad, ref[n]) < 2e-3 or float(ref[n].abs().max()) < 1e-6, (kwargs, n, rel_fro(p.grad, ref[n]))
+        if kwargs:
+            assert step.ddp_check(X, Y, W) == 0.0          # one rank: the exchange is the identity
         # host batches with one step of look-ahead: the staged copy of the next batch must be the one the step consumes
         hostA = [t.cpu().pin_memory() for t in batch]
         hostB = [t.cpu().pin_memory() for t in batch]
