@@ -333,6 +333,19 @@ int pb_corrupt_pad(const uint8_t* seq_bytes, const int64_t* seq_off, const int64
  * No counterpart in the reference (torch picks cuDNN / cuBLAS algorithms internally, modules.py:124-160). */
 int pb_tc_path(const char* op, int B, int L, int C, int G, int ksize, int dil);
 
+/* ---- f-3: the random draws of the data path made on the GPU (data_processing.py:78-83,100-105,125-142) ----------
+ * Philox4x32-10 keyed by `seed`; `counter` distinguishes batches.  Fills the draw arguments of pb_corrupt_pad: crop_start
+ * uniform in [0, len+2-L) where the sample is longer than L, tok_mask ~ Bernoulli(p_tok = 0.05), tok_rand uniform in
+ * [3, 26), coin ~ U[0,1), keep ~ Bernoulli(p_keep = 0.75), add ~ Bernoulli(p_add = 1e-4).  Same distributions as the
+ * reference's torch CPU draws, a different stream: statistically equivalent, not bit-identical. */
+int pb_draw_batch(unsigned long long seed, unsigned long long counter, const int64_t* seq_off, const int64_t* draw_off,
+                  int64_t* crop_start, uint8_t* tok_mask, uint8_t* tok_rand, float* coin, uint8_t* keep, uint8_t* add, int B,
+                  int L, int A, float p_tok, float p_keep, float p_add, void* stream);
+
+/* probe builds only (PB_NVCC_DEFINES=-DPB_GLOBAL_PROBE / -DPB_CONV2_PROBE): device buffer that receives phase
+ * timestamps / cycle counters; NULL switches it off.  Process-global; the shipped library never writes to it. */
+void pb_debug_buffer(void* device_buffer);
+
 /* ---- sizing ------------------------------------------------------------------------------------ */
 size_t pb_workspace_bytes(const char* op, int M, int N, int K);
 

@@ -13,8 +13,8 @@ data-parallel gradient reducer.  All arithmetic runs in libpb_b200.so (C ABI: in
 from . import _lib, ops
 from ._lib import PBError, launch_count
 from .modules import GlobalAttention, GlobalAttentionHead, ProteinBERT, ProteinBERTBlock
-from .training import FusedAdam, GradAllReducer, GraphedPretrainStep, pretraining_loss, pretraining_step
+from .training import FusedAdam, GradAllReducer, GraphedPretrainStep, WarmupThenPlateau, pretrain, pretraining_loss, pretraining_step
 from . import data_processing
 
 __all__ = ["ProteinBERT", "ProteinBERTBlock", "GlobalAttention", "GlobalAttentionHead", "pretraining_loss",
-           "pretraining_step", "GraphedPretrainStep", "GradAllReducer", "FusedAdam", "data_processing", "ops", "PBError", "launch_count"]
+           "pretraining_step", "pretrain", "WarmupThenPlateau", "GraphedPretrainStep", "GradAllReducer", "FusedAdam", "data_processing", "ops", "PBError", "launch_count"]

@@ -68,6 +68,8 @@ PROTOTYPES = {
     "pb_pretrain_loss": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p],
     "pb_sigmoid_bwd": [_p, _p, _p, _p, _ll, _p],
     "pb_corrupt_pad": [_p] * 16 + [_i, _i, _i, _p],
+    "pb_draw_batch": [C.c_ulonglong, C.c_ulonglong] + [_p] * 8 + [_i, _i, _i, _f, _f, _f, _p],
+    "pb_debug_buffer": [_p],
     "pb_workspace_bytes": [C.c_char_p, _i, _i, _i],
     "pb_tc_path": [C.c_char_p, _i, _i, _i, _i, _i, _i],
 }

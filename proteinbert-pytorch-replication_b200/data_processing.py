@@ -7,7 +7,8 @@ packs the raw bytes; all integer work then runs in one CUDA kernel (``pb_corrupt
 with the reference given those draws.
 
     ds     = UniRefGO_PretrainingDataset(df, seq_max_length=512)       # same constructor as the reference
-    loader = DataLoader(ds, batch_size=64, collate_fn=ds.collate)      # the collate runs the kernel
+    loader = DataLoader(ds, batch_size=64)                             # drop-in: one kernel launch per sample
+    loader = DataLoader(ds.raw(), batch_size=64, collate_fn=ds.collate)   # fast: one kernel launch per batch
     for X, Y, W in loader: ...                                         # dicts of device tensors
 
 There is no torchtext dependency (the reference's is un-vendored, unpinned and end-of-life).
@@ -129,28 +130,97 @@ def corrupt_pad(packed, device="cuda"):
             {"local": w_local, "global": w_global})
 
 
-class UniRefGO_PretrainingDataset(torch.utils.data.Dataset):
-    """Same constructor and length as the reference dataset (data_processing.py:146-183).  ``__getitem__``
-    returns the raw sample plus its random draws; ``collate`` turns a list of them into the (X, Y, W) batch on
-    the GPU.  Iterating with the same seed visits the RNG exactly as the reference does."""
+def corrupt_pad_device_draws(seqs, anns, max_length: int, seed: int, counter: int, device="cuda",
+                             p: float = .05, positive_p: float = 0.25, negative_p: float = 0.0001):
+    """corrupt_pad with the random draws made on the GPU (``pb_draw_batch``, Philox keyed by ``seed``, ``counter`` = batch
+    number) instead of the torch CPU generator: the host only packs the residue bytes and the annotation rows."""
+    B, A = len(seqs), len(anns[0])
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("device draws run on a CUDA device only")
+    raw = [s.encode("latin-1", errors="replace") for s in seqs]
+    n_draw = [min(len(r) + 2, max_length) for r in raw]
+    seq_off = np.zeros(B + 1, dtype=np.int64); seq_off[1:] = np.cumsum([len(r) for r in raw])
+    draw_off = np.zeros(B + 1, dtype=np.int64); draw_off[1:] = np.cumsum(n_draw)
+    seq_bytes = np.frombuffer(b"".join(raw) or b"\0", dtype=np.uint8).copy()
+    ann = np.asarray(anns, dtype=np.int64)
+    if ann.min(initial=0) < 0 or ann.max(initial=0) > 255:
+        raise ValueError("annotation values must fit in a byte (the reference uses 0/1 masks)")
+    h = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().to(dev, non_blocking=True)
+    d = {"seq_bytes": h(seq_bytes), "seq_off": h(seq_off), "draw_off": h(draw_off), "ann": h(ann.astype(np.uint8)),
+         "crop_start": torch.empty(B, dtype=torch.int64, device=dev),
+         "tok_mask": torch.empty(max(int(draw_off[-1]), 1), dtype=torch.uint8, device=dev),
+         "tok_rand": torch.empty(max(int(draw_off[-1]), 1), dtype=torch.uint8, device=dev),
+         "coin": torch.empty(B, dtype=torch.float32, device=dev),
+         "keep": torch.empty((B, A), dtype=torch.uint8, device=dev), "add": torch.empty((B, A), dtype=torch.uint8, device=dev),
+         "B": B, "L": max_length, "A": A}
+    st = torch.cuda.current_stream(dev).cuda_stream
+    check(lib().pb_draw_batch(int(seed) & (2 ** 64 - 1), int(counter) & (2 ** 64 - 1), d["seq_off"].data_ptr(), d["draw_off"].data_ptr(),
+                              d["crop_start"].data_ptr(), d["tok_mask"].data_ptr(), d["tok_rand"].data_ptr(), d["coin"].data_ptr(),
+                              d["keep"].data_ptr(), d["add"].data_ptr(), B, max_length, A, float(p), float(1.0 - positive_p),
+                              float(negative_p), st), "pb_draw_batch")
+    return corrupt_pad(d, dev), d
 
-    def __init__(self, df, seq_max_length=128, device="cuda"):
+
+class UniRefGO_PretrainingDataset(torch.utils.data.Dataset):
+    """Same constructor, length and per-sample output as the reference dataset (data_processing.py:146-183): ``ds[i]`` is the
+    ``(X, Y, W)`` triple of dictionaries -- ``local`` int64 [L] / ``global`` float32 [A], weights float64 -- so the reference's
+    ``DataLoader(ds, shuffle=True, num_workers=0, batch_size=32)`` (dummy_tests.py:102-108) works unchanged; the tensors are on
+    the GPU already (each sample is one ``pb_corrupt_pad`` launch of batch 1, default_collate stacks them there).
+    Iterating with the same seed visits the torch CPU RNG exactly as the reference does, so the same seed gives the same batch.
+
+    Faster: ``DataLoader(ds.raw(), batch_size=32, collate_fn=ds.collate)`` hands the raw samples and their draws to ONE kernel
+    launch per batch.  ``draws="device"`` makes ``collate`` take the random draws from the Philox generator on the GPU
+    (``pb_draw_batch``) instead of the torch CPU generator: the same distributions, not the same stream -- for training
+    runs where the host draws (two 8943-element multinomials per sample) would be the bottleneck."""
+
+    def __init__(self, df, seq_max_length=128, device="cuda", draws="host", seed=0):
+        if draws not in ("host", "device"):
+            raise ValueError("draws must be 'host' (the reference's torch CPU RNG stream) or 'device' (Philox on the GPU)")
         self.df = df
         self.vocab = create_amino_acid_vocab()
         self.seq_max_length = seq_max_length
         self.device = device
+        self.draws = draws
+        self.seed = int(seed)
+        self._batches = 0
 
-    def __getitem__(self, index):
+    def raw_item(self, index):
         seq = self.df.iloc[index, 0]
         ann = self.df.iloc[index, 1]
-        return seq, ann, draw_sample(len(seq), len(ann), self.seq_max_length)
+        return seq, ann, (draw_sample(len(seq), len(ann), self.seq_max_length) if self.draws == "host" else None)
+
+    def __getitem__(self, index):
+        seq, ann, d = self.raw_item(index)
+        if d is None:
+            d = draw_sample(len(seq), len(ann), self.seq_max_length)
+        X, Y, W = corrupt_pad(pack_batch([seq], [ann], [d], self.seq_max_length), self.device)
+        return tuple({k: v[0] for k, v in t.items()} for t in (X, Y, W))
 
     def __len__(self):
         return len(self.df.index)
 
+    def raw(self):
+        """A view of this dataset that yields raw samples (sequence, annotations, draws) for ``collate``."""
+        return _RawView(self)
+
     def collate(self, samples):
         seqs, anns, draws = zip(*samples)
+        if self.draws == "device":
+            self._batches += 1
+            return corrupt_pad_device_draws(seqs, anns, self.seq_max_length, self.seed, self._batches, self.device)[0]
         return corrupt_pad(pack_batch(seqs, anns, draws, self.seq_max_length), self.device)
+
+
+class _RawView(torch.utils.data.Dataset):
+    def __init__(self, ds):
+        self.ds = ds
+
+    def __getitem__(self, index):
+        return self.ds.raw_item(index)
+
+    def __len__(self):
+        return len(self.ds)
 
 
 def synthetic_batch(B: int, L: int, A: int, seed: int = 0, vocab_size: int = 26):

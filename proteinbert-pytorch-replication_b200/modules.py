@@ -118,6 +118,13 @@ class ProteinBERTBlock(nn.Module):
         self.global_linear_layer_2 = nn.Sequential(nn.Linear(global_dim, global_dim, device=device), nn.GELU())
         self.global_norm_2 = nn.LayerNorm(normalized_shape=global_dim, device=device)
 
+    def __getstate__(self):
+        """torch.save(model) (utils.py:341) pickles the module: the per-step staging caches are rebuilt on demand, not saved."""
+        st = dict(self.__dict__)
+        for k in ("_staged", "_stage_table", "_prestaged"):
+            st.pop(k, None)
+        return st
+
     def local_track(self, xl: torch.Tensor, g2l: torch.Tensor, arena=None):
         """modules.py:205-219 without the global side: xl [B,L,C], g2l [B,C] -> (h [B,L,C], pool [B,G] = sum_l gelu(h Wv_all))."""
         if xl.shape[1] != self.sequences_length:
@@ -214,6 +221,12 @@ class ProteinBERT(nn.Module):
         ])
         self.pretraining_local_output = nn.Sequential(nn.Linear(local_dim, vocab_size, device=device), nn.Softmax())
         self.pretraining_global_output = nn.Sequential(nn.Linear(global_dim, num_annotations, device=device), nn.Sigmoid())
+
+    def __getstate__(self):
+        st = dict(self.__dict__)
+        for k in ("_stage_table", "_boundary", "_boundary_at"):
+            st.pop(k, None)
+        return st
 
     def set_precision(self, precision: str):
         _dt(precision)

@@ -676,6 +676,137 @@ class FusedAdam(torch.optim.Adam):
         super().add_param_group(param_group)
 
 
+class WarmupThenPlateau:
+    """The learning-rate schedule utils.pretrain intends (utils.py:253-264): linear warm-up ``lr * step / warmup_duration`` for
+    ``warmup_duration`` steps (so the very first step runs at lr = 0, as there), then ``ReduceLROnPlateau(mode='min',
+    patience=...)`` on the training loss.  The reference builds it as ``SequentialLR([LambdaLR, ReduceLROnPlateau])``, which
+    torch >= 2.2 refuses (ReduceLROnPlateau is not an LRScheduler there) and which never passed the loss to
+    the plateau scheduler; this object drives the same two torch schedulers directly.  ``state_dict()`` carries the three
+    entries the reference checkpoint stores."""
+
+    def __init__(self, optimizer, warmup_duration: int, patience: int):
+        from torch.optim.lr_scheduler import LambdaLR, ReduceLROnPlateau
+        self.warmup_duration = max(int(warmup_duration), 1)
+        self.plateau = ReduceLROnPlateau(optimizer=optimizer, mode="min", patience=patience)
+        self.warmup = LambdaLR(optimizer, lr_lambda=lambda step: float(step / self.warmup_duration))
+        self.optimizer = optimizer
+        self.steps = 0
+
+    def get_last_lr(self):
+        return [g["lr"] for g in self.optimizer.param_groups]
+
+    def step(self, loss=None):
+        self.steps += 1
+        if self.steps < self.warmup_duration:
+            self.warmup.step()
+        elif self.steps == self.warmup_duration:
+            self.warmup.step()                              # reaches the base learning rate
+        elif loss is not None:
+            self.plateau.step(loss)
+
+    def state_dict(self):
+        wsd = {k: v for k, v in self.warmup.state_dict().items() if k != "lr_lambdas"}      # the lambda is rebuilt, not pickled
+        return {"scheduler_state_dict": self.plateau.state_dict(), "warmup_scheduler_state_dict": wsd,
+                "full_scheduler_state_dict": {"steps": self.steps, "warmup_duration": self.warmup_duration}}
+
+    def load_state_dict(self, sd):
+        self.plateau.load_state_dict(sd["scheduler_state_dict"])
+        w = dict(sd["warmup_scheduler_state_dict"])
+        w.pop("lr_lambdas", None)
+        self.warmup.__dict__.update(w)
+        self.steps = int(sd["full_scheduler_state_dict"]["steps"])
+
+
+def pretrain(model, train_dataloader, optimizer, local_loss_fn=None, global_loss_fn=None, max_batch_iterations: int = 1000,
+             save_path: str = ".", nb_iterations_checkpoint: int = 1000, optim_scheduler_patience: int = 25,
+             warmup_duration: int = 10000, loaded_checkpoint=None, device=None, use_graph: bool = True, log_every: int = 1):
+    """``utils.pretrain`` (utils.py:220-345) on the kernels of this package: same arguments, same results dictionary, same
+    checkpoint dictionary (``current_batch_iteration``, ``model_state_dict``, ``optimizer_state_dict``, three scheduler
+    entries, ``loss``) and the same whole-model pickle at the end.  Differences, all in the shell and none in the arithmetic:
+
+    * the scheduler is WarmupThenPlateau (the reference's SequentialLR construction does not start on torch >= 2.2);
+    * forward + loss + backward run as GraphedPretrainStep once the batch shape repeats (``use_graph``); batches of another
+      shape (the last one of an epoch) take the eager step.  ``local_loss_fn`` / ``global_loss_fn`` are accepted for
+      signature compatibility; the loss is the fused kernel's, equal to ``CrossEntropyLoss(reduction='none')`` /
+      ``BCELoss(reduction='none')`` in the reference expression (utils.py:293-294);
+    * the loss is not read with ``.item()`` every iteration (a device synchronisation per step, utils.py:295): it is copied
+      to pinned host memory asynchronously and logged / fed to the plateau scheduler one iteration late."""
+    import logging
+    from datetime import datetime
+    from pathlib import Path
+    from timeit import default_timer as time
+
+    dev = torch.device(device) if device is not None else next(model.parameters()).device
+    results = {"train_loss": []}
+    sched = WarmupThenPlateau(optimizer, warmup_duration, optim_scheduler_patience)
+    if loaded_checkpoint is not None:
+        logging.info("Loading checkpoint...")
+        current = loaded_checkpoint["current_batch_iteration"]
+        model.load_state_dict(loaded_checkpoint["model_state_dict"])
+        optimizer.load_state_dict(loaded_checkpoint["optimizer_state_dict"])
+        sched.load_state_dict(loaded_checkpoint)
+        logging.info("Checkpoint loaded!")
+    else:
+        current = 0
+    model.train()
+    graphs = {}                       # batch shape -> GraphedPretrainStep
+    pending = []                      # (iteration, pinned host scalar, event, start time)
+    last_loss = None
+
+    def drain(block: bool):
+        nonlocal last_loss
+        while pending and (block or pending[0][2].query()):
+            it, host, ev, t0 = pending.pop(0)
+            ev.synchronize()
+            last_loss = float(host[0])
+            results["train_loss"].append(last_loss)
+            if log_every and it % log_every == 0:
+                logging.info(f"Current batch iteration: {it} | Train loss: {last_loss:.4f} | "
+                             f"Learning rate: {sched.get_last_lr()[0]} | Batch Iteration time: {time() - t0:.4f} seconds")
+
+    while current < max_batch_iterations:
+        n_before = current
+        for X, Y, W in train_dataloader:
+            t0 = time()
+            X = {k: v.to(dev, non_blocking=True) for k, v in X.items()}
+            Y = {k: v.to(dev, non_blocking=True) for k, v in Y.items()}
+            W = {k: v.to(dev, non_blocking=True) for k, v in W.items()}
+            key = (tuple(X["local"].shape), tuple(X["global"].shape))
+            if use_graph and key in graphs:
+                loss = graphs[key](X, Y, W)
+            else:
+                loss = pretraining_step(model, X, Y, W)
+                if use_graph and key not in graphs and graphs.get("seen") == key:
+                    graphs[key] = GraphedPretrainStep(model, X, Y, W, warmup=1)      # the shape repeated: capture it
+                graphs["seen"] = key
+            optimizer.step()
+            host = torch.empty(1, dtype=torch.float64).pin_memory()
+            host.copy_(loss.detach().reshape(1), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            current += 1
+            pending.append((current, host, ev, t0))
+            drain(block=len(pending) > 2)
+            sched.step(last_loss)
+            if current >= max_batch_iterations:
+                break
+            if current % nb_iterations_checkpoint == 0:
+                drain(block=True)
+                logging.info(f"Saving checkpoint to {save_path}...")
+                ck = {"current_batch_iteration": current, "model_state_dict": model.state_dict(),
+                      "optimizer_state_dict": optimizer.state_dict(), "loss": results["train_loss"][-1]}
+                ck.update(sched.state_dict())
+                torch.save(ck, Path(save_path) / f"proteinbert_pretraining_checkpoint_{current}.pt")
+        if current == n_before:
+            raise RuntimeError("pretrain: the data loader yielded no batches")
+    drain(block=True)
+    graphs.clear()
+    stamp = datetime.now().strftime('%m-%d-%Y_%H-%M-%S')
+    logging.info(f"Save whole model to {save_path}...")
+    torch.save(model, Path(save_path) / f"proteinbert_pretrained_model_{stamp}.pt")
+    return results
+
+
 def _lib_error(msg):
     from ._lib import PBError
     return PBError(msg)

@@ -102,3 +102,50 @@ def test_vocab_matches_reference(pb):
     assert len(v) == 26 and v["<pad>"] == 0 and v["out of vocab"] == v["<unk>"] == 3
     lut = data_oracle.char_lut()
     assert all(lut[ord(c)] == v[c] for c in data_oracle.ALL_AMINO_ACIDS)
+
+
+def test_reference_state_dict_loads_strictly_and_the_module_pickles(tmp_path):
+    """utils.py:270 (load_state_dict of a reference checkpoint) and :341 (torch.save(model)): the golden file carries the REAL
+    reference's state_dict (tests/golden/make_golden.py ran the reference); it must load with strict=True, and the module
+    must survive a pickle round trip with the same tensors (no GPU needed: the modules are parameter containers)."""
+    import torch
+    import proteinbert_b200 as pb
+    from helpers import load_model_golden
+    gold = load_model_golden()
+    cfg = {k: int(v) for k, v in gold["cfg"].items()}
+    model = pb.ProteinBERT(device="cpu", **cfg)
+    sd = {k: torch.from_numpy(v) for k, v in gold["w"].items() if k in model.state_dict()}
+    assert len(sd) == len(model.state_dict())
+    missing, unexpected = model.load_state_dict(sd, strict=True)
+    assert not missing and not unexpected
+    path = tmp_path / "model.pt"
+    torch.save(model, path)
+    back = torch.load(path, weights_only=False)
+    assert list(back.state_dict()) == list(model.state_dict())
+    for k, v in model.state_dict().items():
+        assert torch.equal(back.state_dict()[k], v), k
+    heads_a, heads_b = model.head_tensors(), back.head_tensors()       # the unregistered head tensors travel with the pickle too
+    assert all(torch.equal(heads_a[k], heads_b[k]) for k in heads_a)
+
+
+def test_warmup_then_plateau_follows_the_reference_schedule():
+    """utils.py:253-264: lr = base * step / warmup for `warmup` steps (0 at the very first step), then ReduceLROnPlateau."""
+    import torch
+    import proteinbert_b200 as pb
+    p = torch.nn.Parameter(torch.zeros(3))
+    opt = torch.optim.SGD([p], lr=1.0)
+    sch = pb.WarmupThenPlateau(opt, warmup_duration=4, patience=2)
+    lrs = [sch.get_last_lr()[0]]
+    for i in range(4):
+        sch.step(1.0)
+        lrs.append(sch.get_last_lr()[0])
+    assert lrs == [0.0, 0.25, 0.5, 0.75, 1.0]
+    for _ in range(4):                       # a flat loss: patience 2 -> the plateau scheduler cuts the rate by 10
+        sch.step(1.0)
+    assert abs(sch.get_last_lr()[0] - 0.1) < 1e-12
+    sd = sch.state_dict()
+    assert set(sd) == {"scheduler_state_dict", "warmup_scheduler_state_dict", "full_scheduler_state_dict"}
+    opt2 = torch.optim.SGD([p], lr=1.0)
+    sch2 = pb.WarmupThenPlateau(opt2, warmup_duration=4, patience=2)
+    sch2.load_state_dict(sd)
+    assert sch2.steps == sch.steps
