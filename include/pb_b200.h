@@ -285,6 +285,23 @@ int pb_attn_pool_bwd(const void* h_act, const void* wvT_wt, const void* wv_wt, c
                      void* dzv_act, void* dh_out_act, float* dWvT, int head_dv, int B, int L, int C, int G, int dt, void* ws,
                      size_t ws_bytes, void* stream);
 
+/* ---- a11/a12, op-faithful: GlobalAttention as the reference executes it, one fused launch per block (csrc/ops_attention.cu)
+ * per head: q = tanh(g Wq) (the K query rows are identical, modules.py:51-53), kt = tanh(h Wk), s = q.kt^T / sqrt(K),
+ * P = softmax(s) over `axis` (0: the repeated-query axis, the reference's nn.Softmax(dim=1), which makes every weight 1/K;
+ * 1: the sequence positions -- the `softmax_axis="sequence"` mode), v = gelu(h Wv), out = P v;
+ * att[b, head*Dv + d] = sum(W_parameter) * out[d] (:87-92).  Wq [H,G,K], Wk [H,C,K], Wv [H,C,Dv]: the heads' matrices stacked.
+ * Scores, probabilities and values stay on chip; q_out [B,H,K], p_out [B,H,L], pool_out [B,G] are kept for backward.
+ * Backward ACCUMULATES into dh [B,L,C] float, dg [B,G], dWq, dWk, dWv (zero on entry), writes dWp [K]; scratch = one float,
+ * zero on entry.  fp32 SIMT arithmetic: this is the checker of the closed form (pb_attn_pool_*) and the only
+ * implementation of axis 1. */
+size_t pb_attention_smem(int L, int C, int K, int Dv, int backward);
+int pb_attention_fwd(const void* h_act, const float* g, const float* Wq, const float* Wk, const float* Wv, const float* Wp, float* att,
+                     float* q_out, float* p_out, float* pool_out, int B, int L, int C, int G, int K, int H, int axis, int dt,
+                     void* stream);
+int pb_attention_bwd(const void* h_act, const float* g, const float* Wq, const float* Wk, const float* Wv, const float* Wp,
+                     const float* datt, const float* q, const float* p, const float* pool, float* dh, float* dg, float* dWq, float* dWk,
+                     float* dWv, float* dWp, float* scratch, int B, int L, int C, int G, int K, int H, int axis, int dt, void* stream);
+
 /* ---- a15: token head, softmax over the BATCH axis (modules.py:277-284; nn.Softmax() on 3-D) ----- */
 int pb_token_head_fwd(const void* h_act, const float* Wo, const float* bo, float* p_local, int B, int L, int C,
                       int V, int dt, void* stream);

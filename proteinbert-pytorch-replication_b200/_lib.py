@@ -60,6 +60,9 @@ PROTOTYPES = {
     "pb_local_linear_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p],
     "pb_attn_pool_fwd": [_p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_attn_pool_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p, _sz, _p],
+    "pb_attention_smem": [_i, _i, _i, _i, _i],
+    "pb_attention_fwd": [_p] * 10 + [_i] * 8 + [_p],
+    "pb_attention_bwd": [_p] * 17 + [_i] * 8 + [_p],
     "pb_token_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "pb_token_head_tc_ok": [_i, _i, _i, _i],
@@ -73,7 +76,8 @@ PROTOTYPES = {
     "pb_workspace_bytes": [C.c_char_p, _i, _i, _i],
     "pb_tc_path": [C.c_char_p, _i, _i, _i, _i, _i, _i],
 }
-_RESTYPES = {"pb_last_error": C.c_char_p, "pb_launch_count": _ll, "pb_workspace_bytes": _sz, "pb_linear_tc_workspace": _sz}
+_RESTYPES = {"pb_last_error": C.c_char_p, "pb_launch_count": _ll, "pb_workspace_bytes": _sz, "pb_linear_tc_workspace": _sz, "pb_attention_smem": _sz,
+             "pb_debug_buffer": None}
 
 _lib = None
 

@@ -12,9 +12,16 @@ Reference behaviours that are reproduced on purpose:
     ``(sum(W_parameter)/key_dim) * sum_l gelu(x_l Wv)`` (modules.py:34,51-60,92);
   * the token head's ``nn.Softmax()`` acts on the batch axis (modules.py:283).
 
-One extra, optional constructor keyword: ``precision`` = "fp32" (default; fp32 storage and fp32 arithmetic,
-matches the reference to ~1e-5) or "bf16" (bf16 activations, tcgen05 tensor-core contractions with fp32
-accumulation, fp32/fp64 statistics).
+Extra, optional constructor keywords (all default to the reference's behaviour):
+  ``precision``     "fp32" (default; fp32 storage and fp32 arithmetic, matches the reference to ~1e-5) or "bf16" (bf16
+                    activations, tcgen05 tensor-core contractions with fp32 accumulation, fp32/fp64 statistics);
+  ``softmax_axis``  "reference" (default): the attention layer in the closed form the reference's softmax axis implies,
+                    on the tensor cores; "reference_as_executed": the same function through the op-faithful fused kernel
+                    (tanh(g Wq), tanh(h Wk), scores, softmax over the repeated-query axis, gelu(h Wv), P.V) -- a check of
+                    the closed form; "sequence": that kernel with the softmax over the sequence positions, the paper's
+                    semantics (SURVEY.md D1 / 8 f-4) -- the only mode in which Wq and Wk influence the output;
+  ``register_heads``  False (default, as the reference: heads in a plain list, their tensors unregistered) or True (heads in
+                    an nn.ModuleList: they appear in parameters() / state_dict() and are trained).
 """
 from __future__ import annotations
 
@@ -30,6 +37,15 @@ _DEFAULT_DEVICE = ('cuda' if torch.cuda.is_available() else 'cpu')
 _DEFAULT_PRECISION = os.environ.get("PB_B200_PRECISION", "fp32")
 
 
+def _axis(softmax_axis: str) -> int:
+    """kernel code of the softmax axis: 0 = the reference's repeated-query axis, 1 = sequence positions"""
+    if softmax_axis in ("reference", "reference_as_executed"):
+        return 0
+    if softmax_axis == "sequence":
+        return 1
+    raise ValueError(f"softmax_axis must be 'reference', 'reference_as_executed' or 'sequence', got {softmax_axis!r}")
+
+
 def _dt(precision: str) -> int:
     if precision == "fp32":
         return F32
@@ -42,8 +58,10 @@ class GlobalAttentionHead(nn.Module):
     """reference: modules.py:21-60."""
 
     def __init__(self, local_dim: int, global_dim: int, value_dim: int, key_dim: int,
-                 device: torch.device = _DEFAULT_DEVICE):
+                 device: torch.device = _DEFAULT_DEVICE, softmax_axis: str = "reference"):
         super().__init__()
+        _axis(softmax_axis)
+        self.softmax_axis = softmax_axis
         self.key_dim = key_dim
         self.global_dim = global_dim
         self.gelu = nn.GELU()
@@ -57,30 +75,46 @@ class GlobalAttentionHead(nn.Module):
         """{"local": [B,L,C], "global": [B,G]} -> [B, key_dim, value_dim].  Every one of the key_dim rows is
         (1/key_dim) * sum_l gelu(x_l Wv): the K query rows are identical copies of the global vector, and the
         softmax runs over that axis (modules.py:51-60), so Wq / Wk cancel out of the result exactly."""
-        pool = ops.AttnPoolFn.apply(x["local"], self.Wv_parameter.t())          # [B, Dv]
-        return (pool / self.key_dim).unsqueeze(1).expand(-1, self.key_dim, -1)
+        if self.softmax_axis == "reference":
+            pool = ops.AttnPoolFn.apply(x["local"], self.Wv_parameter.t())          # [B, Dv]
+            return (pool / self.key_dim).unsqueeze(1).expand(-1, self.key_dim, -1)
+        # op-faithful kernel, one head; a unit mix (sum = 1) leaves the head's own [K, Dv] output, all rows equal
+        mix = torch.full((self.key_dim,), 1.0 / self.key_dim, device=self.Wv_parameter.device)
+        out = ops.AttentionFn.apply(x["local"], x["global"], self.Wq_parameter.unsqueeze(0), self.Wk_parameter.unsqueeze(0),
+                                    self.Wv_parameter.unsqueeze(0), mix, _axis(self.softmax_axis))
+        return out.unsqueeze(1).expand(-1, self.key_dim, -1)
 
 
 class GlobalAttention(nn.Module):
     """reference: modules.py:63-92."""
 
     def __init__(self, num_heads: int, local_dim: int, global_dim: int, value_dim: int, key_dim: int,
-                 device: torch.device = _DEFAULT_DEVICE):
+                 device: torch.device = _DEFAULT_DEVICE, softmax_axis: str = "reference", register_heads: bool = False):
         super().__init__()
-        # a plain list, exactly like the reference: the head tensors are not registered parameters
-        self.global_attention_heads = [
-            GlobalAttentionHead(local_dim=local_dim, global_dim=global_dim, value_dim=value_dim, key_dim=key_dim,
-                                device=device) for _ in range(num_heads)
-        ]
+        _axis(softmax_axis)
+        self.softmax_axis = softmax_axis
+        # a plain list, exactly like the reference: the head tensors are not registered parameters (register_heads=True
+        # is the opt-in fix: an nn.ModuleList)
+        heads = [GlobalAttentionHead(local_dim=local_dim, global_dim=global_dim, value_dim=value_dim, key_dim=key_dim,
+                                     device=device, softmax_axis=softmax_axis) for _ in range(num_heads)]
+        self.global_attention_heads = nn.ModuleList(heads) if register_heads else heads
         self.W_parameter = nn.Parameter(data=torch.randn(key_dim, device=device), requires_grad=True)
 
     def wv_all_t(self) -> torch.Tensor:
         """cat_heads(Wv)^T, [G, C] (autograd routes the gradient back to each head's Wv_parameter)."""
         return torch.cat([h.Wv_parameter for h in self.global_attention_heads], dim=1).t()
 
+    def stacked(self):
+        """(Wq [H,G,K], Wk [H,C,K], Wv [H,C,Dv]): the heads' matrices stacked for the fused kernel (gradients flow back to each head)."""
+        hs = self.global_attention_heads
+        return (torch.stack([h.Wq_parameter for h in hs]), torch.stack([h.Wk_parameter for h in hs]),
+                torch.stack([h.Wv_parameter for h in hs]))
+
     def forward(self, x):
-        pool = ops.AttnPoolFn.apply(x["local"], self.wv_all_t())
-        return pool * (self.W_parameter.sum() / self.W_parameter.numel())
+        if self.softmax_axis == "reference":
+            pool = ops.AttnPoolFn.apply(x["local"], self.wv_all_t())
+            return pool * (self.W_parameter.sum() / self.W_parameter.numel())
+        return ops.AttentionFn.apply(x["local"], x["global"], *self.stacked(), self.W_parameter, _axis(self.softmax_axis))
 
 
 class ProteinBERTBlock(nn.Module):
@@ -88,8 +122,10 @@ class ProteinBERTBlock(nn.Module):
 
     def __init__(self, sequences_length, local_dim: int, global_dim: int, num_heads: int, key_dim: int,
                  conv_kernel_size: int = 9, wide_conv_dilation: int = 5, device: torch.device = _DEFAULT_DEVICE,
-                 precision: str = _DEFAULT_PRECISION):
+                 precision: str = _DEFAULT_PRECISION, softmax_axis: str = "reference", register_heads: bool = False):
         super().__init__()
+        _axis(softmax_axis)
+        self.softmax_axis = softmax_axis
         assert global_dim % num_heads == 0, \
             f"Global_dim must be divisible by num_heads. Global_dim: {global_dim}. Num_heads: {num_heads}"
         self.sequences_length = sequences_length
@@ -101,7 +137,8 @@ class ProteinBERTBlock(nn.Module):
         self.fuse_global = os.environ.get("PB_B200_FUSE_GLOBAL", "1") == "1"   # 4-launch global track (ops_global_fused.cu)
 
         self.global_attention_layer = GlobalAttention(num_heads=num_heads, local_dim=local_dim, global_dim=global_dim,
-                                                      value_dim=int(global_dim / num_heads), key_dim=key_dim, device=device)
+                                                      value_dim=int(global_dim / num_heads), key_dim=key_dim, device=device,
+                                                      softmax_axis=softmax_axis, register_heads=register_heads)
         self.local_narrow_conv_layer = nn.Sequential(
             nn.Conv1d(local_dim, local_dim, kernel_size=conv_kernel_size, stride=1, dilation=1, padding="same", device=device),
             nn.GELU())
@@ -177,18 +214,25 @@ class ProteinBERTBlock(nn.Module):
             g2l, gh = ops.GlobalPreFn.apply(g, g2l_lin.weight, g2l_lin.bias, gl1.weight, gl1.bias, link)   # :208, :221
         else:
             g2l = ops.linear_act(g, g2l_lin.weight, g2l_lin.bias, ACT_GELU)                    # modules.py:208
+        closed = self.softmax_axis == "reference"
         h, pool = ops.LocalTrackFn.apply(                                                      # :205-219
             xl, g2l, nconv.weight, nconv.bias, wconv.weight, wconv.bias,
             self.local_norm_1.weight, self.local_norm_1.bias, lin.weight, lin.bias,
             self.local_norm_2.weight, self.local_norm_2.bias, staged,
             self.conv_kernel_size, self.wide_conv_dilation, self.head_grads, arena,
-            *[hd.Wv_parameter for hd in att.global_attention_heads])
+            *([hd.Wv_parameter for hd in att.global_attention_heads] if closed else []))
+        w_mix = att.W_parameter
+        if not closed:
+            # the attention layer through the op-faithful fused kernel (softmax over the reference's axis or over the
+            # sequence): it returns sum(W_parameter) * P.V, so the kernels behind it get a unit mix (sum(w)/K = 1)
+            pool = att({"local": h, "global": g})                                              # :219
+            w_mix = torch.ones_like(att.W_parameter)
         if fused:       # LN(g + gh + att), Linear+GELU, LN in one launch                       # :223-229
-            g2 = ops.GlobalPostFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias,
+            g2 = ops.GlobalPostFn.apply(g, gh, pool, w_mix, self.global_norm_1.weight, self.global_norm_1.bias,
                                         gl2.weight, gl2.bias, self.global_norm_2.weight, self.global_norm_2.bias, link)
             return h, g2
         gh = ops.linear_act(g, gl1.weight, gl1.bias, ACT_GELU)                                  # :221
-        g1 = ops.ResLnRowsFn.apply(g, gh, pool, att.W_parameter, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224
+        g1 = ops.ResLnRowsFn.apply(g, gh, pool, w_mix, self.global_norm_1.weight, self.global_norm_1.bias)   # :223-224
         gh2 = ops.linear_act(g1, gl2.weight, gl2.bias, ACT_GELU)                                # :226
         g2 = ops.ResLnRowsFn.apply(g1, gh2, None, None, self.global_norm_2.weight, self.global_norm_2.bias)           # :228-229
         return h, g2
@@ -207,16 +251,20 @@ class ProteinBERT(nn.Module):
 
     def __init__(self, sequences_length: int, num_annotations: int, local_dim: int, global_dim: int, key_dim: int,
                  num_heads: int, num_blocks: int, conv_kernel_size: int = 9, wide_conv_dilation: int = 5,
-                 vocab_size: int = 26, device: torch.device = _DEFAULT_DEVICE, precision: str = _DEFAULT_PRECISION):
+                 vocab_size: int = 26, device: torch.device = _DEFAULT_DEVICE, precision: str = _DEFAULT_PRECISION,
+                 softmax_axis: str = "reference", register_heads: bool = False):
         super().__init__()
         _dt(precision)
+        _axis(softmax_axis)
         self.precision = precision
+        self.softmax_axis = softmax_axis
         self.local_embedding = nn.Embedding(num_embeddings=vocab_size, embedding_dim=local_dim, device=device)
         self.global_linear_layer = nn.Sequential(nn.Linear(num_annotations, global_dim, device=device), nn.GELU())
         self.proteinBERT_blocks = nn.Sequential(*[
             ProteinBERTBlock(sequences_length=sequences_length, global_dim=global_dim, local_dim=local_dim,
                              key_dim=key_dim, num_heads=num_heads, conv_kernel_size=conv_kernel_size,
-                             wide_conv_dilation=wide_conv_dilation, device=device, precision=precision)
+                             wide_conv_dilation=wide_conv_dilation, device=device, precision=precision,
+                             softmax_axis=softmax_axis, register_heads=register_heads)
             for _ in range(num_blocks)
         ])
         self.pretraining_local_output = nn.Sequential(nn.Linear(local_dim, vocab_size, device=device), nn.Softmax())
@@ -246,7 +294,7 @@ class ProteinBERT(nn.Module):
         """Whether forward runs the global track as one cluster launch per block boundary (ops.GTrackFn) at this batch size."""
         blocks = list(self.proteinBERT_blocks)
         G = self.global_linear_layer[0].weight.shape[0]
-        return (all(b.fuse_global for b in blocks) and os.environ.get("PB_B200_GTRACK", "1") == "1"
+        return (all(b.fuse_global and b.softmax_axis == "reference" for b in blocks) and os.environ.get("PB_B200_GTRACK", "1") == "1"
                 and ops.gtrack_ok(batch, G, blocks[0].local_dim))
 
     def head_tensors(self):

@@ -666,6 +666,7 @@ class LocalTrackFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, g2l, Wn, bn, Ww, bw, ln1w, ln1b, W2, b2, ln2w, ln2b, staged, ksize, dil, head_grads, arena, *head_wv):
+        with_pool = len(head_wv) > 0          # no head tensors: the caller evaluates the attention layer itself (ops.AttentionFn)
         _need_cuda(x, g2l, Wn)
         x = x.contiguous()
         dt = dt_of(x)
@@ -692,8 +693,10 @@ class LocalTrackFn(torch.autograd.Function):
         _call("pb_ln_joint_apply", _p(u1), _p(stats1), _p(ln1w), _p(ln1b), _p(h1), B, L, C, LN_EPS, dt, st)
         _call("pb_local_linear_fwd", _p(h1), _p(W2w), _p(b2), _p(z2), _p(u2), _p(stats2), B, L, C, dt, st)
         _call("pb_ln_joint_apply", _p(u2), _p(stats2), _p(ln2w), _p(ln2b), _p(h2), B, L, C, LN_EPS, dt, st)
-        pool = arena.take((B, G), torch.float32) if arena is not None else torch.zeros((B, G), dtype=torch.float32, device=dev)
-        _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
+        pool = None
+        if with_pool:
+            pool = arena.take((B, G), torch.float32) if arena is not None else torch.zeros((B, G), dtype=torch.float32, device=dev)
+            _call("pb_attn_pool_fwd", _p(h2), _p(wvTw), _p(pool), B, L, C, G, dt, st)
         ctx.save_for_backward(x, zn, zw, u1, stats1, h1, z2, u2, stats2, h2, ln1w, ln2w)
         # the zeroed accumulators of backward are reserved now, from the same per-step fill
         ctx.bwd_zero = arena.take((ZeroArena._acc_floats(B, L, C),), torch.float32) if arena is not None else None
@@ -715,7 +718,8 @@ class LocalTrackFn(torch.autograd.Function):
         if dh2 is None:
             dh2 = torch.zeros_like(x)
         dh2 = dh2.contiguous().to(adt)
-        dpool = torch.zeros((B, G), dtype=torch.float32, device=dev) if dpool is None else dpool.contiguous()
+        if n_heads > 0:
+            dpool = torch.zeros((B, G), dtype=torch.float32, device=dev) if dpool is None else dpool.contiguous()
 
         def f32(*shape):
             return torch.empty(shape, dtype=torch.float32, device=dev)
@@ -738,11 +742,6 @@ class LocalTrackFn(torch.autograd.Function):
         dg2l = arena[o + 3 * C:o + 3 * C + B * C].view(B, C)
         sums_all = arena[n_acc:].view(torch.float64).view(2, B, 2)          # two [B,2] double scratch areas
 
-        # attention pooling
-        dzv = torch.empty((B * L, G), dtype=adt, device=dev)
-        dh2t = torch.empty_like(x)
-        Dv = G // n_heads
-        dWv = f32(n_heads, C, Dv) if head_grads else None          # one contiguous [C, Dv] gradient per head
         side = _side_stream(dev) if WGRAD_STREAM else None
         main = torch.cuda.current_stream(dev)
 
@@ -756,13 +755,21 @@ class LocalTrackFn(torch.autograd.Function):
                     t.record_stream(side)
             _SIDE_PENDING.add(dev)
 
-        if side is None:
-            _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
+        # attention pooling (n_heads == 0: the caller evaluates the attention layer itself, ops.AttentionFn)
+        Dv = G // max(n_heads, 1)
+        dWv = f32(n_heads, C, Dv) if (head_grads and n_heads > 0) else None          # one contiguous [C, Dv] gradient per head
+        if n_heads == 0:
+            dh2t, dzv = dh2.clone(), None          # dh2t is reused as scratch below: never autograd's own tensor
         else:
-            _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), None, Dv, B, L, C, G, dt, None, 0, st)
-            if dWv is not None:
-                on_side(lambda: _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), None, None, _p(dzv), None, _p(dWv), Dv, B, L, C, G, dt,
-                                      *_wgrad_ws(dev), _st()), h2, dzv, dWv, wvTw, wvw)
+            dzv = torch.empty((B * L, G), dtype=adt, device=dev)
+            dh2t = torch.empty_like(x)
+            if side is None:
+                _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), _p(dWv), Dv, B, L, C, G, dt, *_wgrad_ws(dev), st)
+            else:
+                _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), _p(dpool), _p(dh2), _p(dzv), _p(dh2t), None, Dv, B, L, C, G, dt, None, 0, st)
+                if dWv is not None:
+                    on_side(lambda: _call("pb_attn_pool_bwd", _p(h2), _p(wvTw), _p(wvw), None, None, _p(dzv), None, _p(dWv), Dv, B, L, C, G, dt,
+                                          *_wgrad_ws(dev), _st()), h2, dzv, dWv, wvTw, wvw)
         del dzv
         fused = bool(L_.pb_ln_joint_bwd_gelu_ok(B, L, C))
         # LN2 (+ the linear layer's GELU gradient when the fused kernel takes the shape)
@@ -819,7 +826,7 @@ class LocalTrackFn(torch.autograd.Function):
                 on_side(wgrad, x, dzn, dzw, dWn, dWw)
             if not DEFER_WGRAD_JOIN:
                 join_side_streams()
-        if head_grads:
+        if head_grads and n_heads > 0:
             dheads = tuple(dWv[h] for h in range(n_heads))
         else:
             dheads = (None,) * n_heads
@@ -857,6 +864,41 @@ class AttnPoolFn(torch.autograd.Function):
         _call("pb_attn_pool_bwd", _p(h), _p(wvTw), _p(wvw), _p(dpool.contiguous()), _p(zero), _p(dzv), _p(dh), _p(dWvT), 0, B, L, C, G,
                                      dt, *_wgrad_ws(dev), _st())
         return dh, dWvT
+
+
+class AttentionFn(torch.autograd.Function):
+    """GlobalAttention as the reference executes it (modules.py:21-92), one fused launch (csrc/ops_attention.cu): tanh(g Wq),
+    tanh(h Wk), scores / sqrt(K), softmax over `axis` (0: the reference's repeated-query axis; 1: sequence positions),
+    gelu(h Wv), P.V and the W_parameter mix.  Wq [H,G,K], Wk [H,C,K], Wv [H,C,Dv] are the heads' matrices stacked."""
+
+    @staticmethod
+    def forward(ctx, h, g, Wq, Wk, Wv, Wp, axis):
+        _need_cuda(h, g, Wq)
+        h, g = h.contiguous(), g.contiguous().float()
+        Wq, Wk, Wv, Wp = Wq.contiguous().float(), Wk.contiguous().float(), Wv.contiguous().float(), Wp.contiguous().float()
+        dt = dt_of(h)
+        B, L, C = h.shape
+        H, G, K = Wq.shape
+        dev = h.device
+        f32 = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
+        att, q, p, pool = f32(B, G), f32(B, H, K), f32(B, H, L), f32(B, G)
+        _call("pb_attention_fwd", _p(h), _p(g), _p(Wq), _p(Wk), _p(Wv), _p(Wp), _p(att), _p(q), _p(p), _p(pool), B, L, C, G, K, H,
+              int(axis), dt, _st())
+        ctx.save_for_backward(h, g, Wq, Wk, Wv, Wp, q, p, pool)
+        ctx.cfg = (B, L, C, G, K, H, int(axis), dt)
+        return att
+
+    @staticmethod
+    def backward(ctx, datt):
+        h, g, Wq, Wk, Wv, Wp, q, p, pool = ctx.saved_tensors
+        B, L, C, G, K, H, axis, dt = ctx.cfg
+        dev = h.device
+        z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
+        dh, dg, dWq, dWk, dWv, scratch = z(B, L, C), z(B, G), z(*Wq.shape), z(*Wk.shape), z(*Wv.shape), z(1)
+        dWp = torch.empty_like(Wp)
+        _call("pb_attention_bwd", _p(h), _p(g), _p(Wq), _p(Wk), _p(Wv), _p(Wp), _p(datt.contiguous().float()), _p(q), _p(p), _p(pool),
+              _p(dh), _p(dg), _p(dWq), _p(dWk), _p(dWv), _p(dWp), _p(scratch), B, L, C, G, K, H, axis, dt, _st())
+        return dh.to(h.dtype), dg, dWq, dWk, dWv, dWp, None
 
 
 class TokenHeadFn(torch.autograd.Function):
@@ -953,4 +995,4 @@ def linear_act(x, W, b, act, tc=False):
 
 
 __all__ = ["ACT_GELU", "ACT_NONE", "ACT_SIGMOID", "BF16", "F32", "EmbeddingFn", "LinearActFn", "ResLnRowsFn",
-           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "CutFn", "GTrackFn", "GTrackLink", "gtrack_ok", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
+           "LocalTrackFn", "GlobalPreFn", "GlobalPostFn", "GlobalLink", "CutFn", "AttentionFn", "GTrackFn", "GTrackLink", "gtrack_ok", "ZeroArena", "join_side_streams", "global_fused_ok", "AttnPoolFn", "TokenHeadFn", "PretrainLossFn", "linear_act", "act_dtype", "dt_of", "to_wt", "conv_pack"]
