@@ -85,6 +85,14 @@ typedef struct pb_chunk_desc {
 } pb_chunk_desc;
 int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_flat, float scale, void* stream);
 
+/* Gradient exchange with the NVSwitch's in-fabric reduction (no counterpart in the single-process reference).
+ * mc_base: MULTICAST address of a symmetric buffer (torch.distributed._symmetric_memory: every rank's copy of the flat
+ * bucket behind one address); the range [offset, offset + numel) floats is all-reduced (sum) in place on every rank: rank r
+ * issues multimem.ld_reduce / multimem.st for its 1/world share.  Multiples of 4 floats.  The caller brackets the launch
+ * with a cross-rank barrier on the same stream (before: every rank's gradients are complete; after: every share is
+ * written).  ctas: CTAs to spend (<= 0: 32). */
+int pb_multimem_allreduce(float* mc_base, long long offset, long long numel, int rank, int world, int ctas, void* stream);
+
 /* ---- a20 / f-2: the optimizer step (utils.py:301 with Adam of dummy_tests.py:127-130), outside the metric's timed
  * region.  One launch updates every tensor of the table in place: m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2,
  * p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)  -- torch.optim.Adam's single-tensor formula (weight_decay adds

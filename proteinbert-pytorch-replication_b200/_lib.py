@@ -26,6 +26,7 @@ PROTOTYPES = {
     "pb_cast_f32_to_bf16": [_p, _p, _ll, _p],
     "pb_stage_weights": [_p, _i, _i, _p],
     "pb_flat_copy": [_p, _i, _p, _i, _f, _p],
+    "pb_multimem_allreduce": [_p, _ll, _ll, _i, _i, _i, _p],
     "pb_adam_step": [_p, _i, _f, C.c_double, C.c_double, _f, _f, _ll, _p],
     "pb_conv_weight_pack": [_p, _p, _p, _i, _i, _i, _p],
     "pb_embedding_fwd": [_p, _p, _p, _ll, _i, _i, _i, _p],

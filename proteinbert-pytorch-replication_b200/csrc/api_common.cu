@@ -244,3 +244,48 @@ size_t pb_workspace_bytes(const char* op, int M, int N, int K) {
 }
 
 }  // extern "C"
+
+// ---- gradient exchange over NVLink / NVSwitch with the switch's in-fabric reduction (NVLS) ---------------------------------
+// `mc` is the MULTICAST address of a symmetric buffer (every rank's copy of the flat gradient bucket mapped behind one
+// address by torch.distributed._symmetric_memory).  Rank r owns elements [r*n/world, (r+1)*n/world): multimem.ld_reduce
+// makes the switch fetch that range from every rank and add it (fp32), multimem.st writes the sum back into every rank's
+// copy.  Two-shot all-reduce with each byte crossing each GPU's links once per direction; the callers bracket the launch
+// with the symmetric-memory barrier (all ranks' gradients complete before, all ranges written after).
+__device__ __forceinline__ float4 mm_ld_reduce(const float* p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st(float* p, const float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// four reductions in flight per thread: the round trip through the switch is microseconds, so the loop is latency-bound
+__global__ void __launch_bounds__(512) multimem_allreduce_kernel(float* mc, long long n4_begin, long long n4_end) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long i = n4_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n4_end; i += 4 * stride) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = mm_ld_reduce(mc + 4 * (i + u * stride));
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mm_st(mc + 4 * (i + u * stride), v[u]);
+    }
+    for (; i < n4_end; i += stride) mm_st(mc + 4 * i, mm_ld_reduce(mc + 4 * i));
+}
+
+extern "C" int pb_multimem_allreduce(float* mc_base, long long offset, long long numel, int rank, int world, int ctas, void* stream) {
+    PB_REQUIRE(mc_base != nullptr && numel >= 0 && world >= 1 && rank >= 0 && rank < world, PB_ERR_SHAPE, "multimem_allreduce: bad arguments");
+    PB_REQUIRE(offset % 4 == 0 && numel % 4 == 0 && ((uintptr_t)mc_base % 16) == 0, PB_ERR_SHAPE,
+               "multimem_allreduce: offset and length must be multiples of 4 floats (16-byte vectors)");
+    if (numel == 0) return PB_OK;
+    const long long n4 = numel / 4, per = (n4 + world - 1) / world;
+    const long long b = offset / 4 + (long long)rank * per, e = offset / 4 + ((long long)(rank + 1) * per < n4 ? (long long)(rank + 1) * per : n4);
+    if (e <= b) return PB_OK;
+    if (ctas < 1) ctas = 32;
+    multimem_allreduce_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(mc_base, b, e);
+    pb_count_launch(1);
+    return pb_check_launch("pb_multimem_allreduce");
+}

@@ -128,7 +128,23 @@ class FlatGradBucket:
             off += (p.numel() + 3) // 4 * 4
         self.group_ranges.append((cur, gstart, off))
         self.numel = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
-        self.flat = torch.zeros((self.numel,), dtype=torch.float32, device=dev)
+        import os
+        self.exchange = os.environ.get("PB_B200_EXCHANGE", "nccl") if self.world > 1 else "nccl"
+        self._symm = None
+        if self.exchange == "nvls":
+            # the bucket in symmetric memory: every rank's copy behind one multicast address, reduced inside the NVSwitch by
+            # pb_multimem_allreduce.  The multicast mapping covers this buffer on every rank of the group.
+            import torch.distributed._symmetric_memory as symm
+            gname = (group or dist.group.WORLD).group_name
+            self.flat = symm.empty(self.numel, dtype=torch.float32, device=dev)
+            self.flat.zero_()
+            self._symm = symm.rendezvous(self.flat, gname)
+            if not self._symm.multicast_ptr:
+                raise RuntimeError("PB_B200_EXCHANGE=nvls needs NVSwitch multicast (no multicast address for the symmetric bucket)")
+            self._comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+            self._nvls_ctas = int(os.environ.get("PB_B200_NVLS_CTAS", "32"))
+        else:
+            self.flat = torch.zeros((self.numel,), dtype=torch.float32, device=dev)
         self.params = dict(named)
         self.loose, self._loose_table, self._loose_n = [], None, 0
         self.nblk = nblk
@@ -208,10 +224,31 @@ class FlatGradBucket:
         return self.numel
 
     def all_reduce(self, a: int = 0, b: Optional[int] = None, async_op: bool = False):
-        if self.world > 1:
-            b = self.numel if b is None else b
+        """Sum flat[a:b] over the ranks, in place.  async_op: the exchange runs beside the current stream; call .wait() on the
+        returned object to make the current stream wait for it."""
+        if self.world <= 1:
+            return None
+        b = self.numel if b is None else b
+        if self.exchange != "nvls":
             return dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
-        return None
+        cur = torch.cuda.current_stream(self.flat.device)
+        stream = self._comm_stream if async_op else cur
+        if async_op:
+            stream.wait_stream(cur)
+        rank = dist.get_rank(self.group)
+        with torch.cuda.stream(stream):
+            self._symm.barrier(channel=0)                  # every rank's gradients of this range are complete
+            ops._call("pb_multimem_allreduce", self._symm.multicast_ptr, a, b - a, rank, self.world, self._nvls_ctas, stream.cuda_stream)
+            self._symm.barrier(channel=1)                  # every rank's share is written
+        if not async_op:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(stream)
+
+        class _Work:
+            def wait(self_inner):
+                torch.cuda.current_stream(self.flat.device).wait_event(ev)
+        return _Work()
 
 
 class GraphedPretrainStep:
