@@ -558,6 +558,8 @@ def main():
         ddp_check = graph.ddp_check(X, Y, W)
         if hasattr(graph, "comm_profile"):
             comm = graph.comm_profile(X, Y, W, steps=max(5, min(args.steps, 20)))
+            comm["exchange"] = graph.bucket.exchange
+            comm["ddp_mode"] = graph.mode
 
     # ---- dominant kernel: conv pair forward, timed live with CUDA events around its launches ------------------
     peaks = load_peaks()

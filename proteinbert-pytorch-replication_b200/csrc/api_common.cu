@@ -262,16 +262,17 @@ __device__ __forceinline__ float4 mm_ld_reduce(const float* p) {
 __device__ __forceinline__ void mm_st(float* p, const float4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
-// four reductions in flight per thread: the round trip through the switch is microseconds, so the loop is latency-bound
+// Eight reductions in flight per thread: the round trip through the switch is microseconds, so the loop is latency-bound.
+// `ctas` encodes the launch shape: low 16 bits = CTAs, high bits = threads per CTA (0 -> 512).
 __global__ void __launch_bounds__(512) multimem_allreduce_kernel(float* mc, long long n4_begin, long long n4_end) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     long long i = n4_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + 3 * stride < n4_end; i += 4 * stride) {
-        float4 v[4];
+    for (; i + 7 * stride < n4_end; i += 8 * stride) {
+        float4 v[8];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = mm_ld_reduce(mc + 4 * (i + u * stride));
+        for (int u = 0; u < 8; ++u) v[u] = mm_ld_reduce(mc + 4 * (i + u * stride));
 #pragma unroll
-        for (int u = 0; u < 4; ++u) mm_st(mc + 4 * (i + u * stride), v[u]);
+        for (int u = 0; u < 8; ++u) mm_st(mc + 4 * (i + u * stride), v[u]);
     }
     for (; i < n4_end; i += stride) mm_st(mc + 4 * i, mm_ld_reduce(mc + 4 * i));
 }
@@ -284,8 +285,11 @@ extern "C" int pb_multimem_allreduce(float* mc_base, long long offset, long long
     const long long n4 = numel / 4, per = (n4 + world - 1) / world;
     const long long b = offset / 4 + (long long)rank * per, e = offset / 4 + ((long long)(rank + 1) * per < n4 ? (long long)(rank + 1) * per : n4);
     if (e <= b) return PB_OK;
-    if (ctas < 1) ctas = 32;
-    multimem_allreduce_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(mc_base, b, e);
+    int threads = ctas >> 16;
+    ctas &= 0xffff;
+    if (ctas < 1) ctas = 16;
+    if (threads < 32 || threads > 512) threads = 512;
+    multimem_allreduce_kernel<<<ctas, threads, 0, (cudaStream_t)stream>>>(mc_base, b, e);
     pb_count_launch(1);
     return pb_check_launch("pb_multimem_allreduce");
 }

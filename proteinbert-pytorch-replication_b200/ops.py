@@ -423,7 +423,12 @@ class CutFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, *gs):
+        if CUT_HOOK is not None:          # one-graph data-parallel step: mark "everything above the cut has been produced"
+            CUT_HOOK()
         return gs
+
+
+CUT_HOOK = None
 
 
 def gtrack_ok(B, G, C) -> bool:
