@@ -37,9 +37,9 @@ int pb_tc_pool_dz(const void* h, const void* wvT, const float* dpool, void* dzv,
 
 bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil);
 int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
-                    void* zw, void* u, double* stats, int B, int L, int ksize, int dil, int bo_mode, cudaStream_t st);
+                    void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, int bo_mode, cudaStream_t st);
 int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
-                      int L, int ksize, int dil, int bo_mode, cudaStream_t st);
+                      int L, int C, int ksize, int dil, int bo_mode, cudaStream_t st);
 void* pb_debug_ptr();
 bool pb_tc_token_ok(int B, int L, int C, int V);
 int pb_tc_token_logits(const void* h, const void* wo_pad, float* logits32, int B, int L, int C, cudaStream_t st);

@@ -209,14 +209,16 @@ int launch_conv(const void* a0, const void* a1, const void* w0, const void* w1, 
 }  // namespace
 
 bool pb_tc_conv_ok(int B, int L, int C, int ksize, int dil) {
-    return pb_tc_enabled() && C == kC && L % kBM == 0 && ksize >= 1 && (ksize & 1) && dil >= 1 && B >= 1;
+    if (!pb_tc_enabled() || !(ksize >= 1 && (ksize & 1) && dil >= 1 && B >= 1)) return false;
+    if (C == kC && L % kBM == 0) return true;                                  // this file's kernel (C = 128)
+    return pb_tc_mode() != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil);           // C = 256: the halo kernel only
 }
 
 int pb_tc_conv_pair_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l,
                         void* zn, void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, cudaStream_t st) {
     const int mode = pb_tc_mode();
     if (mode != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil))       // 256-position halo kernel unless the first generation is forced
-        return pb_tc_conv2_fwd(x, wn, ww, bn, bw, g2l, zn, zw, u, stats, B, L, ksize, dil, 0, st);
+        return pb_tc_conv2_fwd(x, wn, ww, bn, bw, g2l, zn, zw, u, stats, B, L, C, ksize, dil, 0, st);
     ConvEpiParams ep{};
     ep.x = (const bf16*)x; ep.bn = bn; ep.bw = bw; ep.g2l = g2l;
     ep.zn = (bf16*)zn; ep.zw = (bf16*)zw; ep.u = (bf16*)u; ep.stats = stats;
@@ -227,7 +229,7 @@ int pb_tc_conv_pair_dgrad(const void* du, const void* dzn, const void* dzw, cons
                           int B, int L, int C, int ksize, int dil, cudaStream_t st) {
     const int mode = pb_tc_mode();
     if (mode != 4 && pb_tc_conv2_ok(B, L, C, ksize, dil))
-        return pb_tc_conv2_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, ksize, dil, 0, st);
+        return pb_tc_conv2_dgrad(du, dzn, dzw, wn_bwd, ww_bwd, dx, B, L, C, ksize, dil, 0, st);
     ConvEpiParams ep{};
     ep.du = (const bf16*)du; ep.dx = (bf16*)dx;
     return launch_conv<false>(dzn, dzw, wn_bwd, ww_bwd, ep, B, L, ksize, dil, st);

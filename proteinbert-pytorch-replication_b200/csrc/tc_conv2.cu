@@ -27,9 +27,15 @@
 
 namespace {
 
-constexpr int kC = 128;
-constexpr int kRows = 256;                       // positions per CTA (two UMMA M = 128 sub-tiles)
-constexpr int kBTile = kC * 64 * 2;              // one weight tile [128 out-ch x 64 in-ch] bf16 = 16 KB
+constexpr int kBTile = 128 * 64 * 2;             // one weight tile [128 out-ch x 64 in-ch] bf16 = 16 KB
+// Channel count C is a template parameter: 128 (the default model) or 256 (BASELINE config 5).  The 512 TMEM columns hold
+// [C/128 output-channel tiles] x [positions] x [2 convolutions] accumulators, so a CTA takes 256 positions at C = 128 and
+// 128 positions at C = 256; either way the epilogue sees two 128-column halves per accumulator.
+template <int kC> struct ConvCfg {
+    static constexpr int kChunks = kC / 64;      // 64-channel K chunks (one halo buffer each)
+    static constexpr int kCoTiles = kC / 128;    // 128-channel output tiles (MMA M)
+    static constexpr int kN = kC == 128 ? 256 : 128;      // positions per CTA (MMA N)
+};
 constexpr int kThreads = 320;                    // warp 0 TMA, warp 1 MMA + TMEM, warps 2..9 epilogue
 
 struct Conv2Params {
@@ -39,6 +45,7 @@ struct Conv2Params {
     int L, ksize, dil;
     int hr[2];            // halo rows of input 0 / 1
     int a_bytes[2];       // shared-memory bytes of one (input, channel chunk) halo tile, multiple of 1024
+    int both_halos;       // data gradient at C = 256: both inputs' halos are resident from the start (no refill)
     unsigned long long* dbg;   // optional cycle counters of CTA 0 (pb_debug_buffer)
     int debug;            // experiment switches (PB_CONV2_DEBUG): 1 = align tap offsets to 8 rows (wrong results), 2 = skip epilogue math
     int base_offset_mode; // 0 (measured on B200): the 128-byte swizzle is a function of the absolute shared-memory
@@ -57,29 +64,33 @@ __device__ __forceinline__ uint64_t desc_sw128_bo(uint32_t saddr, uint32_t sbo_b
     return d;
 }
 
-template <bool kFwd, int kStages>
+template <bool kFwd, int kStages, int kC>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constant__ CUtensorMap mapA0t,
                 const __grid_constant__ CUtensorMap mapA1m, const __grid_constant__ CUtensorMap mapA1t,
                 const __grid_constant__ CUtensorMap mapB0, const __grid_constant__ CUtensorMap mapB1,
                 const __grid_constant__ CUtensorMap mapS0, const __grid_constant__ CUtensorMap mapS1,
                 const __grid_constant__ CUtensorMap mapS2, Conv2Params p) {
+    constexpr int kChunks = ConvCfg<kC>::kChunks, kCoTiles = ConvCfg<kC>::kCoTiles, kRows = ConvCfg<kC>::kN;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    // layout: two halo buffers (channel chunk 0 / 1, sized for the larger input) | weight ring | barriers.
-    // forward: both buffers hold x (wide margin) for the whole kernel.  dgrad: they hold dzn first; as soon as the
-    // narrow convolution has consumed chunk kc, the same buffer is refilled with dzw for the dilated one.
+    // layout: halo buffers (one per 64-channel chunk, sized for the larger input; two sets when both inputs stay
+    // resident) | weight ring | barriers.
+    // forward: the buffers hold x (wide margin) for the whole kernel.  dgrad at C = 128: they hold dzn first; as soon as
+    // the narrow convolution has consumed chunk kc, the same buffer is refilled with dzw for the dilated one.  dgrad at
+    // C = 256: dzn and dzw each have their own buffers (the 128-position halos are small enough).
     const int a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
-    uint8_t* ring = smem + 2 * a_buf;
+    const int n_abuf = p.both_halos ? 2 * kChunks : kChunks;
+    uint8_t* ring = smem + n_abuf * a_buf;
     // forward: the first half of the epilogue (narrow convolution) runs while the ring still streams the dilated
     // convolution's weights, so the staging tiles get their own area (one 3 x 2 KB buffer per epilogue warp) behind the
-    // ring; dgrad stages inside the ring, idle by then.
-    uint8_t* stage_base = kFwd ? ring + kStages * kBTile : ring;
+    // ring; dgrad stages inside the halo area, dead by then.
+    uint8_t* stage_base = kFwd ? ring + kStages * kBTile : smem;
     uint64_t* full_bar = (uint64_t*)(kFwd ? stage_base + 8 * 3 * 2048 : ring + kStages * kBTile);
     uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* a_full = empty_bar + kStages;          // [2 inputs][2 chunks]
-    uint64_t* a_free = a_full + 4;                   // [2 chunks]: narrow conv done with the buffer (dgrad)
-    uint64_t* tmem_full_bar = a_free + 2;            // [2]: forward: narrow conv's accumulators / all; dgrad uses [1] only
+    uint64_t* a_full = empty_bar + kStages;          // [2 inputs][kChunks]
+    uint64_t* a_free = a_full + 2 * kChunks;         // [kChunks]: narrow conv done with the buffer (dgrad, refill mode)
+    uint64_t* tmem_full_bar = a_free + kChunks;      // [2]: forward: narrow conv's accumulators / all; dgrad uses [1] only
     uint32_t* tmem_slot = (uint32_t*)(tmem_full_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -87,13 +98,15 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     const int b = blockIdx.x / tiles_per_sample;
     const int l0 = (blockIdx.x % tiles_per_sample) * kRows;
     const int half = p.ksize / 2;
-    const int n_iter = 2 * p.ksize * 2;              // (conv, tap, channel chunk)
+    const int per_conv = kCoTiles * kChunks * p.ksize;          // iterations per convolution: (output tile, channel chunk, tap)
+    const int n_iter = 2 * per_conv;
+    auto abuf_of = [&](int in, int kc) { return smem + (size_t)((p.both_halos ? in * kChunks : 0) + kc) * a_buf; };
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA0m); tma_prefetch_desc(&mapA1m); tma_prefetch_desc(&mapB0); tma_prefetch_desc(&mapB1);
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int i = 0; i < 4; ++i) mbar_init(&a_full[i], 1);
-        mbar_init(&a_free[0], 1); mbar_init(&a_free[1], 1);
+        for (int i = 0; i < 2 * kChunks; ++i) mbar_init(&a_full[i], 1);
+        for (int i = 0; i < kChunks; ++i) mbar_init(&a_free[i], 1);
         mbar_init(&tmem_full_bar[0], 1); mbar_init(&tmem_full_bar[1], 1);
         fence_barrier_init();
     }
@@ -104,45 +117,48 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();
 
-    // iteration i -> (conv, channel chunk, tap): chunk-major inside a convolution so that a halo buffer is released
-    // as early as possible
+    // iteration i -> (conv, output tile, channel chunk, tap): chunk-major inside an output tile so that at C = 128 a halo
+    // buffer is released as early as possible
     if (warp == 0) {
         if (lane == 0) {
             auto load_halo = [&](int in, int kc) {
                 const int margin = half * (in == 0 ? 1 : p.dil);
                 const int tail_rows = p.hr[in] - kRows;
-                uint64_t* bar = &a_full[in * 2 + kc];
-                uint8_t* dst = smem + kc * a_buf;
+                uint64_t* bar = &a_full[in * kChunks + kc];
+                uint8_t* dst = abuf_of(in, kc);
                 mbar_expect_tx(bar, p.hr[in] * 128);
                 tma_load_3d(dst, in == 0 ? &mapA0m : &mapA1m, bar, kc * 64, l0 - margin, b);
                 if (tail_rows > 0)
                     tma_load_3d(dst + kRows * 128, in == 0 ? &mapA0t : &mapA1t, bar, kc * 64, l0 - margin + kRows, b);
             };
             const int in_first = kFwd ? 1 : 0;
-            load_halo(in_first, 0);
-            load_halo(in_first, 1);
+            for (int kc = 0; kc < kChunks; ++kc) load_halo(in_first, kc);
+            if (!kFwd && p.both_halos)
+                for (int kc = 0; kc < kChunks; ++kc) load_halo(1, kc);
             for (int i = 0; i < n_iter; ++i) {
                 const int s = i % kStages;
-                const int conv = i / (p.ksize * 2), kc = (i / p.ksize) & 1, t = i % p.ksize;
-                if (!kFwd && conv == 1 && t == 0) {          // refill this chunk's buffer with the dilated conv's input
+                const int conv = i / per_conv, r = i % per_conv;
+                const int cot = r / (kChunks * p.ksize), kc = (r / p.ksize) % kChunks, t = r % p.ksize;
+                if (!kFwd && !p.both_halos && conv == 1 && t == 0) {   // refill this chunk's buffer with the dilated conv's input
                     mbar_wait(&a_free[kc], 0);
                     load_halo(1, kc);
                 }
                 mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
                 mbar_expect_tx(&full_bar[s], kBTile);
-                tma_load_2d(ring + s * kBTile, conv == 0 ? &mapB0 : &mapB1, &full_bar[s], kc * 64, t * kC);
+                tma_load_2d(ring + s * kBTile, conv == 0 ? &mapB0 : &mapB1, &full_bar[s], kc * 64, t * kC + cot * 128);
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(kC, kRows, 0, 0);        // M = 128 output channels, N = 256 positions
+            constexpr uint32_t idesc = make_idesc_bf16(128, kRows, 0, 0);       // M = 128 output channels, N = positions of the CTA
 #ifdef PB_CONV2_PROBE
             long long t_wait_full = 0, t_wait_a = 0;
             const long long t_begin = clock64();
 #endif
             for (int i = 0; i < n_iter; ++i) {
                 const int s = i % kStages;
-                const int conv = i / (p.ksize * 2), kc = (i / p.ksize) & 1, t = i % p.ksize;
+                const int conv = i / per_conv, r = i % per_conv;
+                const int cot = r / (kChunks * p.ksize), kc = (r / p.ksize) % kChunks, t = r % p.ksize;
                 const int in = kFwd ? 1 : conv;
                 const int d = conv == 0 ? 1 : p.dil;
                 // row of the halo tile at which this tap's window starts
@@ -151,7 +167,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
 #ifdef PB_CONV2_PROBE
                 long long c0 = clock64();
 #endif
-                if (t == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * 2 + kc], 0);
+                if (t == 0 && cot == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * kChunks + kc], 0);
 #ifdef PB_CONV2_PROBE
                 long long c1 = clock64();
 #endif
@@ -162,18 +178,19 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 tc_fence_after();
                 // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start address
                 // field (bits 0..13), so they are formed by adding constants -- the issuing thread is the bottleneck
-                const uint64_t dact = desc_sw128_bo(smem_u32(smem + kc * a_buf) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
+                const uint64_t dact = desc_sw128_bo(smem_u32(abuf_of(in, kc)) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
                 const uint64_t dwgt = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
-                // forward: one accumulator per convolution (the narrow one is drained while the dilated one is still being
-                // formed); data gradient: both convolutions add into the same accumulator
-                const uint32_t tm = tmem_base + (kFwd ? conv * kRows : 0);
-                const uint32_t acc0 = kFwd ? ((t == 0 && kc == 0) ? 0u : 1u) : (i == 0 ? 0u : 1u);
+                // forward: one accumulator set per convolution (the narrow one is drained while the dilated one is still
+                // being formed); data gradient: both convolutions add into the same accumulators.  Output tile `cot` owns
+                // columns [cot*128, +128) of its set at C = 256; at C = 128 the single tile spans all 256.
+                const uint32_t tm = tmem_base + (kFwd ? conv * 256 : 0) + cot * 128;
+                const uint32_t acc0 = kFwd ? ((t == 0 && kc == 0) ? 0u : 1u) : ((conv == 0 && t == 0 && kc == 0) ? 0u : 1u);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
                     umma_bf16(tm, dwgt + (uint64_t)(k * 2), dact + (uint64_t)(k * 2), idesc, k == 0 ? acc0 : 1u);
                 umma_commit(&empty_bar[s]);
-                if (!kFwd && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
-                if (kFwd && i == p.ksize * 2 - 1) umma_commit(&tmem_full_bar[0]);       // narrow conv complete
+                if (!kFwd && !p.both_halos && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
+                if (kFwd && i == per_conv - 1) umma_commit(&tmem_full_bar[0]);          // narrow conv complete
             }
             umma_commit(&tmem_full_bar[1]);
 #ifdef PB_CONV2_PROBE
@@ -192,12 +209,15 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
         const long long e0 = clock64();
         long long e1 = e0;
 #endif
-        const int hpos = (warp - 2) >> 2, q = warp & 3;
-        const int co = q * 32 + lane;                                   // this thread's channel
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + hpos * 128;
+        // C = 128: the warp's half selects positions 128*hsel .. +127 of the single output tile; C = 256: it selects the output
+        // tile (channels 128*hsel ..) and the warp covers all 128 positions.  Either way: TMEM columns 128*hsel .. +127.
+        const int hsel = (warp - 2) >> 2, q = warp & 3;
+        const int hpos = kC == 128 ? hsel : 0;                          // position half
+        const int co = (kC == 128 ? 0 : hsel * 128) + q * 32 + lane;    // this thread's channel
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + hsel * 128;
         // Output tiles leave through TMA: each warp stages a [32 positions x 32 channels] bf16 tile per tensor in shared
         // memory (64-byte swizzle) and one lane issues the bulk tensor store.
-        uint8_t* stage = stage_base + (warp - 2) * (kFwd ? 3 * 2048 : 2 * 3 * 2048);
+        uint8_t* stage = stage_base + (warp - 2) * (kFwd ? 3 * 2048 : 2 * 2048);
         const int lrow = l0 + hpos * 128;                               // first position of this warp's half
         const bool odd = lane & 1;
         const int cw = lane >> 1;                                       // 32-bit word of the pair (co & ~1, co | 1) in a 64-byte row
@@ -230,7 +250,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             // row is a multiple of 4 ((2 * half * dil) % 8 == 0, positions in steps of 32), so (row0 + j) & 7 == (j & 7) ^ (row0 & 7):
             // the per-position part of the swizzle is a compile-time constant
             const int xsw = (((co & 63) >> 3) ^ ((half * p.dil) & 7)) << 4;
-            const uint8_t* xbase = smem + (co >> 6) * a_buf + (co & 7) * 2;
+            const uint8_t* xbase = smem + (size_t)(co >> 6) * a_buf + (co & 7) * 2;
             mbar_wait(&tmem_full_bar[0], 0);
 #ifdef PB_CONV2_PROBE
             e1 = clock64();
@@ -258,7 +278,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 stage_transposed(sbuf, on);
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) { tma_store_3d(&mapS0, sbuf, q * 32, lrow + ch * 32, b); tma_store_commit(); }
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, co - lane, lrow + ch * 32, b); tma_store_commit(); }
             }
             // ---- second half, after the last MMA: zw = acc + bw, u = partial + gelu(zw), LayerNorm sums
             const float bwl = __ldg(p.bw + co);
@@ -268,7 +288,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             for (int ch = 0; ch < ((p.debug & 2) ? 0 : 4); ++ch) {
                 float pa[32], aw[32];
                 tmem_ld32(taddr + ch * 32, pa);
-                tmem_ld32(taddr + kRows + ch * 32, aw);
+                tmem_ld32(taddr + 256 + ch * 32, aw);
                 __align__(16) bf16 ow[32], ou[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
@@ -286,8 +306,8 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) {
-                    tma_store_3d(&mapS1, stage, q * 32, lrow + ch * 32, b);
-                    tma_store_3d(&mapS2, stage + 2048, q * 32, lrow + ch * 32, b);
+                    tma_store_3d(&mapS1, stage, co - lane, lrow + ch * 32, b);
+                    tma_store_3d(&mapS2, stage + 2048, co - lane, lrow + ch * 32, b);
                     tma_store_commit();
                 }
             }
@@ -306,7 +326,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 for (int j = 0; j < 32; ++j) dv[j] = dup[(size_t)j * kC];
                 float an[32];
                 tmem_ld32(taddr + ch * 32, an);
-                uint8_t* sbuf = stage + (ch & 1) * (3 * 2048);
+                uint8_t* sbuf = stage + (ch & 1) * 2048;
                 if (ch >= 2) {                                           // the buffer's previous store must have read it
                     if (lane == 0) tma_store_wait_read<1>();
                     __syncwarp();
@@ -317,7 +337,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 stage_transposed(sbuf, od);
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) { tma_store_3d(&mapS0, sbuf, q * 32, lrow + ch * 32, b); tma_store_commit(); }
+                if (lane == 0) { tma_store_3d(&mapS0, sbuf, co - lane, lrow + ch * 32, b); tma_store_commit(); }
             }
         }
         if (lane == 0) tma_store_wait<0>();
@@ -337,21 +357,22 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     }
 }
 
-int act_map(CUtensorMap* m, const void* base, int B, int L, int box_rows) {
-    const uint64_t dims[3] = {(uint64_t)kC, (uint64_t)L, (uint64_t)B};
-    const uint64_t strides[2] = {(uint64_t)kC * 2, (uint64_t)L * kC * 2};
+int act_map(CUtensorMap* m, const void* base, int B, int L, int C, int box_rows) {
+    const uint64_t dims[3] = {(uint64_t)C, (uint64_t)L, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)C * 2, (uint64_t)L * C * 2};
     const uint32_t box[3] = {64, (uint32_t)box_rows, 1};
     return pb_make_tmap_bf16(m, base, 3, dims, strides, box);
 }
-int w_map(CUtensorMap* m, const void* base, int ksize) {
-    const uint64_t dims[2] = {(uint64_t)kC, (uint64_t)ksize * kC};
-    const uint64_t strides[1] = {(uint64_t)kC * 2};
-    const uint32_t box[2] = {64, (uint32_t)kC};
+int w_map(CUtensorMap* m, const void* base, int C, int ksize) {          // [k][Co][Ci] pack: rows = tap*Co + co, box = 128 x 64
+    const uint64_t dims[2] = {(uint64_t)C, (uint64_t)ksize * C};
+    const uint64_t strides[1] = {(uint64_t)C * 2};
+    const uint32_t box[2] = {64, 128};
     return pb_make_tmap_bf16(m, base, 2, dims, strides, box);
 }
 
-template <bool kFwd, int kStages>
+template <bool kFwd, int kStages, int kC>
 int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv2Params p, int B, int L, cudaStream_t st) {
+    constexpr int kRows = ConvCfg<kC>::kN, kChunks = ConvCfg<kC>::kChunks;
     const int half = p.ksize / 2;
     static const int debug_env = [] { const char* e = getenv("PB_CONV2_DEBUG"); return e ? atoi(e) : 0; }();   // read once
     p.debug = debug_env;
@@ -359,6 +380,7 @@ int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv
     p.hr[0] = kRows + 2 * half;
     p.hr[1] = kRows + 2 * half * p.dil;
     for (int i = 0; i < 2; ++i) p.a_bytes[i] = (p.hr[i] * 128 + 1023) / 1024 * 1024;
+    p.both_halos = (!kFwd && kC == 256) ? 1 : 0;
     CUtensorMap mA0m, mA0t, mA1m, mA1t, mB0, mB1, mS0, mS1, mS2;
     int rc;
     {   // store maps: 32 positions x 32 channels per box, 64-byte swizzle
@@ -372,51 +394,64 @@ int launch2(const void* a0, const void* a1, const void* w0, const void* w1, Conv
         if ((rc = pb_make_tmap_bf16(&mS1, o1, 3, dims, strides, box, 64))) return rc;
         if ((rc = pb_make_tmap_bf16(&mS2, o2, 3, dims, strides, box, 64))) return rc;
     }
-    if ((rc = act_map(&mA0m, a0, B, L, kRows))) return rc;
-    if ((rc = act_map(&mA0t, a0, B, L, p.hr[0] - kRows))) return rc;
-    if ((rc = act_map(&mA1m, a1, B, L, kRows))) return rc;
-    if ((rc = act_map(&mA1t, a1, B, L, p.hr[1] - kRows))) return rc;
-    if ((rc = w_map(&mB0, w0, p.ksize))) return rc;
-    if ((rc = w_map(&mB1, w1, p.ksize))) return rc;
+    if ((rc = act_map(&mA0m, a0, B, L, kC, kRows))) return rc;
+    if ((rc = act_map(&mA0t, a0, B, L, kC, p.hr[0] - kRows))) return rc;
+    if ((rc = act_map(&mA1m, a1, B, L, kC, kRows))) return rc;
+    if ((rc = act_map(&mA1t, a1, B, L, kC, p.hr[1] - kRows))) return rc;
+    if ((rc = w_map(&mB0, w0, kC, p.ksize))) return rc;
+    if ((rc = w_map(&mB1, w1, kC, p.ksize))) return rc;
     const size_t a_buf = p.a_bytes[0] > p.a_bytes[1] ? p.a_bytes[0] : p.a_bytes[1];
-    const size_t smem = 2 * a_buf + (size_t)kStages * kBTile + (kFwd ? 8 * 3 * 2048 : 0) + 1024 + 256;
+    const size_t smem = (size_t)(p.both_halos ? 2 : 1) * kChunks * a_buf + (size_t)kStages * kBTile + (kFwd ? 8 * 3 * 2048 : 0) + 1024 + 256;
     PB_REQUIRE(smem <= 232448, PB_ERR_UNSUPPORTED, "conv2: %zu bytes of shared memory needed", smem);
     static size_t smem_set = 0;
     if (smem_set != smem) {
-        PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PB_CUDA(cudaFuncSetAttribute(tc_conv2_kernel<kFwd, kStages, kC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set = smem;
     }
-    PB_CUDA(pb_launch_pdl(tc_conv2_kernel<kFwd, kStages>, dim3(B * (L / kRows)), dim3(kThreads), smem, st, mA0m, mA0t, mA1m, mA1t,
+    PB_CUDA(pb_launch_pdl(tc_conv2_kernel<kFwd, kStages, kC>, dim3(B * (L / kRows)), dim3(kThreads), smem, st, mA0m, mA0t, mA1m, mA1t,
                           mB0, mB1, mS0, mS1, mS2, p));
     pb_count_launch(1);
     return pb_check_launch(kFwd ? "tc_conv2_fwd" : "tc_conv2_dgrad");
 }
 
+// ring depths: C = 128: 6 stages forward (+ 48 KB of staging), 9 data gradient; C = 256 (four halo chunks): 4 and 3
+constexpr int kStF128 = 6, kStD128 = 9, kStF256 = 4, kStD256 = 3;
+
+size_t conv2_smem(int C, bool fwd, int ksize, int dil) {
+    const int half = ksize / 2, rows = C == 128 ? 256 : 128, chunks = C / 64;
+    const size_t a0 = ((size_t)(rows + 2 * half) * 128 + 1023) / 1024 * 1024, a1 = ((size_t)(rows + 2 * half * dil) * 128 + 1023) / 1024 * 1024;
+    const size_t am = a0 > a1 ? a0 : a1;
+    const int st = C == 128 ? (fwd ? kStF128 : kStD128) : (fwd ? kStF256 : kStD256);
+    return (size_t)((!fwd && C == 256) ? 2 : 1) * chunks * am + (size_t)st * kBTile + (fwd ? 8 * 3 * 2048 : 0) + 1024 + 256;
+}
+
 }  // namespace
 
-// halo kernel covers: C = 128, L a multiple of 256, kernel size 9 class shapes whose halos fit shared memory
+// halo kernel covers: C = 128 (L a multiple of 256) or C = 256 (L a multiple of 128), odd kernel sizes whose halos fit shared memory
 bool pb_tc_conv2_ok(int B, int L, int C, int ksize, int dil) {
-    if (!(C == kC && L % kRows == 0 && (ksize & 1) && ksize >= 3 && dil >= 1 && B >= 1)) return false;
+    if (!((C == 128 || C == 256) && (ksize & 1) && ksize >= 3 && dil >= 1 && B >= 1)) return false;
+    const int rows = C == 128 ? 256 : 128;
+    if (L % rows != 0) return false;
     const int half = ksize / 2;
     if ((2 * half) % 8 != 0 || (2 * half * dil) % 8 != 0) return false;     // halo tails are whole 8-row swizzle groups
-    const size_t a0 = (size_t)(kRows + 2 * half) * 128, a1 = (size_t)(kRows + 2 * half * dil) * 128;
-    const size_t am = a0 > a1 ? a0 : a1;
-    return 2 * am + 9 * kBTile + 2048 <= 232448 && 2 * am + 6 * kBTile + 8 * 3 * 2048 + 2048 <= 232448 && 2 * half * dil <= 256;
+    return conv2_smem(C, true, ksize, dil) <= 232448 && conv2_smem(C, false, ksize, dil) <= 232448 && 2 * half * dil <= rows;
 }
 
 int pb_tc_conv2_fwd(const void* x, const void* wn, const void* ww, const float* bn, const float* bw, const float* g2l, void* zn,
-                    void* zw, void* u, double* stats, int B, int L, int ksize, int dil, int bo_mode, cudaStream_t st) {
+                    void* zw, void* u, double* stats, int B, int L, int C, int ksize, int dil, int bo_mode, cudaStream_t st) {
     Conv2Params p{};
     p.x = (const bf16*)x; p.bn = bn; p.bw = bw; p.g2l = g2l;
     p.zn = (bf16*)zn; p.zw = (bf16*)zw; p.u = (bf16*)u; p.stats = stats;
     p.L = L; p.ksize = ksize; p.dil = dil; p.base_offset_mode = bo_mode;
-    return launch2<true, 6>(x, x, wn, ww, p, B, L, st);      // 6-stage ring + 48 KB of epilogue staging
+    if (C == 256) return launch2<true, kStF256, 256>(x, x, wn, ww, p, B, L, st);
+    return launch2<true, kStF128, 128>(x, x, wn, ww, p, B, L, st);
 }
 
 int pb_tc_conv2_dgrad(const void* du, const void* dzn, const void* dzw, const void* wn_bwd, const void* ww_bwd, void* dx, int B,
-                      int L, int ksize, int dil, int bo_mode, cudaStream_t st) {
+                      int L, int C, int ksize, int dil, int bo_mode, cudaStream_t st) {
     Conv2Params p{};
     p.du = (const bf16*)du; p.dx = (bf16*)dx;
     p.L = L; p.ksize = ksize; p.dil = dil; p.base_offset_mode = bo_mode;
-    return launch2<false, 9>(dzn, dzw, wn_bwd, ww_bwd, p, B, L, st);
+    if (C == 256) return launch2<false, kStD256, 256>(dzn, dzw, wn_bwd, ww_bwd, p, B, L, st);
+    return launch2<false, kStD128, 128>(dzn, dzw, wn_bwd, ww_bwd, p, B, L, st);
 }

@@ -19,6 +19,7 @@ from test_gpu_parity import CANCELLATION_PRONE, MATH_ZERO, build_model, check_bf
 pytestmark = pytest.mark.gpu
 
 CONFIG1 = dict(sequences_length=512, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=6)
+CONFIG5 = dict(sequences_length=1024, num_annotations=8943, local_dim=256, global_dim=1024, key_dim=64, num_heads=4, num_blocks=2)
 CONFIG4 = dict(sequences_length=2048, num_annotations=8943, local_dim=128, global_dim=512, key_dim=64, num_heads=4, num_blocks=2)
 
 # bf16 precision, tensors whose gradient is a cancelling sum (global-track weights, W_parameter, the heads' Wv):
@@ -53,6 +54,29 @@ def config1_ref():
 @pytest.fixture(scope="module")
 def config4_ref():
     return oracle_case(CONFIG4, 2, 31)
+
+
+@pytest.fixture(scope="module")
+def config5_ref():
+    return oracle_case(CONFIG5, 2, 41)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_config5_shape_full_step_against_fp64_oracle(pb, config5_ref, precision):
+    """The scaled-width shape of BASELINE.json configs[4] (local 256 / global 1024, seq 1024), 2 blocks: the convolutions take
+    the C = 256 instantiation of the halo kernel, the linear / pooling GEMMs the general tcgen05 kernels."""
+    params, batch, ref = config5_ref
+    model = build_model(pb, CONFIG5, params, precision)
+    p_local, p_global, loss, grads = run_step(pb, model, batch)
+    if precision == "fp32":
+        assert_close_rel(p_local, ref[0], 1e-4, what="p_local")
+        assert_close_rel(p_global, ref[1], 1e-4, what="p_global")
+        assert abs(float(loss) - float(ref[2])) <= 1e-4 * abs(float(ref[2]))
+        check_fp32(grads, ref[3], "config5/")
+    else:
+        assert_tensor_core_paths(pb, 2, CONFIG5)
+        check_bf16(p_local, p_global, loss, grads, ref)
+        check_bf16_cancellation_prone(grads, ref[3], "config5/")
 
 
 def assert_tensor_core_paths(pb, B, cfg):
@@ -146,9 +170,9 @@ def test_config2_batch64_graphed_step_matches_eager_and_oracle_sample(pb):
     assert abs(loss_e - ref_loss) <= 2e-3 * abs(ref_loss), (loss_e, ref_loss)
 
 
-def _conv_case(B, L, seed):
+def _conv_case(B, L, seed, C=128):
     g = torch.Generator().manual_seed(seed)
-    C, KS = 128, 9
+    KS = 9
     x = torch.randn(B, L, C, generator=g).bfloat16()
     wn = (torch.randn(C, C, KS, generator=g) * 0.05)
     ww = (torch.randn(C, C, KS, generator=g) * 0.05)
@@ -157,21 +181,23 @@ def _conv_case(B, L, seed):
 
 
 def _row_windows(L):
-    """Row ranges asserted separately: both sequence ends and every 256-row tile seam (+-20 rows: the dilated halo)."""
+    """Row ranges asserted separately: both sequence ends and every 128-row tile seam (+-20 rows: the dilated halo; the CTAs
+    take 256 positions at C = 128 and 128 at C = 256)."""
     wins = [("first rows", slice(0, 20)), ("last rows", slice(L - 20, L))]
-    for seam in range(256, L, 256):
+    for seam in range(128, L, 128):
         wins.append((f"seam {seam}", slice(seam - 20, seam + 20)))
     return wins
 
 
-@pytest.mark.parametrize("B,L", [(3, 512), (2, 2048)])
-def test_conv_pair_forward_bf16_across_tile_seams(pb, B, L):
-    """pb_conv_pair_fwd (tcgen05 halo kernel) against conv1d in fp64 on the bf16-rounded operands, element-wise."""
+@pytest.mark.parametrize("B,L,C", [(3, 512, 128), (2, 2048, 128), (2, 1024, 256), (3, 384, 256)])
+def test_conv_pair_forward_bf16_across_tile_seams(pb, B, L, C):
+    """pb_conv_pair_fwd (tcgen05 halo kernel; C = 128: 256 positions per CTA, C = 256: 128) against conv1d in fp64 on the
+    bf16-rounded operands, element-wise."""
     from proteinbert_b200 import ops
     lib = pb._lib.lib()
-    C, KS, DIL = 128, 9, 5
+    KS, DIL = 9, 5
     assert lib.pb_tc_path(b"conv", B, L, C, 0, KS, DIL) == 2
-    x, wn, ww, bn, bw, g2l = _conv_case(B, L, 40 + L)
+    x, wn, ww, bn, bw, g2l = _conv_case(B, L, 40 + L, C)
     xd = x.cuda()
     wn_f, _ = ops.conv_pack(wn.cuda(), 1)
     ww_f, _ = ops.conv_pack(ww.cuda(), 1)
@@ -198,15 +224,15 @@ def test_conv_pair_forward_bf16_across_tile_seams(pb, B, L):
     assert_close_rel(stats[:, 1], (us * us).sum((1, 2)), 1e-5, what="sum u^2")
 
 
-@pytest.mark.parametrize("B,L", [(3, 512), (2, 2048)])
-def test_conv_pair_backward_bf16_across_tile_seams(pb, B, L):
+@pytest.mark.parametrize("B,L,C", [(3, 512, 128), (2, 2048, 128), (2, 1024, 256), (3, 384, 256)])
+def test_conv_pair_backward_bf16_across_tile_seams(pb, B, L, C):
     """pb_conv_pair_bwd (tcgen05 data gradient + three-tap weight-gradient kernel) against torch autograd of conv1d in
     fp64 on the bf16-rounded operands: dx element-wise incl. the tile seams, dWn, dWw."""
     from proteinbert_b200 import ops
     lib = pb._lib.lib()
-    C, KS, DIL = 128, 9, 5
+    KS, DIL = 9, 5
     assert lib.pb_tc_path(b"conv", B, L, C, 0, KS, DIL) == 2
-    x, wn, ww, _, _, _ = _conv_case(B, L, 50 + L)
+    x, wn, ww, _, _, _ = _conv_case(B, L, 50 + L, C)
     g = torch.Generator().manual_seed(60 + L)
     du = (torch.randn(B, L, C, generator=g) * 0.1).bfloat16()
     dzn = (torch.randn(B, L, C, generator=g) * 0.1).bfloat16()
