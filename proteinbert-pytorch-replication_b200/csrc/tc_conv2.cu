@@ -98,8 +98,6 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
     const int b = blockIdx.x / tiles_per_sample;
     const int l0 = (blockIdx.x % tiles_per_sample) * kRows;
     const int half = p.ksize / 2;
-    const int per_conv = kCoTiles * kChunks * p.ksize;          // iterations per convolution: (output tile, channel chunk, tap)
-    const int n_iter = 2 * per_conv;
     auto abuf_of = [&](int in, int kc) { return smem + (size_t)((p.both_halos ? in * kChunks : 0) + kc) * a_buf; };
 
     if (warp == 0 && lane == 0) {
@@ -135,18 +133,21 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             for (int kc = 0; kc < kChunks; ++kc) load_halo(in_first, kc);
             if (!kFwd && p.both_halos)
                 for (int kc = 0; kc < kChunks; ++kc) load_halo(1, kc);
-            for (int i = 0; i < n_iter; ++i) {
-                const int s = i % kStages;
-                const int conv = i / per_conv, r = i % per_conv;
-                const int cot = r / (kChunks * p.ksize), kc = (r / p.ksize) % kChunks, t = r % p.ksize;
-                if (!kFwd && !p.both_halos && conv == 1 && t == 0) {   // refill this chunk's buffer with the dilated conv's input
-                    mbar_wait(&a_free[kc], 0);
-                    load_halo(1, kc);
-                }
-                mbar_wait(&empty_bar[s], ((i / kStages) & 1) ^ 1);
-                mbar_expect_tx(&full_bar[s], kBTile);
-                tma_load_2d(ring + s * kBTile, conv == 0 ? &mapB0 : &mapB1, &full_bar[s], kc * 64, t * kC + cot * 128);
-            }
+            int s = 0;
+            uint32_t ph = 1;                                 // parity to wait for on empty_bar[s]: flips each time the ring wraps
+            for (int conv = 0; conv < 2; ++conv)
+                for (int cot = 0; cot < kCoTiles; ++cot)
+                    for (int kc = 0; kc < kChunks; ++kc)
+                        for (int t = 0; t < p.ksize; ++t) {
+                            if (!kFwd && !p.both_halos && conv == 1 && t == 0) {   // refill this chunk's buffer with the dilated conv's input
+                                mbar_wait(&a_free[kc], 0);
+                                load_halo(1, kc);
+                            }
+                            mbar_wait(&empty_bar[s], ph);
+                            mbar_expect_tx(&full_bar[s], kBTile);
+                            tma_load_2d(ring + s * kBTile, conv == 0 ? &mapB0 : &mapB1, &full_bar[s], kc * 64, t * kC + cot * 128);
+                            if (++s == kStages) { s = 0; ph ^= 1; }
+                        }
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -155,42 +156,50 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             long long t_wait_full = 0, t_wait_a = 0;
             const long long t_begin = clock64();
 #endif
-            for (int i = 0; i < n_iter; ++i) {
-                const int s = i % kStages;
-                const int conv = i / per_conv, r = i % per_conv;
-                const int cot = r / (kChunks * p.ksize), kc = (r / p.ksize) % kChunks, t = r % p.ksize;
+            int s = 0;
+            uint32_t ph = 0;                                 // parity to wait for on full_bar[s]
+            for (int conv = 0; conv < 2; ++conv) {
                 const int in = kFwd ? 1 : conv;
                 const int d = conv == 0 ? 1 : p.dil;
-                // row of the halo tile at which this tap's window starts
-                int row_off = kFwd ? half * (p.dil - d) + t * d : (2 * half - t) * d;
-                if (p.debug & 1) row_off &= ~7;
+                for (int cot = 0; cot < kCoTiles; ++cot) {
+                    // forward: one accumulator set per convolution (the narrow one is drained while the dilated one is still
+                    // being formed); data gradient: both convolutions add into the same accumulators.  Output tile `cot` owns
+                    // columns [cot*128, +128) of its set at C = 256; at C = 128 the single tile spans all 256.
+                    const uint32_t tm = tmem_base + (kFwd ? conv * 256 : 0) + cot * 128;
+                    for (int kc = 0; kc < kChunks; ++kc) {
+                        const uint32_t abase = smem_u32(smem + (size_t)((p.both_halos ? in * kChunks : 0) + kc) * a_buf);
+                        for (int t = 0; t < p.ksize; ++t) {
+                            // row of the halo tile at which this tap's window starts
+                            int row_off = kFwd ? half * (p.dil - d) + t * d : (2 * half - t) * d;
+                            if (p.debug & 1) row_off &= ~7;
 #ifdef PB_CONV2_PROBE
-                long long c0 = clock64();
+                            long long c0 = clock64();
 #endif
-                if (t == 0 && cot == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * kChunks + kc], 0);
+                            if (t == 0 && cot == 0 && (conv == 0 || !kFwd)) mbar_wait(&a_full[in * kChunks + kc], 0);
 #ifdef PB_CONV2_PROBE
-                long long c1 = clock64();
+                            long long c1 = clock64();
 #endif
-                mbar_wait(&full_bar[s], (i / kStages) & 1);
+                            mbar_wait(&full_bar[s], ph);
 #ifdef PB_CONV2_PROBE
-                t_wait_a += c1 - c0; t_wait_full += clock64() - c1;
+                            t_wait_a += c1 - c0; t_wait_full += clock64() - c1;
 #endif
-                tc_fence_after();
-                // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start address
-                // field (bits 0..13), so they are formed by adding constants -- the issuing thread is the bottleneck
-                const uint64_t dact = desc_sw128_bo(smem_u32(abuf_of(in, kc)) + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
-                const uint64_t dwgt = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
-                // forward: one accumulator set per convolution (the narrow one is drained while the dilated one is still
-                // being formed); data gradient: both convolutions add into the same accumulators.  Output tile `cot` owns
-                // columns [cot*128, +128) of its set at C = 256; at C = 128 the single tile spans all 256.
-                const uint32_t tm = tmem_base + (kFwd ? conv * 256 : 0) + cot * 128;
-                const uint32_t acc0 = kFwd ? ((t == 0 && kc == 0) ? 0u : 1u) : ((conv == 0 && t == 0 && kc == 0) ? 0u : 1u);
+                            tc_fence_after();
+                            // one descriptor pair per stage; the per-MMA variants differ only in the 16-byte-granular start
+                            // address field (bits 0..13), so they are formed by adding constants -- the issuing thread is the
+                            // bottleneck (no divisions in this loop either)
+                            const uint64_t dact = desc_sw128_bo(abase + (uint32_t)row_off * 128u, 1024, p.base_offset_mode);
+                            const uint64_t dwgt = make_smem_desc_sw128(smem_u32(ring + s * kBTile), 16, 1024);
+                            const uint32_t acc0 = kFwd ? ((t == 0 && kc == 0) ? 0u : 1u) : ((conv == 0 && t == 0 && kc == 0) ? 0u : 1u);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    umma_bf16(tm, dwgt + (uint64_t)(k * 2), dact + (uint64_t)(k * 2), idesc, k == 0 ? acc0 : 1u);
-                umma_commit(&empty_bar[s]);
-                if (!kFwd && !p.both_halos && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
-                if (kFwd && i == per_conv - 1) umma_commit(&tmem_full_bar[0]);          // narrow conv complete
+                            for (int k = 0; k < 4; ++k)
+                                umma_bf16(tm, dwgt + (uint64_t)(k * 2), dact + (uint64_t)(k * 2), idesc, k == 0 ? acc0 : 1u);
+                            umma_commit(&empty_bar[s]);
+                            if (!kFwd && !p.both_halos && conv == 0 && t == p.ksize - 1) umma_commit(&a_free[kc]);   // buffer kc may be refilled
+                            if (++s == kStages) { s = 0; ph ^= 1; }
+                        }
+                    }
+                }
+                if (kFwd && conv == 0) umma_commit(&tmem_full_bar[0]);          // narrow conv complete
             }
             umma_commit(&tmem_full_bar[1]);
 #ifdef PB_CONV2_PROBE
