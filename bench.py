@@ -518,7 +518,8 @@ def main():
             n0 = pb.launch_count()
             graph = pb.GraphedPretrainStep(model, X, Y, W, warmup=1, overlap=bool(args.ddp_overlap))
             launches_per_step = (pb.launch_count() - n0) // 2          # one warm-up step + the captured step
-            graph(X, Y, W)
+            for _ in range(max(1, min(3, args.warmup))):      # warm replays of the very thing that is timed (first exchanges set up links)
+                graph(X, Y, W)
             torch.cuda.synchronize()
         except Exception as e:          # capture is an optimisation of launch overhead, not a correctness path
             print(f"[bench] CUDA graph capture failed ({type(e).__name__}: {e}); timing eagerly", file=sys.stderr)
@@ -530,6 +531,9 @@ def main():
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    import gc
+    gc.collect()
+    gc.disable()          # a collection pause on one of N host processes would be charged to every rank's step (max over ranks)
     barrier()
     n0 = pb.launch_count()
     e0.record()
@@ -542,6 +546,7 @@ def main():
             step()
     e1.record()
     barrier()
+    gc.enable()
     ms = e0.elapsed_time(e1)
     extra = getattr(graph, "launches_outside_graph", 0) if (graph is not None and world > 1) else 0
     launches = ((launches_per_step + extra) * args.steps) if graph is not None else (pb.launch_count() - n0)
@@ -560,6 +565,8 @@ def main():
             comm = graph.comm_profile(X, Y, W, steps=max(5, min(args.steps, 20)))
             comm["exchange"] = graph.bucket.exchange
             comm["ddp_mode"] = graph.mode
+            comm["exchanges_per_step"] = 1 + len(graph.cut_offsets or [])
+            comm["early_exchange_bytes"] = [4 * o for o in (graph.cut_offsets or [])]
 
     # ---- dominant kernel: conv pair forward, timed live with CUDA events around its launches ------------------
     peaks = load_peaks()

@@ -90,7 +90,8 @@ int pb_flat_copy(const pb_chunk_desc* chunks_dev, int n, float* flat, int to_fla
  * bucket behind one address); the range [offset, offset + numel) floats is all-reduced (sum) in place on every rank: rank r
  * issues multimem.ld_reduce / multimem.st for its 1/world share.  Multiples of 4 floats.  The caller brackets the launch
  * with a cross-rank barrier on the same stream (before: every rank's gradients are complete; after: every share is
- * written).  ctas: CTAs to spend in the low 16 bits (0: 16), threads per CTA in the bits above (0: 512). */
+ * written).  ctas: launch shape -- bits 0-15 CTAs (0: 16), bits 16-27 threads per CTA (0: 512), bits 28-30 reductions in
+ * flight per thread (0: 8, 1: 1, 2: 2, 3: 4); small shapes are for an exchange that runs beside compute kernels. */
 int pb_multimem_allreduce(float* mc_base, long long offset, long long numel, int rank, int world, int ctas, void* stream);
 
 /* ---- a20 / f-2: the optimizer step (utils.py:301 with Adam of dummy_tests.py:127-130), outside the metric's timed

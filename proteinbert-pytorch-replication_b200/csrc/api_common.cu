@@ -262,17 +262,20 @@ __device__ __forceinline__ float4 mm_ld_reduce(const float* p) {
 __device__ __forceinline__ void mm_st(float* p, const float4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
-// Eight reductions in flight per thread: the round trip through the switch is microseconds, so the loop is latency-bound.
-// `ctas` encodes the launch shape: low 16 bits = CTAs, high bits = threads per CTA (0 -> 512).
+// kInFlight reductions in flight per thread: the round trip through the switch is microseconds, so the loop is latency-bound.
+// `ctas` encodes the launch shape: bits 0-15 = CTAs (0 -> 16), bits 16-27 = threads per CTA (0 -> 512), bits 28-30 = in-flight
+// selector (0 -> 8, 1 -> 1, 2 -> 2, 3 -> 4).  The small shapes are for an exchange that runs BESIDE compute kernels: every
+// outstanding reduction holds a load slot of its SM for the whole round trip, and CTAs of other kernels on that SM queue behind.
+template <int kInFlight>
 __global__ void __launch_bounds__(512) multimem_allreduce_kernel(float* mc, long long n4_begin, long long n4_end) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     long long i = n4_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    for (; i + 7 * stride < n4_end; i += 8 * stride) {
-        float4 v[8];
+    for (; i + (kInFlight - 1) * stride < n4_end; i += kInFlight * stride) {
+        float4 v[kInFlight];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = mm_ld_reduce(mc + 4 * (i + u * stride));
+        for (int u = 0; u < kInFlight; ++u) v[u] = mm_ld_reduce(mc + 4 * (i + u * stride));
 #pragma unroll
-        for (int u = 0; u < 8; ++u) mm_st(mc + 4 * (i + u * stride), v[u]);
+        for (int u = 0; u < kInFlight; ++u) mm_st(mc + 4 * (i + u * stride), v[u]);
     }
     for (; i < n4_end; i += stride) mm_st(mc + 4 * i, mm_ld_reduce(mc + 4 * i));
 }
@@ -285,11 +288,18 @@ extern "C" int pb_multimem_allreduce(float* mc_base, long long offset, long long
     const long long n4 = numel / 4, per = (n4 + world - 1) / world;
     const long long b = offset / 4 + (long long)rank * per, e = offset / 4 + ((long long)(rank + 1) * per < n4 ? (long long)(rank + 1) * per : n4);
     if (e <= b) return PB_OK;
-    int threads = ctas >> 16;
+    int threads = (ctas >> 16) & 0xfff;
+    const int sel = (ctas >> 28) & 7;
     ctas &= 0xffff;
     if (ctas < 1) ctas = 16;
     if (threads < 32 || threads > 512) threads = 512;
-    multimem_allreduce_kernel<<<ctas, threads, 0, (cudaStream_t)stream>>>(mc_base, b, e);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (sel) {
+        case 1: multimem_allreduce_kernel<1><<<ctas, threads, 0, st>>>(mc_base, b, e); break;
+        case 2: multimem_allreduce_kernel<2><<<ctas, threads, 0, st>>>(mc_base, b, e); break;
+        case 3: multimem_allreduce_kernel<4><<<ctas, threads, 0, st>>>(mc_base, b, e); break;
+        default: multimem_allreduce_kernel<8><<<ctas, threads, 0, st>>>(mc_base, b, e); break;
+    }
     pb_count_launch(1);
     return pb_check_launch("pb_multimem_allreduce");
 }

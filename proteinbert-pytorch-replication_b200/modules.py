@@ -317,7 +317,10 @@ class ProteinBERT(nn.Module):
         g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU, tc)                # :301
         blocks = list(self.proteinBERT_blocks)
         ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
-        cut = getattr(self, "_boundary_at", None)        # training.GraphedPretrainStep: where backward is split in two
+        # training.GraphedPretrainStep: where backward is split in two (an int: the boundary tensors are kept in _boundary) or
+        # marked for the gradient exchange (a collection of block indices: ops.CUT_HOOK fires at each in backward)
+        cut = getattr(self, "_boundary_at", None)
+        cuts = () if cut is None else ((cut,) if isinstance(cut, int) else tuple(cut))
         Bsz, Lseq, Cloc = h.shape
         arena = ops.ZeroArena(len(blocks) * ops.ZeroArena.block_bytes(Bsz, Lseq, Cloc, g.shape[1]), h.device)   # one fill per step
         Cdim = blocks[0].local_dim
@@ -330,18 +333,20 @@ class ProteinBERT(nn.Module):
             for i, blk in enumerate(blocks):
                 blk._prestaged = dt
                 h, pool = blk.local_track(h, g2l, arena)
-                if cut is not None and i + 1 == cut:
+                if i + 1 in cuts:
                     # a proper cut of the autograd graph: everything above consumes only these four tensors (the inputs of the
                     # unit that spans the boundary and of block `cut`'s local track); h and pool come out of the same node
-                    h, pool, g, gh = ops.CutFn.apply(h, pool, g, gh)
-                    self._boundary = (h, pool, g, gh)
+                    h, pool, g, gh = ops.CutFn.apply(i + 1, h, pool, g, gh)
+                    if isinstance(cut, int):
+                        self._boundary = (h, pool, g, gh)
                 nxt = blocks[i + 1].global_pre_params() if i + 1 < len(blocks) else (None,) * 4
                 g, g2l, gh = ops.GTrackFn.apply(g, gh, pool, *blk.global_post_params(), *nxt, Cdim, links[i], links[i + 1])
         else:
             for i, blk in enumerate(blocks):
-                if cut is not None and i == cut:
-                    h, g = ops.CutFn.apply(h, g)
-                    self._boundary = (h, g)
+                if i in cuts:
+                    h, g = ops.CutFn.apply(i, h, g)
+                    if isinstance(cut, int):
+                        self._boundary = (h, g)
                 blk._prestaged = dt
                 h, g = blk.forward_channels_last(h, g, arena)
         lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]

@@ -418,14 +418,15 @@ class CutFn(torch.autograd.Function):
     runs before the second half asks for it."""
 
     @staticmethod
-    def forward(ctx, *ts):
+    def forward(ctx, tag, *ts):
+        ctx.tag = tag                     # which cut this is (the index of the block above it)
         return tuple(t.view_as(t) for t in ts)
 
     @staticmethod
     def backward(ctx, *gs):
-        if CUT_HOOK is not None:          # one-graph data-parallel step: mark "everything above the cut has been produced"
-            CUT_HOOK()
-        return gs
+        if CUT_HOOK is not None:          # one-graph data-parallel step: mark "everything above this cut has been produced"
+            CUT_HOOK(ctx.tag)
+        return (None,) + gs
 
 
 CUT_HOOK = None

@@ -146,7 +146,15 @@ class FlatGradBucket:
                 # rank of the group
                 self.flat, self._symm, self.exchange = flat, hdl, "nvls"
                 # 16 CTAs of 512 threads saturate the exchange on 8 GPUs (8 -> 160 us, 16 -> 156 us, 64 -> 170 us for 64.7 MB)
-                self._nvls_ctas = int(os.environ.get("PB_B200_NVLS_CTAS", "16")) | (int(os.environ.get("PB_B200_NVLS_THREADS", "512")) << 16)
+                self._nvls_ctas = self.nvls_shape(int(os.environ.get("PB_B200_NVLS_CTAS", "16")), int(os.environ.get("PB_B200_NVLS_THREADS", "512")))
+                # shape of an exchange that runs BESIDE backward (GraphedPretrainStep's early parts): every outstanding reduction
+                # holds a load slot of its SM for the microseconds of the switch round trip, and the compute CTAs sharing that SM
+                # queue behind them -- at 16 x 512 x 8 in flight concurrent LayerNorm / reduce kernels ran 3-6x slower and the
+                # overlap gained nothing.  8 x B200, step time: no overlap 1930 us, 16x512x8 1921, 8x256x4 1866, 148x32x2 1871,
+                # 32x128x2 1843, 16x128x4 1841 (scripts/ddp_sweep.py).
+                self._nvls_ctas_early = self.nvls_shape(int(os.environ.get("PB_B200_NVLS_EARLY_CTAS", "16")),
+                                                        int(os.environ.get("PB_B200_NVLS_EARLY_THREADS", "128")),
+                                                        int(os.environ.get("PB_B200_NVLS_EARLY_INFLIGHT", "4")))
             except Exception as e:
                 if want == "nvls":
                     raise
@@ -168,6 +176,11 @@ class FlatGradBucket:
         arr = np.array(rows, dtype=[("ptr", "<u8"), ("offset", "<i8"), ("numel", "<i8")])
         self._zero_table = torch.from_numpy(arr.view(np.uint8).copy()).to(dev)
         self._zero_n = len(rows)
+
+    @staticmethod
+    def nvls_shape(ctas: int, threads: int = 512, in_flight: int = 8) -> int:
+        """Launch shape word of pb_multimem_allreduce (include/pb_b200.h)."""
+        return (ctas & 0xffff) | ((threads & 0xfff) << 16) | ({8: 0, 1: 1, 2: 2, 4: 3}[in_flight] << 28)
 
     def sink(self):
         return ops.GradSink(self.flat, self.table)
@@ -249,11 +262,12 @@ class FlatGradBucket:
             return None
         stream = self._comm_stream
         if after_event is not None:
-            stream.wait_event(after_event)
+            for ev in (after_event if isinstance(after_event, (list, tuple)) else [after_event]):
+                stream.wait_event(ev)
         else:
             stream.wait_stream(cur)
         with torch.cuda.stream(stream):
-            self._exchange(a, b, stream)
+            self._exchange(a, b, stream, early=True)
         ev = torch.cuda.Event()
         ev.record(stream)
         flat = self.flat
@@ -264,12 +278,12 @@ class FlatGradBucket:
                 flat.record_stream(torch.cuda.current_stream(dev))
         return _Work()
 
-    def _exchange(self, a, b, stream):
-        """The collective itself, issued with `stream` current."""
+    def _exchange(self, a, b, stream, early=False):
+        """The collective itself, issued with `stream` current.  early: it runs beside backward."""
         if self.exchange == "nvls":
             self._symm.barrier(channel=0)                  # every rank's gradients of this range are complete
-            ops._call("pb_multimem_allreduce", self._symm.multicast_ptr, a, b - a, dist.get_rank(self.group), self.world, self._nvls_ctas,
-                      stream.cuda_stream)
+            ops._call("pb_multimem_allreduce", self._symm.multicast_ptr, a, b - a, dist.get_rank(self.group), self.world,
+                      self._nvls_ctas_early if early else self._nvls_ctas, stream.cuda_stream)
             self._symm.barrier(channel=1)                  # every rank's share is written
         else:
             dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, group=self.group)
@@ -285,11 +299,13 @@ class GraphedPretrainStep:
     construction.
 
     Data-parallel (torch.distributed initialised with world > 1): every gradient is written by its kernel into ONE flat
-    bucket (``FlatGradBucket``; ``.grad`` are views of it, 1/world is folded into the loss gradient) and backward is captured
-    as TWO graphs split at the middle block.  Per step: replay A (forward, loss, backward of the heads and the upper
-    blocks) -> asynchronous NCCL all-reduce of the first part of the bucket on NCCL's stream -> replay B (the lower
-    blocks, embedding, annotation-input layer) while that all-reduce runs -> all-reduce of the rest -> join.  No gather,
-    scatter or scaling kernels.  ``overlap=False`` keeps one graph and one all-reduce after it.
+    bucket (``FlatGradBucket``; ``.grad`` are views of it, 1/world is folded into the loss gradient).  The step stays ONE
+    graph; identity nodes (``ops.CutFn``) at chosen block boundaries record external events inside it, and the part of the
+    bucket that is complete above each cut is summed over the ranks on the communication stream while the graph goes on
+    below it -- with a small launch shape (few loads in flight per SM), because a full-rate exchange starves the compute
+    CTAs it shares SMs with.  What backward produces last (block 0, embedding, annotation-input matrix) is exchanged after
+    the graph at full rate.  No gather, scatter or scaling kernels.  ``overlap=False``: one exchange after the graph;
+    ``PB_B200_DDP_MODE=split``: two graphs with the first exchange issued between their replays.
 
         step = GraphedPretrainStep(model, X, Y, W)      # example batch fixes shapes / dtypes
         loss = step(X, Y, W)                            # host or device tensors
@@ -320,10 +336,22 @@ class GraphedPretrainStep:
         self.bucket = FlatGradBucket(model) if (distributed or force_bucket or force_split) else None
         self.graph_b = None
         self.launches_outside_graph = 0
-        cut = nblk // 2
+        # "event" mode marks several cuts (block indices, top-down): everything above a cut is exchanged while backward goes on
+        # below it.  Default: the middle block and block 1 -- what is left for the exposed last exchange is block 0, the
+        # embedding and the annotation-input matrix (18.3 of the 64.7 MB; its gradient is the last thing backward produces).
+        default_cuts = ([nblk // 2, 1] if nblk >= 4 else [nblk // 2]) if nblk >= 2 else [0]
+        cuts = [min(max(int(c), 1), nblk - 1) for c in os.environ.get("PB_B200_DDP_CUT", ",".join(map(str, default_cuts))).split(",")] if nblk >= 2 else [0]
+        cuts = sorted(set(cuts), reverse=True)
+        if mode != "event":
+            cuts = cuts[:1]
+        cut = cuts[0]
         units = model.uses_cluster_units(self.static[0].shape[0])
-        self.cut_offset = self.bucket.split_offset(cut, units) if (self.bucket is not None and mode in ("split", "event")) else None
-        self._cut_event = torch.cuda.Event(external=True) if mode == "event" else None
+        self.cuts = cuts
+        self.cut_offsets = [self.bucket.split_offset(c, units) for c in cuts] if (self.bucket is not None and mode in ("split", "event")) else None
+        self.cut_offset = self.cut_offsets[-1] if self.cut_offsets else None          # everything below it goes in the last exchange
+        # one pair of events per cut: the capture stream and the weight-gradient side stream
+        self._cut_events = {c: (torch.cuda.Event(external=True), torch.cuda.Event(external=True)) for c in cuts} if mode == "event" else {}
+        join_at_cut = os.environ.get("PB_B200_DDP_JOIN_AT_CUT", "0") == "1"
         scale = None
         if self.world > 1:
             scale = torch.tensor(1.0 / self.world, dtype=torch.float64, device=dev)      # sum over ranks -> mean
@@ -378,9 +406,14 @@ class GraphedPretrainStep:
                 ops.DEFER_WGRAD_JOIN = False
                 ops.join_side_streams()
 
-        def cut_hook():              # runs inside backward, when everything above the cut has been issued (ops.CutFn.backward)
-            ops.join_side_streams()              # ... including the weight gradients on the side stream
-            self._cut_event.record()
+        def cut_hook(tag):           # runs inside backward, when everything above cut `tag` has been issued (ops.CutFn.backward)
+            # ... on two streams: the weight gradients are on the side stream, which is NOT joined here (a join would hold the
+            # critical path until the side stream has drained); the exchange waits for one event per stream instead
+            if join_at_cut:
+                ops.join_side_streams()
+            ev_main, ev_side = self._cut_events[tag]
+            ev_main.record()
+            ev_side.record(ops._side_stream(dev))
 
         def one_graph_step():
             if self.bucket is not None:
@@ -388,7 +421,7 @@ class GraphedPretrainStep:
                 self.bucket.zero()
             if mode != "event":
                 return pretraining_step(model, sx, sy, sw, grad_scale=scale)
-            model._boundary_at, ops.CUT_HOOK = cut, cut_hook
+            model._boundary_at, ops.CUT_HOOK = tuple(cuts), cut_hook
             try:
                 return pretraining_step(model, sx, sy, sw, grad_scale=scale)
             finally:
@@ -415,6 +448,10 @@ class GraphedPretrainStep:
         _clear_grads(model)
         self.graph = torch.cuda.CUDAGraph()
         cap = {"stream": side} if hipri else {}
+        if distributed:
+            # NCCL's watchdog thread polls events while this thread captures; under the default (global) capture mode that
+            # poll raises "operation not permitted when stream is capturing" in the watchdog and aborts the process
+            cap["capture_error_mode"] = "thread_local"
         if self.split:
             with torch.cuda.graph(self.graph, **cap):
                 out = with_sink(stage_a)
@@ -428,7 +465,9 @@ class GraphedPretrainStep:
                 self.loss = with_sink(one_graph_step)
         if self.bucket is not None:         # the captured backward fixed the gradient addresses
             self.bucket.adopt()
-            self.launches_outside_graph = 2 if self.bucket.loose else 0
+            # kernels of this library launched per step outside the graph: the loose-tensor gather/scatter and the NVLS exchanges
+            n_ex = (1 + (len(self.cut_offsets) if (self.cut_offsets and not self.bucket.loose) else 0)) if self.bucket.exchange == "nvls" else 0
+            self.launches_outside_graph = (2 if self.bucket.loose else 0) + (n_ex if self.world > 1 else 0)
 
     def _dicts(self):
         s = self.static
@@ -505,7 +544,12 @@ class GraphedPretrainStep:
         if self.mode == "split":
             return bk.all_reduce(0, self.cut_offset, async_op=True)
         if self.mode == "event":
-            return bk.all_reduce(0, self.cut_offset, async_op=True, after_event=self._cut_event)
+            work, a = None, 0
+            for c, off in zip(self.cuts, self.cut_offsets):          # top-down; the exchanges queue on the communication stream
+                if off > a:
+                    work = bk.all_reduce(a, off, async_op=True, after_event=list(self._cut_events[c]))
+                    a = off
+            return work
         return None
 
     def _exchange_rest(self, work):
