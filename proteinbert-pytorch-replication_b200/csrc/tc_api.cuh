@@ -45,3 +45,4 @@ bool pb_tc_token_ok(int B, int L, int C, int V);
 int pb_tc_token_logits(const void* h, const void* wo_pad, float* logits32, int B, int L, int C, cudaStream_t st);
 int pb_tc_token_bwd(const void* dlogit_pad, const void* woT_pad, const void* h, void* dh, float* dWo_pad, int B, int L, int C,
                     void* ws, size_t ws_bytes, cudaStream_t st);
+

@@ -243,7 +243,11 @@ def test_conv_pair_against_torch_conv1d(pb):
 
 
 @pytest.mark.parametrize("dtype,two,shape", [("fp32", True, (5, 96, 32)), ("fp32", False, (3, 40, 64)),
-                                            ("bf16", True, (19, 256, 128)), ("bf16", False, (6, 128, 256))])
+                                            ("bf16", True, (19, 256, 128)), ("bf16", False, (6, 128, 256)),
+                                            # L*C = 65536: the one-launch cluster kernel, two vectors per thread; 150 samples =
+                                            # several rounds per cluster
+                                            ("bf16", True, (9, 512, 128)), ("bf16", False, (150, 512, 128)),
+                                            ("bf16", True, (64, 512, 128))])
 def test_fused_layernorm_gelu_backward(pb, dtype, two, shape):
     """pb_ln_joint_bwd_gelu against torch autograd (double) of u -> LayerNorm((L,C)) with z -> gelu side branches
     (modules.py:207-217 in reverse): du, dz, dgamma/dbeta, channel sums and the per-sample sums."""
