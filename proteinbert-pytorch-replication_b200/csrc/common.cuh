@@ -80,6 +80,22 @@ __device__ __forceinline__ float normal_cdf_fast(float x) {
     return x <= -4.f ? 0.f : c;
 }
 __device__ __forceinline__ float gelu_fast(float t) { return t * normal_cdf_fast(t); }
+// The same polynomial with a symmetric clamp (one instruction less: no select).  Below -4 the CDF stays at its value at -4
+// (3.2e-5) instead of 0, i.e. gelu(t) = 3.2e-5 t there (true value ~0): an absolute error of 3e-4 at t = -10.  For epilogues
+// whose result is ADDED to O(1) terms and rounded to bf16 (conv pair, local linear); the pooling sums keep gelu_fast.
+__device__ __forceinline__ float gelu_fast_sym(float t) {
+    const float xc = fminf(fmaxf(t, -4.f), 4.f), x2 = xc * xc;
+    float q = 8.525598940e-11f;
+    q = fmaf(q, x2, -7.295943751e-09f);
+    q = fmaf(q, x2, 2.791821216e-07f);
+    q = fmaf(q, x2, -6.397967703e-06f);
+    q = fmaf(q, x2, 9.969764565e-05f);
+    q = fmaf(q, x2, -1.137310887e-03f);
+    q = fmaf(q, x2, 9.885057402e-03f);
+    q = fmaf(q, x2, -6.641803427e-02f);
+    q = fmaf(q, x2, 3.989247710e-01f);
+    return t * fmaf(q, xc, 0.5f);
+}
 // gelu'(x) = Phi(x) + x phi(x) directly: gelu'(x) - 1/2 is odd, fitted by a degree-19 odd polynomial on |x| <= 4 (weighted
 // Chebyshev fit, |abs error| <= 4.4e-5 in fp32 Horner form), argument clamped outside (there gelu' is within 5e-4 of its
 // value at +-4: 1.0005 / -0.0005).  13 FP32 instructions, no MUFU; the previous form (Phi polynomial + ex2) took 19 and

@@ -228,26 +228,18 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
         // memory (64-byte swizzle) and one lane issues the bulk tensor store.
         uint8_t* stage = stage_base + (warp - 2) * (kFwd ? 3 * 2048 : 2 * 2048);
         const int lrow = l0 + hpos * 128;                               // first position of this warp's half
-        const bool odd = lane & 1;
-        const int cw = lane >> 1;                                       // 32-bit word of the pair (co & ~1, co | 1) in a 64-byte row
-        // transposing store: v[j] = this lane's channel at position j.  Neighbouring lanes exchange one value per position
-        // pair, so that even lanes write the word (co, co+1) of row j and odd lanes the word (co-1, co) of row j+1: the two
-        // half-warps hit the two bank halves, conflict-free.
+        // transposing store: v[j] = this lane's channel at position j goes to row j of a [32 positions x 32 channels] tile
+        // (64-byte rows, 64-byte swizzle: 16-byte chunk index ^ ((row >> 1) & 3)).  One 2-byte store per value: the 32 lanes of a
+        // warp write the 64 contiguous bytes of one row (two lanes per 32-bit word, one wavefront).  The swizzle term takes four
+        // values, so the four lane-dependent base offsets are formed once and every store address is base + constant.
+        // (The first version packed pairs through a shuffle to store 32-bit words: 16 stores instead of 32 per tile, but 48 more
+        // ALU instructions, and this epilogue is bound by instruction issue.)
+        uint32_t sw_off[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sw_off[k] = ((((uint32_t)lane >> 3) ^ (uint32_t)k) << 4) + ((uint32_t)lane & 7u) * 2u;
         auto stage_transposed = [&](uint8_t* tile, const bf16 (&v)[32]) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                const uint32_t mine = odd ? ((uint32_t)__bfloat16_as_ushort(v[j]) | ((uint32_t)__bfloat16_as_ushort(v[j + 2]) << 16))
-                                          : ((uint32_t)__bfloat16_as_ushort(v[j + 1]) | ((uint32_t)__bfloat16_as_ushort(v[j + 3]) << 16));
-                const uint32_t got = __shfl_xor_sync(0xffffffffu, mine, 1);
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int r = j + 2 * h + (odd ? 1 : 0);
-                    const uint32_t other = (got >> (16 * h)) & 0xffffu;
-                    const uint32_t own = odd ? __bfloat16_as_ushort(v[j + 2 * h + 1]) : __bfloat16_as_ushort(v[j + 2 * h]);
-                    const uint32_t word = odd ? (other | (own << 16)) : (own | (other << 16));
-                    *reinterpret_cast<uint32_t*>(tile + r * 64 + ((((cw >> 2) ^ ((r >> 1) & 3))) << 4) + (cw & 3) * 4) = word;
-                }
-            }
+            for (int j = 0; j < 32; ++j) *reinterpret_cast<bf16*>(tile + j * 64 + sw_off[(j >> 1) & 3]) = v[j];
         };
         float s_sum = 0.f, s_sq = 0.f;
         if (kFwd) {
@@ -260,6 +252,9 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
             // the per-position part of the swizzle is a compile-time constant
             const int xsw = (((co & 63) >> 3) ^ ((half * p.dil) & 7)) << 4;
             const uint8_t* xbase = smem + (size_t)(co >> 6) * a_buf + (co & 7) * 2;
+            uint32_t xoff[8];                       // swizzled chunk offset for positions j with (j & 7) == k
+#pragma unroll
+            for (int k = 0; k < 8; ++k) xoff[k] = (uint32_t)(xsw ^ (k << 4));
             mbar_wait(&tmem_full_bar[0], 0);
 #ifdef PB_CONV2_PROBE
             e1 = clock64();
@@ -274,10 +269,10 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 __align__(16) bf16 on[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const bf16 xv = *reinterpret_cast<const bf16*>(xrow + j * 128 + (xsw ^ ((j & 7) << 4)));
+                    const bf16 xv = *reinterpret_cast<const bf16*>(xrow + j * 128 + xoff[j & 7]);
                     const bf16 zn = __float2bfloat16_rn(an[j] + bnl);
                     on[j] = zn;
-                    an[j] = (__bfloat162float(xv) + gelu_fast(__bfloat162float(zn))) + gl;
+                    an[j] = (__bfloat162float(xv) + gelu_fast_sym(__bfloat162float(zn))) + gl;
                 }
                 tmem_st32(taddr + ch * 32, an);
                 if (ch >= 2) {                                           // the buffer's previous store must have read it
@@ -303,7 +298,7 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 for (int j = 0; j < 32; ++j) {
                     const bf16 zw = __float2bfloat16_rn(aw[j] + bwl);
                     ow[j] = zw;
-                    const bf16 ub = __float2bfloat16_rn(pa[j] + gelu_fast(__bfloat162float(zw)));
+                    const bf16 ub = __float2bfloat16_rn(pa[j] + gelu_fast_sym(__bfloat162float(zw)));
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;

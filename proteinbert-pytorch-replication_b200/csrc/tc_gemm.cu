@@ -146,7 +146,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) {
                     const bf16 z = __float2bfloat16_rn(acc[j] + __shfl_sync(0xffffffffu, bl, j));
                     oz[j] = z;
-                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_fast(__bfloat162float(z)));
+                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_fast_sym(__bfloat162float(z)));
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;
