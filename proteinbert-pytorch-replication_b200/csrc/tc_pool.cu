@@ -6,7 +6,9 @@
 // CTA sets up (barriers, TMEM allocation, TMA round trip, MMAs).  Here the whole weight matrix Wv^T [G x 128] stays in
 // shared memory (128 KB), the CTA walks (row tile, column tile) units, the MMA warp runs up to four units ahead into
 // four TMEM accumulators (all 512 columns) and four groups of four epilogue warps drain one accumulator each, so the
-// FP32 pipe never waits for a tile and every scheduler has four epilogue warps to pick from.
+// FP32 pipe never waits for a tile and every scheduler has four epilogue warps to pick from.  ncu (round 2,
+// profiles/r02_conv_pool_ncu.md): issue slots 62-68 % busy, FMA pipe 39-42 %, ALU pipe 26-39 %: instruction count per
+// element is what is left to cut.
 #include "tc_common.cuh"
 #include "tc_api.cuh"
 
@@ -16,7 +18,7 @@ constexpr int kTile = 128 * 64 * 2;                  // one 128-row x 64-k bf16 
 constexpr int kAStages = 2;                          // A ring: stage = one 128 x 128 activation tile (two k-chunks)
 constexpr int kMaxTilesN = 4;                        // resident weights: 4 column tiles x 2 k-chunks x 16 KB = 128 KB
 constexpr int kGroups = 4;                           // epilogue groups of four warps, one per TMEM accumulator
-constexpr int kStageArea = kGroups * 4 * 2048;       // POOL_DZ: one 2 KB staging tile per epilogue warp; POOL_FWD: column sums
+constexpr int kStageArea = kGroups * 4 * 2048;       // POOL_DZ: one 2 KB staging tile per epilogue warp
 constexpr int kSmemBytes = kMaxTilesN * 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;
 constexpr int kThreads = 64 + kGroups * 128;         // warp 0 TMA, warp 1 MMA + TMEM, then the epilogue groups
 
@@ -93,18 +95,24 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     const uint64_t db = make_smem_desc_sw128(smem_u32(b_res + (n * 2 + kc) * kTile), 16, 1024);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16(tmem_base + a * 128, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kc == 0 && k == 0) ? 0u : 1u);
+                        // POOL_FWD: weights as the A operand (M = 128 columns of Wv), positions as N -- accumulator lane = column
+                        // of Wv; POOL_DZ: positions as M (its output rows are positions)
+                        umma_bf16(tmem_base + a * 128, (EPI == POOL_FWD ? db : da) + (uint64_t)(k * 2),
+                                  (EPI == POOL_FWD ? da : db) + (uint64_t)(k * 2), idesc, (kc == 0 && k == 0) ? 0u : 1u);
                 }
                 umma_commit(&a_empty[s]);
                 umma_commit(&acc_full[a]);
             }
         }
     } else {
-        // ===== epilogue: groups of four warps; group g drains units g, g + kGroups, ... (always accumulator g);
-        //       TMEM lane quarter = warp % 4.  Four groups = four warps per scheduler: the epilogue is FP32-issue bound =====
+        // ===== epilogue: groups of four warps; group g drains units g, g + kGroups, ... (always accumulator g).
+        //       POOL_FWD accumulators are TRANSPOSED (TMEM lane = column of Wv, TMEM column = position of the row tile): the sum
+        //       over positions is then a sum inside each thread.  (With positions as lanes the column sums took a 32 x 32
+        //       shuffle transpose per chunk: 7.6 of the 24.5 instructions per element; 16.8 -> 14.4 us per launch.)
+        //       POOL_DZ keeps positions as lanes: its output rows are positions, so 16-byte row stores beat the 2-byte
+        //       transposing stores (17.3 against 17.8 us), even with one shuffle per element to broadcast dpool.
+        //       Four groups = four warps per scheduler: these epilogues are bound by instruction issue =====
         const int grp = (warp - 2) >> 2, q = warp & 3;
-        const int gt = ((warp - 2) & 3) * 32 + lane;                 // thread index inside the group
-        float* colsum = reinterpret_cast<float*>(stage_area) + grp * (4 * 128);      // POOL_FWD: [4 lane quarters][128 columns]
         uint8_t* stage = stage_area + (warp - 2) * 2048;                             // POOL_DZ: one staging tile per warp
         const int sw = (lane >> 1) & 3;
         int n_staged = 0;
@@ -117,6 +125,7 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             mbar_wait(&acc_full[a], (i >> 2) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + a * 128;
+            float colsum = 0.f;                                      // POOL_FWD: column n*128 + q*32 + lane over the tile's positions
 #pragma unroll 1
             for (int ch = 0; ch < 4; ++ch) {
                 float acc[32];
@@ -128,15 +137,15 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     if (lane == 0) mbar_arrive(&acc_empty[a]);
                 }
                 if (EPI == POOL_FWD) {
+                    float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) acc[j] = gelu_fast(acc[j]);
-                    colsum[q * 128 + c0 + lane] = warp_transpose_sum(acc, lane);
+                    for (int j = 0; j < 32; j += 2) { s0 += gelu_fast(acc[j]); s1 += gelu_fast(acc[j + 1]); }
+                    colsum += s0 + s1;
                 } else {
                     const float dl = __ldg(p.dpool + (size_t)b * p.G + n * 128 + c0 + lane);
                     __align__(16) bf16 od[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * gelu_grad_fast(acc[j]));
-                    uint8_t* sbuf = stage;
                     if (n_staged >= 1) {                             // the buffer's previous store must have read it
                         if (lane == 0) tma_store_wait_read<0>();
                         __syncwarp();
@@ -144,18 +153,13 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     ++n_staged;
 #pragma unroll
                     for (int v = 0; v < 4; ++v)
-                        *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
+                        *reinterpret_cast<uint4*>(stage + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];
                     fence_proxy_async();
                     __syncwarp();
-                    if (lane == 0) { tma_store_2d(&mapS, sbuf, n * 128 + c0, m * 128 + q * 32); tma_store_commit(); }
+                    if (lane == 0) { tma_store_2d(&mapS, stage, n * 128 + c0, m * 128 + q * 32); tma_store_commit(); }
                 }
             }
-            if (EPI == POOL_FWD) {
-                asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");       // this group's four warps
-                const float tot = colsum[gt] + colsum[128 + gt] + colsum[256 + gt] + colsum[384 + gt];
-                atomicAdd(&p.pool[(size_t)b * p.G + n * 128 + gt], tot);
-                asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");       // column sums may be overwritten
-            }
+            if (EPI == POOL_FWD) atomicAdd(&p.pool[(size_t)b * p.G + n * 128 + q * 32 + lane], colsum);
         }
         if (EPI == POOL_DZ && lane == 0) tma_store_wait<0>();
     }
