@@ -80,22 +80,6 @@ __device__ __forceinline__ float normal_cdf_fast(float x) {
     return x <= -4.f ? 0.f : c;
 }
 __device__ __forceinline__ float gelu_fast(float t) { return t * normal_cdf_fast(t); }
-// The same polynomial with a symmetric clamp (one instruction less: no select).  Below -4 the CDF stays at its value at -4
-// (3.2e-5) instead of 0, i.e. gelu(t) = 3.2e-5 t there (true value ~0): an absolute error of 3e-4 at t = -10.  For epilogues
-// whose result is ADDED to O(1) terms and rounded to bf16 (conv pair, local linear); the pooling sums keep gelu_fast.
-__device__ __forceinline__ float gelu_fast_sym(float t) {
-    const float xc = fminf(fmaxf(t, -4.f), 4.f), x2 = xc * xc;
-    float q = 8.525598940e-11f;
-    q = fmaf(q, x2, -7.295943751e-09f);
-    q = fmaf(q, x2, 2.791821216e-07f);
-    q = fmaf(q, x2, -6.397967703e-06f);
-    q = fmaf(q, x2, 9.969764565e-05f);
-    q = fmaf(q, x2, -1.137310887e-03f);
-    q = fmaf(q, x2, 9.885057402e-03f);
-    q = fmaf(q, x2, -6.641803427e-02f);
-    q = fmaf(q, x2, 3.989247710e-01f);
-    return t * fmaf(q, xc, 0.5f);
-}
 // gelu'(x) = Phi(x) + x phi(x) directly: gelu'(x) - 1/2 is odd, fitted by a degree-19 odd polynomial on |x| <= 4 (weighted
 // Chebyshev fit, |abs error| <= 4.4e-5 in fp32 Horner form), argument clamped outside (there gelu' is within 5e-4 of its
 // value at +-4: 1.0005 / -0.0005).  13 FP32 instructions, no MUFU; the previous form (Phi polynomial + ex2) took 19 and
@@ -113,6 +97,68 @@ __device__ __forceinline__ float gelu_grad_fast(float x) {
     q = fmaf(q, x2, -2.656380801e-01f);
     q = fmaf(q, x2, 7.978171689e-01f);
     return fmaf(q, xc, 0.5f);
+}
+
+// --- packed pairs: fma.rn.f32x2 / mul.rn.f32x2 (SASS FFMA2 / FMUL2) evaluate two independent fp32 operations per issued
+// instruction, each rounded exactly like the scalar one.  The FP32 pipe does the same work (a microbenchmark that saturates the
+// pipe gains nothing: profiles/r01_ffma2_probe.md), but the GELU epilogues of this library are bound by instruction ISSUE
+// (ncu: issue slots 62-68 % busy, FMA pipe ~40 %), and the polynomial is 10 of their ~15-25 instructions per element.
+typedef unsigned long long pb_f32x2;
+__device__ __forceinline__ pb_f32x2 pk2(float a, float b) { pb_f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void up2(pb_f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ pb_f32x2 fma2(pb_f32x2 a, pb_f32x2 b, pb_f32x2 c) {
+    pb_f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+__device__ __forceinline__ pb_f32x2 mul2(pb_f32x2 a, pb_f32x2 b) { pb_f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+#define PB_BOTH(c) pk2(c, c)
+// Phi(x) for two arguments, argument clamped to [-4, 4] on both sides.  The constant term is 0.5 - Phi_poly(-4) = 0.4999826f,
+// which makes the value at and below -4 EXACTLY 0 in fp32 (checked by evaluating the Horner form with single-rounding FMAs),
+// as normal_cdf_fast's select does, without the compare + select; everywhere else Phi moves by -1.74e-5 (the polynomial's own
+// error is 1.6e-5).  max |gelu error| 2.1e-4 (at x = 6; 1.3e-4 for gelu_fast), far inside bf16 rounding.
+__device__ __forceinline__ pb_f32x2 normal_cdf_fast2(float x0, float x1, pb_f32x2& xc) {
+    xc = pk2(fminf(fmaxf(x0, -4.f), 4.f), fminf(fmaxf(x1, -4.f), 4.f));
+    const pb_f32x2 x2 = mul2(xc, xc);
+    pb_f32x2 q = fma2(PB_BOTH(8.525598940e-11f), x2, PB_BOTH(-7.295943751e-09f));
+    q = fma2(q, x2, PB_BOTH(2.791821216e-07f));
+    q = fma2(q, x2, PB_BOTH(-6.397967703e-06f));
+    q = fma2(q, x2, PB_BOTH(9.969764565e-05f));
+    q = fma2(q, x2, PB_BOTH(-1.137310887e-03f));
+    q = fma2(q, x2, PB_BOTH(9.885057402e-03f));
+    q = fma2(q, x2, PB_BOTH(-6.641803427e-02f));
+    q = fma2(q, x2, PB_BOTH(3.989247710e-01f));
+    return fma2(q, xc, PB_BOTH(0.4999826f));
+}
+// y = gelu(t) for two values
+__device__ __forceinline__ void gelu_fast2(float t0, float t1, float& y0, float& y1) {
+    pb_f32x2 xc;
+    const pb_f32x2 c = normal_cdf_fast2(t0, t1, xc);
+    up2(mul2(pk2(t0, t1), c), y0, y1);
+}
+// y = gelu'(t) for two values (the polynomial of gelu_grad_fast)
+__device__ __forceinline__ void gelu_grad_fast2(float t0, float t1, float& y0, float& y1) {
+    const pb_f32x2 xc = pk2(fminf(fmaxf(t0, -4.f), 4.f), fminf(fmaxf(t1, -4.f), 4.f));
+    const pb_f32x2 x2 = mul2(xc, xc);
+    pb_f32x2 q = fma2(PB_BOTH(-5.066656453e-11f), x2, PB_BOTH(4.789404823e-09f));
+    q = fma2(q, x2, PB_BOTH(-2.026334901e-07f));
+    q = fma2(q, x2, PB_BOTH(5.107091856e-06f));
+    q = fma2(q, x2, PB_BOTH(-8.623214197e-05f));
+    q = fma2(q, x2, PB_BOTH(1.038562907e-03f));
+    q = fma2(q, x2, PB_BOTH(-9.190203826e-03f));
+    q = fma2(q, x2, PB_BOTH(5.937874753e-02f));
+    q = fma2(q, x2, PB_BOTH(-2.656380801e-01f));
+    q = fma2(q, x2, PB_BOTH(7.978171689e-01f));
+    up2(fma2(q, xc, PB_BOTH(0.5f)), y0, y1);
+}
+// in place over an array of even length
+template <int N>
+__device__ __forceinline__ void gelu_fast_n(float (&v)[N]) {
+#pragma unroll
+    for (int j = 0; j < N; j += 2) gelu_fast2(v[j], v[j + 1], v[j], v[j + 1]);
+}
+template <int N>
+__device__ __forceinline__ void gelu_grad_fast_n(float (&v)[N]) {
+#pragma unroll
+    for (int j = 0; j < N; j += 2) gelu_grad_fast2(v[j], v[j + 1], v[j], v[j + 1]);
 }
 
 __device__ __forceinline__ float sigmoid_f(float t) { return 1.0f / (1.0f + expf(-t)); }

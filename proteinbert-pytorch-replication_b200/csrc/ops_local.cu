@@ -298,6 +298,10 @@ template <> struct V8<float> {
         *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
     }
     static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_f(z); }
+    static __device__ __forceinline__ void gelu_grad8(float (&z)[8]) {          // in place
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[j] = gelu_grad_f(z[j]);
+    }
     struct Raw { float4 a, b; };
     static __device__ __forceinline__ Raw ld_raw(const float* p) { return Raw{*reinterpret_cast<const float4*>(p), *reinterpret_cast<const float4*>(p + 4)}; }
     static __device__ __forceinline__ void unpack(const Raw& r, float (&v)[8]) {
@@ -323,6 +327,7 @@ template <> struct V8<bf16> {
         *reinterpret_cast<uint4*>(p) = r;
     }
     static __device__ __forceinline__ float gelu_grad(float z) { return gelu_grad_fast(z); }
+    static __device__ __forceinline__ void gelu_grad8(float (&z)[8]) { gelu_grad_fast_n(z); }      // in place, packed pairs
     typedef uint4 Raw;
     static __device__ __forceinline__ Raw ld_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
     static __device__ __forceinline__ void unpack(const Raw& r, float (&v)[8]) {
@@ -459,15 +464,17 @@ __global__ void gelu_bwd_colsum_vec_kernel(const T* __restrict__ dy, const T* __
             float d[8], z[8], o[8];
             V8<T>::ld(dy + off, d);
             V8<T>::ld(z0 + off, z);
+            V8<T>::gelu_grad8(z);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { sy[j] += d[j]; o[j] = d[j] * V8<T>::gelu_grad(z[j]); }
+            for (int j = 0; j < 8; ++j) { sy[j] += d[j]; o[j] = d[j] * z[j]; }
             V8<T>::st(dz0 + off, o);
 #pragma unroll
             for (int j = 0; j < 8; ++j) s0[j] += o[j];
             if (z1) {
                 V8<T>::ld(z1 + off, z);
+                V8<T>::gelu_grad8(z);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) o[j] = d[j] * V8<T>::gelu_grad(z[j]);
+                for (int j = 0; j < 8; ++j) o[j] = d[j] * z[j];
                 V8<T>::st(dz1 + off, o);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) s1[j] += o[j];
@@ -566,14 +573,16 @@ ln_bwd_apply_gelu_kernel(const T* __restrict__ dy, const T* __restrict__ u, cons
                 ab[j] += d[j];
             }
             V8<T>::st(du + off, o);                  // o now holds the stored (rounded) values
+            V8<T>::gelu_grad8(za);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) e[j] = o[j] * V8<T>::gelu_grad(za[j]);
+            for (int j = 0; j < 8; ++j) e[j] = o[j] * za[j];
             V8<T>::st(dz0 + off, e);
 #pragma unroll
             for (int j = 0; j < 8; ++j) c0[j] += e[j];
             if (TWO) {
+                V8<T>::gelu_grad8(zb);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) e[j] = o[j] * V8<T>::gelu_grad(zb[j]);
+                for (int j = 0; j < 8; ++j) e[j] = o[j] * zb[j];
                 V8<T>::st(dz1 + off, e);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) c1[j] += e[j];

@@ -133,8 +133,10 @@ tc_conv_pair_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_cons
                     const bf16 zn = __float2bfloat16_rn(an[j] + __ldg(ep.bn + c));
                     const bf16 zw = __float2bfloat16_rn(aw[j] + __ldg(ep.bw + c));
                     on[j] = zn; ow[j] = zw;
-                    float v = __bfloat162float(xb[j]) + gelu_fast(__bfloat162float(zn));
-                    v += gelu_fast(__bfloat162float(zw));
+                    float gn, gw;
+                    gelu_fast2(__bfloat162float(zn), __bfloat162float(zw), gn, gw);
+                    float v = __bfloat162float(xb[j]) + gn;
+                    v += gw;
                     v += __ldg(ep.g2l + (size_t)b * kC + c);
                     const bf16 ub = __float2bfloat16_rn(v);
                     ou[j] = ub;

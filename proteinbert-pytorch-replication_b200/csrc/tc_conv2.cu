@@ -267,12 +267,18 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 uint8_t* sbuf = stage + (ch & 1) * 2048;
                 const uint8_t* xrow = xbase + (size_t)(half * p.dil + hpos * 128 + ch * 32) * 128;     // halo row of the chunk's first position
                 __align__(16) bf16 on[32];
+                float gz[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const bf16 zn = __float2bfloat16_rn(an[j] + bnl);
+                    on[j] = zn;
+                    gz[j] = __bfloat162float(zn);
+                }
+                gelu_fast_n(gz);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const bf16 xv = *reinterpret_cast<const bf16*>(xrow + j * 128 + xoff[j & 7]);
-                    const bf16 zn = __float2bfloat16_rn(an[j] + bnl);
-                    on[j] = zn;
-                    an[j] = (__bfloat162float(xv) + gelu_fast_sym(__bfloat162float(zn))) + gl;
+                    an[j] = (__bfloat162float(xv) + gz[j]) + gl;
                 }
                 tmem_st32(taddr + ch * 32, an);
                 if (ch >= 2) {                                           // the buffer's previous store must have read it
@@ -298,7 +304,12 @@ tc_conv2_kernel(const __grid_constant__ CUtensorMap mapA0m, const __grid_constan
                 for (int j = 0; j < 32; ++j) {
                     const bf16 zw = __float2bfloat16_rn(aw[j] + bwl);
                     ow[j] = zw;
-                    const bf16 ub = __float2bfloat16_rn(pa[j] + gelu_fast_sym(__bfloat162float(zw)));
+                    aw[j] = __bfloat162float(zw);
+                }
+                gelu_fast_n(aw);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const bf16 ub = __float2bfloat16_rn(pa[j] + aw[j]);
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;

@@ -146,7 +146,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 for (int j = 0; j < 32; ++j) {
                     const bf16 z = __float2bfloat16_rn(acc[j] + __shfl_sync(0xffffffffu, bl, j));
                     oz[j] = z;
-                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + gelu_fast_sym(__bfloat162float(z)));
+                    acc[j] = __bfloat162float(z);
+                }
+                gelu_fast_n(acc);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const bf16 ub = __float2bfloat16_rn(__bfloat162float(hb[j]) + acc[j]);
                     ou[j] = ub;
                     const float ur = __bfloat162float(ub);
                     s_sum += ur; s_sq += ur * ur;
@@ -158,16 +163,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     *reinterpret_cast<uint4*>(sbuf + 2048 + off) = reinterpret_cast<const uint4*>(ou)[v];
                 }
             } else if (EPI == EPI_POOL_FWD) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) acc[j] = gelu_fast(acc[j]);
+                gelu_fast_n(acc);
                 const float cs = warp_transpose_sum(acc, lane);
                 colsum[q * kBN + c0 + lane] = cs;
             } else if (EPI == EPI_POOL_DZ) {
                 const float dl = __ldg(ep.dpool + (size_t)b * ep.ldn + n0 + c0 + lane);
                 __align__(16) bf16 od[32];
+                gelu_grad_fast_n(acc);
 #pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * gelu_grad_fast(acc[j]));
+                for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * acc[j]);
 #pragma unroll
                 for (int v = 0; v < 4; ++v)
                     *reinterpret_cast<uint4*>(sbuf + lane * 64 + ((v ^ sw) * 16)) = reinterpret_cast<const uint4*>(od)[v];

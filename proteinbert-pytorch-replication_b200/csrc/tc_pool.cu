@@ -138,14 +138,16 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 }
                 if (EPI == POOL_FWD) {
                     float s0 = 0.f, s1 = 0.f;
+                    gelu_fast_n(acc);
 #pragma unroll
-                    for (int j = 0; j < 32; j += 2) { s0 += gelu_fast(acc[j]); s1 += gelu_fast(acc[j + 1]); }
+                    for (int j = 0; j < 32; j += 2) { s0 += acc[j]; s1 += acc[j + 1]; }
                     colsum += s0 + s1;
                 } else {
                     const float dl = __ldg(p.dpool + (size_t)b * p.G + n * 128 + c0 + lane);
                     __align__(16) bf16 od[32];
+                    gelu_grad_fast_n(acc);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * gelu_grad_fast(acc[j]));
+                    for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * acc[j]);
                     if (n_staged >= 1) {                             // the buffer's previous store must have read it
                         if (lane == 0) tma_store_wait_read<0>();
                         __syncwarp();
