@@ -19,7 +19,7 @@ constexpr int kAStages = 2;                          // A ring: stage = one 128 
 constexpr int kMaxTilesN = 4;                        // resident weights: 4 column tiles x 2 k-chunks x 16 KB = 128 KB
 constexpr int kGroups = 4;                           // epilogue groups of four warps, one per TMEM accumulator
 constexpr int kStageArea = kGroups * 4 * 2048;       // POOL_DZ: one 2 KB staging tile per epilogue warp
-constexpr int kSmemBytes = kMaxTilesN * 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;
+constexpr int kSmemBytes = kMaxTilesN * 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;   // barriers + TMEM slot in the last KB
 constexpr int kThreads = 64 + kGroups * 128;         // warp 0 TMA, warp 1 MMA + TMEM, then the epilogue groups
 
 enum { POOL_FWD = 0, POOL_DZ = 1 };
@@ -40,8 +40,8 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     uint8_t* b_res = smem;                                           // [tiles_n][2][16 KB]
     uint8_t* a_ring = smem + kMaxTilesN * 2 * kTile;                 // [kAStages][2][16 KB]
     uint8_t* stage_area = a_ring + kAStages * 2 * kTile;
-    uint64_t* b_full = (uint64_t*)(stage_area + kStageArea);
-    uint64_t* a_full = b_full + 1;
+    uint64_t* b_full = (uint64_t*)(stage_area + kStageArea);         // [kMaxTilesN]: one per resident column tile of the weights
+    uint64_t* a_full = b_full + kMaxTilesN;
     uint64_t* a_empty = a_full + kAStages;
     uint64_t* acc_full = a_empty + kAStages;                         // [4]
     uint64_t* acc_empty = acc_full + 4;                              // [4]
@@ -53,7 +53,7 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA); tma_prefetch_desc(&mapB);
-        mbar_init(b_full, 1);
+        for (int n = 0; n < kMaxTilesN; ++n) mbar_init(&b_full[n], 1);
         for (int s = 0; s < kAStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
         for (int a = 0; a < 4; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
         fence_barrier_init();
@@ -67,25 +67,36 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     if (warp == 0) {
         if (lane == 0 && n_mine > 0) {
-            mbar_expect_tx(b_full, p.tiles_n * 2 * kTile);
-            for (int n = 0; n < p.tiles_n; ++n)
-                for (int kc = 0; kc < 2; ++kc) tma_load_2d(b_res + (n * 2 + kc) * kTile, &mapB, b_full, kc * 64, n * 128);
+            // the weights arrive one column tile at a time, each behind its own barrier and in the order this CTA's units need
+            // them (a unit's column tile is u % tiles_n), with the first activation tile in between: the first MMA starts after
+            // 64 KB instead of after the whole 128 KB + 32 KB
+            uint32_t b_req = 0;                                       // bit n: column tile n has been requested
+            auto request_b = [&](int n) {
+                if (b_req & (1u << n)) return;
+                b_req |= 1u << n;
+                mbar_expect_tx(&b_full[n], 2 * kTile);
+                for (int kc = 0; kc < 2; ++kc) tma_load_2d(b_res + (n * 2 + kc) * kTile, &mapB, &b_full[n], kc * 64, n * 128);
+            };
             for (int i = 0; i < n_mine; ++i) {
                 const int s = i % kAStages;
-                const int m = ((int)blockIdx.x + i * (int)gridDim.x) / p.tiles_n;
+                const int u = (int)blockIdx.x + i * (int)gridDim.x;
+                const int m = u / p.tiles_n;
+                request_b(u % p.tiles_n);
                 mbar_wait(&a_empty[s], ((i / kAStages) & 1) ^ 1);
                 mbar_expect_tx(&a_full[s], 2 * kTile);
                 tma_load_2d(a_ring + (s * 2) * kTile, &mapA, &a_full[s], 0, m * 128);
                 tma_load_2d(a_ring + (s * 2 + 1) * kTile, &mapA, &a_full[s], 64, m * 128);
+                if (i == 0)                                           // the rest of the weights right behind the first unit's operands
+                    for (int n = 0; n < p.tiles_n; ++n) request_b(n);
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && n_mine > 0) {
             constexpr uint32_t idesc = make_idesc_bf16(128, 128, 0, 0);
-            mbar_wait(b_full, 0);
             for (int i = 0; i < n_mine; ++i) {
                 const int s = i % kAStages, a = i & 3;
                 const int n = ((int)blockIdx.x + i * (int)gridDim.x) % p.tiles_n;
+                mbar_wait(&b_full[n], 0);                            // completes once; later waits on the same tile return at once
                 mbar_wait(&acc_empty[a], ((i >> 2) & 1) ^ 1);        // the epilogue has drained this accumulator
                 mbar_wait(&a_full[s], (i / kAStages) & 1);
                 tc_fence_after();
