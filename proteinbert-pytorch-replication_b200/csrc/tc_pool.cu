@@ -15,18 +15,19 @@
 namespace {
 
 constexpr int kTile = 128 * 64 * 2;                  // one 128-row x 64-k bf16 tile: 16 KB
-constexpr int kAStages = 2;                          // A ring: stage = one 128 x 128 activation tile (two k-chunks)
-constexpr int kMaxTilesN = 4;                        // resident weights: 4 column tiles x 2 k-chunks x 16 KB = 128 KB
+constexpr int kAStages = 3;                          // A ring: stage = one 128 x 128 activation tile (two k-chunks)
+constexpr int kMaxTilesN = 8;                        // column tiles of the weights (G <= 1024); a CTA keeps ONE of them resident (32 KB)
 constexpr int kGroups = 4;                           // epilogue groups of four warps, one per TMEM accumulator
-constexpr int kStageArea = kGroups * 4 * 2048;       // POOL_DZ: one 2 KB staging tile per epilogue warp
-constexpr int kSmemBytes = kMaxTilesN * 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;   // barriers + TMEM slot in the last KB
+constexpr int kStageArea = kGroups * 4 * 2 * 2048;   // POOL_DZ: two 2 KB staging tiles per epilogue warp
+constexpr int kSmemBytes = 2 * kTile + kAStages * 2 * kTile + kStageArea + 1024 + 1024;   // barriers + TMEM slot in the last KB
 constexpr int kThreads = 64 + kGroups * 128;         // warp 0 TMA, warp 1 MMA + TMEM, then the epilogue groups
 
 enum { POOL_FWD = 0, POOL_DZ = 1 };
 
 struct PoolParams {
     int L, G;                       // rows per sample, total columns
-    int tiles_n, n_units;           // units = row tiles x column tiles, walked column-tile fastest
+    int tiles_n, row_tiles;         // units = row tiles x column tiles; CTA c owns column tile c % tiles_n and walks row tiles
+                                    // c / tiles_n, c / tiles_n + gridDim.x / tiles_n, ... (gridDim.x is a multiple of tiles_n)
     float* pool;                    // POOL_FWD [B, G] (accumulated)
     const float* dpool;             // POOL_DZ  [B, G]
 };
@@ -37,23 +38,26 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                const __grid_constant__ CUtensorMap mapS, PoolParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* b_res = smem;                                           // [tiles_n][2][16 KB]
-    uint8_t* a_ring = smem + kMaxTilesN * 2 * kTile;                 // [kAStages][2][16 KB]
+    uint8_t* b_res = smem;                                           // [2][16 KB]: this CTA's column tile of the weights
+    uint8_t* a_ring = smem + 2 * kTile;                              // [kAStages][2][16 KB]
     uint8_t* stage_area = a_ring + kAStages * 2 * kTile;
-    uint64_t* b_full = (uint64_t*)(stage_area + kStageArea);         // [kMaxTilesN]: one per resident column tile of the weights
-    uint64_t* a_full = b_full + kMaxTilesN;
+    uint64_t* b_full = (uint64_t*)(stage_area + kStageArea);
+    uint64_t* a_full = b_full + 1;
     uint64_t* a_empty = a_full + kAStages;
     uint64_t* acc_full = a_empty + kAStages;                         // [4]
     uint64_t* acc_empty = acc_full + 4;                              // [4]
     uint32_t* tmem_slot = (uint32_t*)(acc_empty + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // this CTA's units: u = blockIdx.x, blockIdx.x + gridDim.x, ...
-    const int n_mine = p.n_units > (int)blockIdx.x ? (p.n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    // this CTA's units: column tile n_cta, row tiles m0, m0 + m_step, ...  (One resident column tile instead of all of them:
+    // 32 KB instead of 128 KB to wait for before the first MMA, and room for a third activation stage and double-buffered
+    // output staging.  The activation tile is fetched per unit either way.)
+    const int n_cta = (int)blockIdx.x % p.tiles_n, m0 = (int)blockIdx.x / p.tiles_n, m_step = (int)gridDim.x / p.tiles_n;
+    const int n_mine = p.row_tiles > m0 ? (p.row_tiles - m0 + m_step - 1) / m_step : 0;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA); tma_prefetch_desc(&mapB);
-        for (int n = 0; n < kMaxTilesN; ++n) mbar_init(&b_full[n], 1);
+        mbar_init(b_full, 1);
         for (int s = 0; s < kAStages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
         for (int a = 0; a < 4; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
         fence_barrier_init();
@@ -67,43 +71,30 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     if (warp == 0) {
         if (lane == 0 && n_mine > 0) {
-            // the weights arrive one column tile at a time, each behind its own barrier and in the order this CTA's units need
-            // them (a unit's column tile is u % tiles_n), with the first activation tile in between: the first MMA starts after
-            // 64 KB instead of after the whole 128 KB + 32 KB
-            uint32_t b_req = 0;                                       // bit n: column tile n has been requested
-            auto request_b = [&](int n) {
-                if (b_req & (1u << n)) return;
-                b_req |= 1u << n;
-                mbar_expect_tx(&b_full[n], 2 * kTile);
-                for (int kc = 0; kc < 2; ++kc) tma_load_2d(b_res + (n * 2 + kc) * kTile, &mapB, &b_full[n], kc * 64, n * 128);
-            };
+            mbar_expect_tx(b_full, 2 * kTile);
+            for (int kc = 0; kc < 2; ++kc) tma_load_2d(b_res + kc * kTile, &mapB, b_full, kc * 64, n_cta * 128);
             for (int i = 0; i < n_mine; ++i) {
                 const int s = i % kAStages;
-                const int u = (int)blockIdx.x + i * (int)gridDim.x;
-                const int m = u / p.tiles_n;
-                request_b(u % p.tiles_n);
+                const int m = m0 + i * m_step;
                 mbar_wait(&a_empty[s], ((i / kAStages) & 1) ^ 1);
                 mbar_expect_tx(&a_full[s], 2 * kTile);
                 tma_load_2d(a_ring + (s * 2) * kTile, &mapA, &a_full[s], 0, m * 128);
                 tma_load_2d(a_ring + (s * 2 + 1) * kTile, &mapA, &a_full[s], 64, m * 128);
-                if (i == 0)                                           // the rest of the weights right behind the first unit's operands
-                    for (int n = 0; n < p.tiles_n; ++n) request_b(n);
             }
         }
     } else if (warp == 1) {
         if (lane == 0 && n_mine > 0) {
             constexpr uint32_t idesc = make_idesc_bf16(128, 128, 0, 0);
+            mbar_wait(b_full, 0);
             for (int i = 0; i < n_mine; ++i) {
                 const int s = i % kAStages, a = i & 3;
-                const int n = ((int)blockIdx.x + i * (int)gridDim.x) % p.tiles_n;
-                mbar_wait(&b_full[n], 0);                            // completes once; later waits on the same tile return at once
                 mbar_wait(&acc_empty[a], ((i >> 2) & 1) ^ 1);        // the epilogue has drained this accumulator
                 mbar_wait(&a_full[s], (i / kAStages) & 1);
                 tc_fence_after();
 #pragma unroll
                 for (int kc = 0; kc < 2; ++kc) {
                     const uint64_t da = make_smem_desc_sw128(smem_u32(a_ring + (s * 2 + kc) * kTile), 16, 1024);
-                    const uint64_t db = make_smem_desc_sw128(smem_u32(b_res + (n * 2 + kc) * kTile), 16, 1024);
+                    const uint64_t db = make_smem_desc_sw128(smem_u32(b_res + kc * kTile), 16, 1024);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
                         // POOL_FWD: weights as the A operand (M = 128 columns of Wv), positions as N -- accumulator lane = column
@@ -124,14 +115,13 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         //       transposing stores (17.3 against 17.8 us), even with one shuffle per element to broadcast dpool.
         //       Four groups = four warps per scheduler: these epilogues are bound by instruction issue =====
         const int grp = (warp - 2) >> 2, q = warp & 3;
-        uint8_t* stage = stage_area + (warp - 2) * 2048;                             // POOL_DZ: one staging tile per warp
+        uint8_t* stage0 = stage_area + (warp - 2) * 2 * 2048;                        // POOL_DZ: two staging tiles per warp
         const int sw = (lane >> 1) & 3;
         int n_staged = 0;
 #pragma unroll 1
         for (int i = grp; i < n_mine; i += kGroups) {
             const int a = i & 3;
-            const int u = (int)blockIdx.x + i * (int)gridDim.x;
-            const int m = u / p.tiles_n, n = u % p.tiles_n;
+            const int m = m0 + i * m_step, n = n_cta;
             const int b = (m * 128) / p.L;                           // tiles never straddle samples (L % 128 == 0)
             mbar_wait(&acc_full[a], (i >> 2) & 1);
             tc_fence_after();
@@ -159,8 +149,9 @@ tc_pool_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     gelu_grad_fast_n(acc);
 #pragma unroll
                     for (int j = 0; j < 32; ++j) od[j] = __float2bfloat16_rn(__shfl_sync(0xffffffffu, dl, j) * acc[j]);
-                    if (n_staged >= 1) {                             // the buffer's previous store must have read it
-                        if (lane == 0) tma_store_wait_read<0>();
+                    uint8_t* stage = stage0 + (n_staged & 1) * 2048;
+                    if (n_staged >= 2) {                             // the buffer's previous store (two stores ago) must have read it
+                        if (lane == 0) tma_store_wait_read<1>();
                         __syncwarp();
                     }
                     ++n_staged;
@@ -208,7 +199,8 @@ int launch_pool(const void* h, const void* wvT, void* dzv, PoolParams p, int M, 
         PB_CUDA(cudaFuncSetAttribute(tc_pool_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
         attr_set = true;
     }
-    const int grid = p.n_units < 148 ? p.n_units : 148;
+    int grid = (148 / p.tiles_n) * p.tiles_n;                        // a multiple of tiles_n: every CTA owns one column tile
+    if (grid > p.row_tiles * p.tiles_n) grid = p.row_tiles * p.tiles_n;
     PB_CUDA(pb_launch_pdl(tc_pool_kernel<EPI>, dim3(grid), dim3(kThreads), kSmemBytes, st, mA, mB, mS, p));
     pb_count_launch(1);
     return pb_check_launch(what);
@@ -222,12 +214,12 @@ bool pb_tc_pool_ok(int B, int L, int C, int G) {
 
 int pb_tc_pool_fwd(const void* h, const void* wvT, float* pool, int B, int L, int G, cudaStream_t st) {
     PoolParams p{};
-    p.L = L; p.G = G; p.tiles_n = G / 128; p.n_units = (B * L / 128) * p.tiles_n; p.pool = pool;
+    p.L = L; p.G = G; p.tiles_n = G / 128; p.row_tiles = B * L / 128; p.pool = pool;
     return launch_pool<POOL_FWD>(h, wvT, nullptr, p, B * L, st, "tc_pool_fwd");
 }
 
 int pb_tc_pool_dz(const void* h, const void* wvT, const float* dpool, void* dzv, int B, int L, int G, cudaStream_t st) {
     PoolParams p{};
-    p.L = L; p.G = G; p.tiles_n = G / 128; p.n_units = (B * L / 128) * p.tiles_n; p.dpool = dpool;
+    p.L = L; p.G = G; p.tiles_n = G / 128; p.row_tiles = B * L / 128; p.dpool = dpool;
     return launch_pool<POOL_DZ>(h, wvT, dzv, p, B * L, st, "tc_pool_dz");
 }
