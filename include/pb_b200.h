@@ -144,7 +144,9 @@ int pb_linear_bwd(const float* dY, const float* ZY, const float* X, const float*
  * annotation layers, modules.py:248-251 and 290-297: M = batch rows <= 128).  Same arguments and results; operands are
  * read as fp32, rounded to bf16 on the way into shared memory and accumulated in fp32 (the arithmetic of
  * precision = "bf16"; the fp32 entry points above keep full fp32).  ws is required: pb_linear_tc_workspace(M, N, K)
- * bytes cover both directions.  pb_linear_tc_ok says whether the shape is taken.                                       */
+ * bytes cover both directions.  pb_linear_tc_ok says whether the shape is taken.  pb_linear_bwd_tc may be split in two calls
+ * so that the weight gradient runs on another stream: first with dW = NULL (forms dZ_buf, db and dX), then with dY = NULL
+ * and dX = NULL (dZ_buf is read as it stands; forms dW only).                                                             */
 int pb_linear_tc_ok(int M, int N, int K);
 size_t pb_linear_tc_workspace(int M, int N, int K);
 int pb_linear_fwd_tc(const float* X, const float* W, const float* bias, float* Z, float* Y, int M, int N, int K,
@@ -321,7 +323,8 @@ int pb_token_head_bwd(const float* dP, const float* p_local, const void* h_act, 
 /* Tensor-core variant of the token head (PB_BF16 activations; C, L multiples of 128; V <= 32).  wo_pad / woT_pad are
  * the output weight zero-padded to 128 vocabulary rows, [128, C] and its transpose [C, 128], type wt.  logits_ws
  * [B*L, 32] float and dlogit_ws [B*L, 128] wt are scratch; dWo_pad [128, C] float receives dWo in its first V rows;
- * dbo is ACCUMULATED (zero on entry); ws as pb_workspace_bytes("wgrad", 0, 0, 0). */
+ * dbo is ACCUMULATED (zero on entry); ws as pb_workspace_bytes("wgrad", 0, 0, 0).  pb_token_head_bwd_tc may be split in two
+ * calls: first with dWo_pad = NULL (dlogit_ws, dbo, dh), then with dP = NULL and dh_act = NULL (reads dlogit_ws; dWo_pad). */
 int pb_token_head_tc_ok(int B, int L, int C, int V);
 int pb_token_head_fwd_tc(const void* h_act, const void* wo_pad, const float* bo, float* logits_ws, float* p_local, int B,
                          int L, int C, int V, void* stream);

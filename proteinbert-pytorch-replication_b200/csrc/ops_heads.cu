@@ -503,10 +503,12 @@ int pb_token_head_bwd_tc(const float* dP, const float* p_local, const void* h, c
                          size_t ws_bytes, void* stream) {
     PB_REQUIRE(pb_tc_token_ok(B, L, C, V), PB_ERR_UNSUPPORTED, "token_head_bwd_tc: shape not covered");
     cudaStream_t st = (cudaStream_t)stream;
-    token_dlogit_kernel<<<L, 32 * kTokBL, 0, st>>>(dP, p_local, grad_scale, (bf16*)dlogit_ws, dbo, B, L, V);
-    pb_count_launch(1);
-    int rc = pb_check_launch("pb_token_head_bwd_tc(dlogit)");
-    if (rc) return rc;
+    if (dP != nullptr) {       // dP == NULL: dlogit_ws already holds the logit gradients of an earlier call (and dbo is done)
+        token_dlogit_kernel<<<L, 32 * kTokBL, 0, st>>>(dP, p_local, grad_scale, (bf16*)dlogit_ws, dbo, B, L, V);
+        pb_count_launch(1);
+        int rc = pb_check_launch("pb_token_head_bwd_tc(dlogit)");
+        if (rc) return rc;
+    }
     return pb_tc_token_bwd(dlogit_ws, woT_pad, h, dh, dWo_pad, B, L, C, ws, ws_bytes, st);
 }
 

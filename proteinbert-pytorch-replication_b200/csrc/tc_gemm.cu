@@ -545,9 +545,13 @@ int pb_tc_token_logits(const void* h, const void* wo_pad, float* logits32, int B
 int pb_tc_token_bwd(const void* dlogit_pad, const void* woT_pad, const void* h, void* dh, float* dWo_pad, int B, int L, int C,
                     void* ws, size_t ws_bytes, cudaStream_t st) {
     // dh = dlogit Wo (K = 128 padded vocabulary)  ;  dWo_pad[v, c] = sum_rows dlogit[row, v] h[row, c]
-    GemmEpi ep{};
-    ep.ldn = C; ep.L = L; ep.out0 = (bf16*)dh;
-    int rc = launch_gemm<EPI_STORE>(dlogit_pad, woT_pad, ep, B * L, C, 128, st, "tc_token_bwd(dh)");
-    if (rc) return rc;
+    // either half may be skipped (NULL output): callers put the weight gradient on a second stream
+    if (dh != nullptr) {
+        GemmEpi ep{};
+        ep.ldn = C; ep.L = L; ep.out0 = (bf16*)dh;
+        int rc = launch_gemm<EPI_STORE>(dlogit_pad, woT_pad, ep, B * L, C, 128, st, "tc_token_bwd(dh)");
+        if (rc) return rc;
+    }
+    if (dWo_pad == nullptr) return PB_OK;
     return launch_wgrad(dlogit_pad, nullptr, h, dWo_pad, nullptr, C, 1, 0, B, L, 128, C, 1, 1, 1, ws, ws_bytes, st, "tc_token_bwd(dWo)");
 }

@@ -308,10 +308,12 @@ int pb_linear_bwd_tc(const float* dY, const float* ZY, const float* X, const flo
                      int M, int N, int K, int act, int accumulate_dx, void* ws, size_t ws_bytes, void* stream) {
     PB_REQUIRE(pb_linear_tc_ok(M, N, K), PB_ERR_SHAPE, "linear_bwd_tc: needs 1 <= M <= 128 (got M=%d N=%d K=%d) and the tensor-core engine on", M, N, K);
     PB_REQUIRE(dZ_buf != nullptr, PB_ERR_WORKSPACE, "linear_bwd_tc: dZ_buf is required");
-    PB_REQUIRE(act == PB_ACT_NONE || ZY != nullptr, PB_ERR_SHAPE, "linear_bwd_tc: ZY required for act=%d", act);
+    PB_REQUIRE(dY == nullptr || act == PB_ACT_NONE || ZY != nullptr, PB_ERR_SHAPE, "linear_bwd_tc: ZY required for act=%d", act);
     cudaStream_t st = (cudaStream_t)stream;
-    PB_CUDA(pb_launch_pdl(skinny_dz_kernel, dim3((N + 31) / 32), dim3(32, 8), 0, st, dY, ZY, dZ_buf, db, M, N, act));
-    pb_count_launch(1);
+    if (dY != nullptr) {       // dY == NULL: dZ_buf already holds dZ from an earlier call (and db is done)
+        PB_CUDA(pb_launch_pdl(skinny_dz_kernel, dim3((N + 31) / 32), dim3(32, 8), 0, st, dY, ZY, dZ_buf, db, M, N, act));
+        pb_count_launch(1);
+    }
     int rc;
     if (dX) {       // dX[m, k] = sum_n dZ[m, n] W[n, k]
         const int tiles_k = (K + 127) / 128;

@@ -272,7 +272,7 @@ class ProteinBERT(nn.Module):
 
     def __getstate__(self):
         st = dict(self.__dict__)
-        for k in ("_stage_table", "_boundary", "_boundary_at"):
+        for k in ("_stage_table", "_boundary", "_boundary_at", "_wo_pads"):
             st.pop(k, None)
         return st
 
@@ -311,12 +311,27 @@ class ProteinBERT(nn.Module):
         """{"local": int64 [B,L], "global": float [B,A]} -> (token probs [B,L,V], annotation probs [B,A])."""
         dt = _dt(self.precision)
         x_local, x_global = x["local"], x["global"]
+        ops._need_cuda(x_local, x_global, self.local_embedding.weight)      # no CPU path: refuse before touching any stream
+        blocks = list(self.proteinBERT_blocks)
+        lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
+        # every block's conv packs / W2 / Wv -- and the token head's padded output matrix -- in ONE launch.  (Issued on the side
+        # stream beside the embedding and the annotation-input layer it measured 7 us SLOWER per step: fork + join cost more
+        # than the 21 us kernel hides.)
+        extra, wo_pads = (), None
+        Bsz0, Lseq0 = x_local.shape
+        if dt == ops.BF16 and bool(ops.lib().pb_token_head_tc_ok(Bsz0, Lseq0, lo.weight.shape[1], lo.weight.shape[0])) and lo.weight.shape[1] == 128:
+            pads = getattr(self, "_wo_pads", None)
+            if pads is None or pads.device != lo.weight.device:
+                pads = torch.zeros((2, 128, 128), dtype=torch.bfloat16, device=lo.weight.device)     # rows >= V stay zero
+                self._wo_pads = pads
+            V_ = lo.weight.shape[0]
+            extra = ((lo.weight, pads[0].data_ptr(), pads[1].data_ptr(), 0, V_, 128, 0, 128, 128),)
+            wo_pads = (pads[0], pads[1])
+        ops.stage_blocks(self, blocks, dt, extra)
         h = ops.EmbeddingFn.apply(x_local, self.local_embedding.weight, dt)                     # modules.py:300
         gin = self.global_linear_layer[0]
         tc = dt == ops.BF16           # annotation layers: tensor cores in bf16 precision, fp32 SIMT otherwise
         g = ops.linear_act(x_global.float(), gin.weight, gin.bias, ACT_GELU, tc)                # :301
-        blocks = list(self.proteinBERT_blocks)
-        ops.stage_blocks(self, blocks, dt)                   # every block's conv packs / W2 / Wv in one launch
         # training.GraphedPretrainStep: where backward is split in two (an int: the boundary tensors are kept in _boundary) or
         # marked for the gradient exchange (a collection of block indices: ops.CUT_HOOK fires at each in backward)
         cut = getattr(self, "_boundary_at", None)
@@ -349,7 +364,6 @@ class ProteinBERT(nn.Module):
                         self._boundary = (h, g)
                 blk._prestaged = dt
                 h, g = blk.forward_channels_last(h, g, arena)
-        lo, go = self.pretraining_local_output[0], self.pretraining_global_output[0]
-        p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias)                                  # :277-284
+        p_local = ops.TokenHeadFn.apply(h, lo.weight, lo.bias, wo_pads)                         # :277-284
         p_global = ops.linear_act(g, go.weight, go.bias, ACT_SIGMOID, tc)                       # :286-293
         return p_local, p_global

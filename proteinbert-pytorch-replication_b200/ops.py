@@ -163,9 +163,10 @@ _STAGE_DTYPE = [("src", "<u8"), ("dst0", "<u8"), ("dst1", "<u8"), ("kind", "<i4"
                 ("d2", "<i4"), ("ld0", "<i4"), ("ld1", "<i4"), ("reserved", "<i4"), ("pad", "<i4")]   # 56 B = sizeof(pb_stage_desc)
 
 
-def stage_blocks(owner, blocks, dt):
+def stage_blocks(owner, blocks, dt, extra_jobs=()):
     """Stage the local-track weights of `blocks` with one kernel launch.  The device job table is cached on
-    `owner` and rebuilt only when a parameter's storage or the precision changes."""
+    `owner` and rebuilt only when a parameter's storage or the precision changes.  extra_jobs: more rows of the same
+    table, (src, dst0_ptr, dst1_ptr, kind, d0, d1, d2, ld0, ld1) -- the token head's padded output matrix."""
     import numpy as np
     staged = []
     for blk in blocks:
@@ -174,7 +175,7 @@ def stage_blocks(owner, blocks, dt):
             sw = StagedBlockWeights(blk, dt)
             blk._staged = sw
         staged.append(sw)
-    key = tuple(sw.key() for sw in staged)
+    key = tuple(sw.key() for sw in staged) + tuple((j[0].data_ptr(),) + tuple(j[1:]) for j in extra_jobs)
     cache = getattr(owner, "_stage_table", None)
     if cache is None or cache[0] != key:
         rows = []
@@ -183,6 +184,10 @@ def stage_blocks(owner, blocks, dt):
                 if not src.is_contiguous():
                     raise _lib.PBError("parameters must be contiguous")
                 rows.append((src.data_ptr(), d0p, d1p, kind, a, b, c, ld0, ld1, 0, 0))
+        for (src, d0p, d1p, kind, a, b, c, ld0, ld1) in extra_jobs:
+            if not src.is_contiguous():
+                raise _lib.PBError("parameters must be contiguous")
+            rows.append((src.data_ptr(), d0p, d1p, kind, a, b, c, ld0, ld1, 0, 0))
         arr = np.array(rows, dtype=_STAGE_DTYPE)
         table = torch.from_numpy(arr.view(np.uint8).copy()).to(staged[0].wv.device)
         cache = (key, table, len(rows))
@@ -215,6 +220,8 @@ class EmbeddingFn(torch.autograd.Function):
         V, C, dt = ctx.shape
         dout = dout.contiguous()
         dtable = _gout(ctx.key, (V, C), dout.device)
+        # (on the side stream, beside the last global-track unit, this kernel -- 296 CTAs with 100 KB of shared memory each --
+        # kept the unit's clusters off the SMs: 28 us slower per step)
         _call("pb_embedding_bwd", _p(tok), _p(dout), _p(dtable), tok.numel(), C, V, dt, _st())
         return None, dtable, None
 
@@ -260,8 +267,15 @@ class LinearActFn(torch.autograd.Function):
         db = _gout(ctx.keys[1], (N,), dy.device)
         if ctx.tc:
             ws = _workspace(lib().pb_linear_tc_workspace(M, N, K), dy.device)
-            _call("pb_linear_bwd_tc", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
-                                         _p(ws), ws.numel(), _st())
+            if WGRAD_STREAM and HEAD_WGRAD_SIDE and need_dx and need_dw:
+                # dZ, db and dX on the critical path; dW = dZ^T X (reads dZ as it stands) beside it
+                _call("pb_linear_bwd_tc", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), None, _p(db), M, N, K, ctx.act, 0,
+                                             _p(ws), ws.numel(), _st())
+                run_on_side(dy.device, lambda: _call("pb_linear_bwd_tc", None, None, _p(x), _p(W), _p(dz), None, _p(dW), None, M, N, K,
+                                                     ctx.act, 0, _p(ws), ws.numel(), _st()), x, dz, dW)
+            else:
+                _call("pb_linear_bwd_tc", _p(dy), _p(zy), _p(x), _p(W), _p(dz), _p(dx), _p(dW), _p(db), M, N, K, ctx.act, 0,
+                                             _p(ws), ws.numel(), _st())
         else:
             nbytes = lib().pb_workspace_bytes(b"linear_bwd", M, N, K)
             ws = _workspace(nbytes, dy.device)
@@ -597,6 +611,7 @@ def global_fused_ok(B, G, C) -> bool:
 import os as _os
 
 WGRAD_STREAM = _os.environ.get("PB_B200_WGRAD_STREAM", "1") != "0"
+HEAD_WGRAD_SIDE = _os.environ.get("PB_B200_HEAD_WGRAD_SIDE", "1") == "1"      # dW of the GO-output layer and of the token head
 CONV_WGRAD_EARLY = _os.environ.get("PB_B200_CONV_WGRAD_EARLY", "1") == "1"
 DEFER_WGRAD_JOIN = False
 _SIDE = {}
@@ -912,7 +927,7 @@ class TokenHeadFn(torch.autograd.Function):
     tensor-core-friendly shapes take the tcgen05 GEMM path; everything else the one-CTA-per-position kernel."""
 
     @staticmethod
-    def forward(ctx, h, Wo, bo):
+    def forward(ctx, h, Wo, bo, staged_pad=None):
         _need_cuda(h, Wo, bo)
         h = h.contiguous()
         dt = dt_of(h)
@@ -924,12 +939,16 @@ class TokenHeadFn(torch.autograd.Function):
         ctx.tc = tc
         ctx.keys = (Wo.data_ptr(), bo.data_ptr())
         if tc:
-            # Wo zero-padded to 128 vocabulary rows, and its transpose: the K-major operands of the two GEMMs
-            pad = torch.zeros((2, 128, C), dtype=torch.bfloat16, device=dev) if C == 128 else None
-            wo_pad = pad[0] if pad is not None else torch.zeros((128, C), dtype=torch.bfloat16, device=dev)
-            woT_pad = pad[1] if pad is not None else torch.zeros((C, 128), dtype=torch.bfloat16, device=dev)
-            wo_pad[:V].copy_(Wo)
-            woT_pad[:, :V].copy_(Wo.t())
+            # Wo zero-padded to 128 vocabulary rows, and its transpose: the K-major operands of the two GEMMs.  staged_pad:
+            # the pair already written by this step's weight-staging launch (ProteinBERT.forward)
+            if staged_pad is not None:
+                wo_pad, woT_pad = staged_pad
+            else:
+                pad = torch.zeros((2, 128, C), dtype=torch.bfloat16, device=dev) if C == 128 else None
+                wo_pad = pad[0] if pad is not None else torch.zeros((128, C), dtype=torch.bfloat16, device=dev)
+                woT_pad = pad[1] if pad is not None else torch.zeros((C, 128), dtype=torch.bfloat16, device=dev)
+                wo_pad[:V].copy_(Wo)
+                woT_pad[:, :V].copy_(Wo.t())
             logits = torch.empty((B * L, 32), dtype=torch.float32, device=dev)
             _call("pb_token_head_fwd_tc", _p(h), _p(wo_pad), _p(bo), _p(logits), _p(p), B, L, C, V, _st())
             ctx.save_for_backward(h, Wo, p, woT_pad)
@@ -952,20 +971,27 @@ class TokenHeadFn(torch.autograd.Function):
             dlogit = torch.empty((B * L, 128), dtype=torch.bfloat16, device=dev)
             dWo_pad = torch.empty((128, C), dtype=torch.float32, device=dev)
             dbo = _gout(ctx.keys[1], (V,), dev, zero=True)
-            _call("pb_token_head_bwd_tc", _p(dP), _p(p), _p(h), _p(woT_pad), None, _p(dlogit), _p(dh), _p(dWo_pad), _p(dbo),
-                  B, L, C, V, *_wgrad_ws(dev), _st())
             dWo = dWo_pad[:V]
-            if GRAD_SINK is not None:
-                sl = GRAD_SINK.take(ctx.keys[0], (V, C))
+            sl = GRAD_SINK.take(ctx.keys[0], (V, C)) if GRAD_SINK is not None else None
+
+            def wgrad(first=None):          # dWo from the logit gradients (the padded GEMM output cannot alias the bucket)
+                _call("pb_token_head_bwd_tc", first, _p(p), _p(h), _p(woT_pad), None, _p(dlogit), None if first is None else _p(dh),
+                      _p(dWo_pad), _p(dbo), B, L, C, V, *_wgrad_ws(dev), _st())
                 if sl is not None:
-                    sl.copy_(dWo)               # 26 x 128 floats: the padded GEMM output cannot alias the bucket
-                    dWo = sl
-            return dh, dWo, dbo
+                    sl.copy_(dWo)
+
+            if WGRAD_STREAM and HEAD_WGRAD_SIDE:
+                _call("pb_token_head_bwd_tc", _p(dP), _p(p), _p(h), _p(woT_pad), None, _p(dlogit), _p(dh), None, _p(dbo),
+                      B, L, C, V, None, 0, _st())
+                run_on_side(dev, wgrad, p, h, dlogit, dWo_pad, sl)
+            else:
+                wgrad(_p(dP))
+            return dh, (sl if sl is not None else dWo), dbo, None
         dWo = _gout(ctx.keys[0], tuple(Wo.shape), dev)
         dbo = _gout(ctx.keys[1], (V,), dev)
         _call("pb_token_head_bwd", _p(dP), _p(p), _p(h), _p(Wo.contiguous()), None, _p(dh), _p(dWo), _p(dbo), B, L, C, V,
               dt, _st())
-        return dh, dWo, dbo
+        return dh, dWo, dbo, None
 
 
 class PretrainLossFn(torch.autograd.Function):
@@ -992,8 +1018,13 @@ class PretrainLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dloss):
         dPl, dPg = ctx.saved_tensors
+        if LOSS_GRAD_IS_ONE:          # pretraining_step without a gradient scale: backward starts from 1, nothing to multiply
+            return dPl, dPg, None, None, None, None
         s = dloss.float()
         return dPl * s, dPg * s, None, None, None, None
+
+
+LOSS_GRAD_IS_ONE = False          # set by training.pretraining_step around loss.backward() when it passes no gradient
 
 
 def linear_act(x, W, b, act, tc=False):

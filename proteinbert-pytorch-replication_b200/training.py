@@ -43,10 +43,12 @@ def pretraining_step(model, X, Y, W, reducer: Optional["GradAllReducer"] = None,
     if reducer is not None:
         reducer.prepare()
     ops.DEFER_WGRAD_JOIN = reducer is None          # the eager bucket hooks read gradients as they appear: join per block then
+    ops.LOSS_GRAD_IS_ONE = grad_scale is None
     try:
         loss.backward(gradient=grad_scale)
     finally:
         ops.DEFER_WGRAD_JOIN = False
+        ops.LOSS_GRAD_IS_ONE = False
         ops.join_side_streams()                     # weight gradients issued on the side stream (ops.LocalTrackFn)
     if reducer is not None:
         reducer.finish()
