@@ -106,20 +106,31 @@ def pack_batch(seqs: Sequence[str], anns, draws: Sequence[Dict[str, object]], ma
     return out
 
 
-def corrupt_pad(packed, device="cuda"):
+def corrupt_pad(packed, device="cuda", out=None):
     """Run the corruption/padding kernel.  Returns (X, Y, W) dicts of device tensors with the reference's
-    shapes and dtypes: local int64 [B,L] / global float32 [B,A]; weights float64."""
+    shapes and dtypes: local int64 [B,L] / global float32 [B,A]; weights float64.  ``out``: the (X, Y, W) triple of an
+    earlier call of the same shape, to be overwritten (a training loop that has consumed the previous batch saves six
+    allocations per batch)."""
     B, L, A = packed["B"], packed["L"], packed["A"]
     dev = torch.device(device)
     if dev.type != "cuda":
         raise RuntimeError("corrupt_pad runs on a CUDA device only (no CPU fallback)")
     d = {k: v.to(dev, non_blocking=True) for k, v in packed.items() if isinstance(v, torch.Tensor)}
-    x_local = torch.empty((B, L), dtype=torch.int64, device=dev)
-    y_local = torch.empty((B, L), dtype=torch.int64, device=dev)
-    w_local = torch.empty((B, L), dtype=torch.float64, device=dev)
-    x_global = torch.empty((B, A), dtype=torch.float32, device=dev)
-    y_global = torch.empty((B, A), dtype=torch.float32, device=dev)
-    w_global = torch.empty((B, A), dtype=torch.float64, device=dev)
+    if out is not None:
+        (X, Y, W) = out
+        x_local, y_local, w_local, x_global, y_global, w_global = X["local"], Y["local"], W["local"], X["global"], Y["global"], W["global"]
+        want = (((B, L), torch.int64), ((B, L), torch.int64), ((B, L), torch.float64), ((B, A), torch.float32), ((B, A), torch.float32),
+                ((B, A), torch.float64))
+        for t, (shp, dty) in zip((x_local, y_local, w_local, x_global, y_global, w_global), want):
+            if tuple(t.shape) != shp or t.dtype != dty or t.device != dev or not t.is_contiguous():
+                raise ValueError("corrupt_pad(out=...): tensors of another shape, dtype or device")
+    else:
+        x_local = torch.empty((B, L), dtype=torch.int64, device=dev)
+        y_local = torch.empty((B, L), dtype=torch.int64, device=dev)
+        w_local = torch.empty((B, L), dtype=torch.float64, device=dev)
+        x_global = torch.empty((B, A), dtype=torch.float32, device=dev)
+        y_global = torch.empty((B, A), dtype=torch.float32, device=dev)
+        w_global = torch.empty((B, A), dtype=torch.float64, device=dev)
     st = torch.cuda.current_stream(dev).cuda_stream
     check(lib().pb_corrupt_pad(d["seq_bytes"].data_ptr(), d["seq_off"].data_ptr(), d["crop_start"].data_ptr(),
                                d["tok_mask"].data_ptr(), d["tok_rand"].data_ptr(), d["draw_off"].data_ptr(),

@@ -384,7 +384,13 @@ def test_corrupt_pad_against_oracle_at_full_size(pb):
     anns[3] = 0
     torch.manual_seed(0)
     draws = [pb.data_processing.draw_sample(len(s), A, L) for s in seqs]
-    X, Y, W = pb.data_processing.corrupt_pad(pb.data_processing.pack_batch(seqs, anns, draws, L))
+    packed = pb.data_processing.pack_batch(seqs, anns, draws, L)
+    X, Y, W = pb.data_processing.corrupt_pad(packed)
+    # out=: the same six tensors, overwritten in place (poisoned first)
+    for t in (X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"]):
+        t.fill_(7)
+    X2, Y2, W2 = pb.data_processing.corrupt_pad(packed, out=(X, Y, W))
+    assert X2["local"].data_ptr() == X["local"].data_ptr() and W2["global"].data_ptr() == W["global"].data_ptr()
     nd = [dict(crop_start=d["crop_start"], tok_mask=d["tok_mask"].numpy(), tok_rand=d["tok_rand"].numpy(), coin=d["coin"],
                keep=(d["keep"].numpy() if d["keep"] is not None else np.zeros(A, np.int64)),
                add=(d["add"].numpy() if d["add"] is not None else np.zeros(A, np.int64))) for d in draws]
