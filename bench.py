@@ -616,25 +616,47 @@ def main():
                 "timing": f"CUDA events around {n_conv} back-to-back launches of pb_conv_pair_fwd on the workload's tensors (block 0 weights)"}
 
     # ---- e2e: public API from pinned host buffers, H2D of inputs + D2H of the loss inside the timed region ----
+    pending = [None]
+    losses_read = [0]
+
     def e2e_step():
         if graph is not None:            # public fast path: H2D into the static buffers, graph replay, D2H of the loss
             Xh, Yh, Wh = dicts(host)
             # the next batch's H2D (here: the same pinned host tensors again, a full copy per step) is started on a
-            # side stream while this step computes -- what a data loader with one batch of look-ahead does
-            return graph(Xh, Yh, Wh, prefetch=(Xh, Yh, Wh)).item()
+            # side stream while this step computes -- what a data loader with one batch of look-ahead does.  The loss of
+            # EVERY step is read on the host (8 bytes, pinned), one step late: the host waits for step k-1's copy after it
+            # has issued step k, so the GPU always has the next step queued (a .item() per step leaves it idle meanwhile)
+            graph(Xh, Yh, Wh, prefetch=(Xh, Yh, Wh))
+            h = graph.read_loss_async()
+            if pending[0] is not None:
+                pending[0].value()
+                losses_read[0] += 1
+            pending[0] = h
+            return
         b = [t.to(dev, non_blocking=True) for t in host]
         Xh, Yh, Wh = dicts(b)
         loss = pb.pretraining_step(model, Xh, Yh, Wh, reducer)
-        return loss.item()
+        loss.item()
+        losses_read[0] += 1
+
+    def e2e_drain():
+        if pending[0] is not None:
+            pending[0].value()
+            losses_read[0] += 1
+            pending[0] = None
 
     for _ in range(3):
         e2e_step()
+    e2e_drain()
     barrier()
+    losses_read[0] = 0
     e0.record()
     for _ in range(args.steps):
         e2e_step()
+    e2e_drain()                          # the last step's loss is on the host before the region ends
     e1.record()
     barrier()
+    assert losses_read[0] == args.steps
     ms_e2e = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms_e2e], device=dev)
@@ -695,7 +717,9 @@ def main():
                            "timed_region": "forward + loss + backward" + (" + gradient all-reduce" if world > 1 else "")},
                 "clocks": clocks,
                 "e2e": {"value": gb * args.steps / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d_bytes,
-                        "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / args.steps},
+                        "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e / args.steps,
+                        "loss_read": "every step's loss is copied to pinned host memory and read there one step late "
+                                     "(GraphedPretrainStep.read_loss_async); the last one before the region ends"},
                 "gpu_launches": int(launches), "roofline": roofline,
                 "model_tflops": flops_per_sample(CFG) * value / 1e12,
                 "model_tflops_note": f"FLOPs executed (closed-form attention, {flops_per_sample(CFG) / 1e9:.3f} GF/sample); the reference "

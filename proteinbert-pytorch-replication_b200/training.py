@@ -513,6 +513,27 @@ class GraphedPretrainStep:
                 if t is not dst:
                     dst.copy_(t, non_blocking=True)
 
+    def read_loss_async(self):
+        """Start copying the loss of the step just issued to pinned host memory and return a handle; ``handle.value()`` waits
+        for THAT copy only.  A loop that calls ``.item()`` on the returned loss tensor every step (utils.py:295 does) stalls the
+        host until the step has finished and leaves the GPU idle until the next replay is issued; reading the handle one step
+        late keeps one step queued behind the running one."""
+        if getattr(self, "_loss_host", None) is None:
+            self._loss_host = [torch.empty((), dtype=torch.float64).pin_memory() for _ in range(2)]
+            self._loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+            self._loss_i = 0
+        i = self._loss_i
+        self._loss_i ^= 1
+        host, ev = self._loss_host[i], self._loss_ev[i]
+        host.copy_(self.loss, non_blocking=True)
+        ev.record(torch.cuda.current_stream(self.device))
+
+        class _Handle:
+            def value(self_inner) -> float:
+                ev.synchronize()
+                return float(host)
+        return _Handle()
+
     def replay_local(self):
         """The captured graphs alone: this rank's gradients (already scaled by 1/world), no exchange."""
         self.graph.replay()

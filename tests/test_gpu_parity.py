@@ -463,6 +463,12 @@ def test_graphed_step_and_two_stage_backward_match_eager(pb, wide_ref):
         tol = 1e-6 * abs(float(loss_e))                           # float atomics: replays agree to rounding, not bitwise
         assert abs(lA - float(loss_e)) <= tol and abs(lA2 - lA) <= tol
         assert abs(lB - lB_direct) <= tol and abs(lB - lA) > 100 * tol
+        # losses read one step late through pinned memory: handle k holds step k's loss even after step k+1 was issued
+        step(*dA)
+        hA = step.read_loss_async()
+        step(*dB)
+        hB = step.read_loss_async()
+        assert abs(hA.value() - lA) <= tol and abs(hB.value() - lB) <= tol
         del step
 
 
