@@ -144,12 +144,14 @@ def corrupt_pad(packed, device="cuda", out=None):
 def corrupt_pad_device_draws(seqs, anns, max_length: int, seed: int, counter: int, device="cuda",
                              p: float = .05, positive_p: float = 0.25, negative_p: float = 0.0001):
     """corrupt_pad with the random draws made on the GPU (``pb_draw_batch``, Philox keyed by ``seed``, ``counter`` = batch
-    number) instead of the torch CPU generator: the host only packs the residue bytes and the annotation rows."""
+    number) instead of the torch CPU generator: the host only packs the residue bytes and the annotation rows.
+    ``seqs`` may be str or bytes (h5py hands the ``seqs`` dataset of the reference's H5 record format back as bytes,
+    uniref_dataset.py:236-245) and ``anns`` any integer or bool [B, A] array (its ``annotation_masks`` rows)."""
     B, A = len(seqs), len(anns[0])
     dev = torch.device(device)
     if dev.type != "cuda":
         raise RuntimeError("device draws run on a CUDA device only")
-    raw = [s.encode("latin-1", errors="replace") for s in seqs]
+    raw = [bytes(s) if isinstance(s, (bytes, bytearray, np.bytes_)) else str(s).encode("latin-1", errors="replace") for s in seqs]
     n_draw = [min(len(r) + 2, max_length) for r in raw]
     seq_off = np.zeros(B + 1, dtype=np.int64); seq_off[1:] = np.cumsum([len(r) for r in raw])
     draw_off = np.zeros(B + 1, dtype=np.int64); draw_off[1:] = np.cumsum(n_draw)

@@ -69,6 +69,12 @@ def test_device_draws_have_the_reference_distributions_and_feed_the_same_kernel(
     _, d4 = dp.corrupt_pad_device_draws(seqs, anns, L, seed=8, counter=1)
     assert torch.equal(d2["keep"], d["keep"]) and torch.equal(d2["tok_rand"], d["tok_rand"])
     assert not torch.equal(d3["keep"], d["keep"]) and not torch.equal(d4["keep"], d["keep"])
+    # the reference's H5 record arrays as h5py returns them (uniref_dataset.py:236-245): bytes sequences, bool mask rows
+    seqs_b = np.array([s.encode("ascii") for s in seqs], dtype=object)
+    (Xb, Yb, Wb), _ = dp.corrupt_pad_device_draws(seqs_b, anns.astype(bool), L, seed=7, counter=1)
+    for a, b_ in zip((X["local"], X["global"], Y["local"], Y["global"], W["local"], W["global"]),
+                     (Xb["local"], Xb["global"], Yb["local"], Yb["global"], Wb["local"], Wb["global"])):
+        assert torch.equal(a, b_)
 
 
 def test_dataset_works_under_the_reference_dataloader_recipe(pb):
