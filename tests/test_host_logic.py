@@ -149,3 +149,52 @@ def test_warmup_then_plateau_follows_the_reference_schedule():
     sch2 = pb.WarmupThenPlateau(opt2, warmup_duration=4, patience=2)
     sch2.load_state_dict(sd)
     assert sch2.steps == sch.steps
+
+
+def test_gradient_bucket_layout_follows_production_order():
+    """training.FlatGradBucket: one flat buffer, gradients laid out in the order backward produces them -- heads,
+    blocks last to first (post half, local track, pre half), annotation-input layer and embedding last -- so that everything
+    above a cut of backward is a PREFIX of the buffer.  Host logic only: built on CPU parameters."""
+    import proteinbert_b200 as pb
+    from proteinbert_b200 import training
+    cfg = dict(sequences_length=32, num_annotations=50, local_dim=16, global_dim=32, key_dim=8, num_heads=2, num_blocks=4)
+    model = pb.ProteinBERT(device="cpu", **cfg)
+    bk = training.FlatGradBucket(model)
+    names = [n for n, _ in model.named_parameters()]
+    assert set(bk.slices) == set(names)
+    spans = sorted((off, off + n, name) for name, (off, n) in bk.slices.items())
+    for (a0, a1, na), (b0, b1, nb) in zip(spans, spans[1:]):
+        assert a1 <= b0, (na, nb)                                   # no overlap
+    assert all(off % 4 == 0 for off, _, _ in spans)                 # 16-byte aligned slices (vector stores, multimem)
+    assert bk.numel % bk.ALIGN == 0 and spans[-1][1] <= bk.numel
+    # group order: heads first, then blocks 3, 2, 1, 0, then the tail
+    first = {}
+    for off, _, name in spans:
+        key = "heads" if name.startswith("pretraining_") else (int(name.split(".")[1]) if name.startswith("proteinBERT_blocks.") else "tail")
+        first.setdefault(key, off)
+    assert first["heads"] < first[3] < first[2] < first[1] < first[0] < first["tail"]
+    # inside a block: post half | local track | pre half
+    b2 = [(off, name) for off, _, name in spans if name.startswith("proteinBERT_blocks.2.")]
+    post = [o for o, n in b2 if training._is_block_post_param(n)]
+    pre = [o for o, n in b2 if training._is_block_pre_param(n)]
+    local = [o for o, n in b2 if not training._is_block_post_param(n) and not training._is_block_pre_param(n)]
+    assert max(post) < min(local) and max(local) < min(pre)
+    # accumulated gradients (biases, LayerNorm affines, W_parameter) are exactly what the clearing launch covers
+    covered = lambda off, n: any(a <= off and off + n <= b for a, b in bk.zero_ranges)
+    for name, (off, n) in bk.slices.items():
+        assert covered(off, n) == training._needs_zero(name) or (not training._needs_zero(name) and not covered(off, n)), name
+    # cuts: everything produced above the input of block c is a prefix; cutting lower covers more; with cluster units the post
+    # half of the block below belongs to the part above the cut
+    o3, o2, o1 = (bk.split_offset(c, units=False) for c in (3, 2, 1))
+    assert 0 < o3 < o2 < o1 <= bk.numel
+    for c in (3, 2, 1):
+        off_u, off_p = bk.split_offset(c, units=True), bk.split_offset(c, units=False)
+        assert off_u > off_p
+        below_post = [bk.slices[n] for n in names if n.startswith(f"proteinBERT_blocks.{c - 1}.") and training._is_block_post_param(n)]
+        assert all(o + k <= off_u for o, k in below_post) and all(o >= off_p for o, k in below_post)
+        above = [bk.slices[n] for n in names if n.startswith("pretraining_") or
+                 (n.startswith("proteinBERT_blocks.") and int(n.split(".")[1]) >= c)]
+        assert all(o + k <= off_p for o, k in above)
+    # views alias the flat buffer
+    v = bk.view(names[0])
+    assert v.data_ptr() == bk.flat.data_ptr() + 4 * bk.slices[names[0]][0] and tuple(v.shape) == tuple(dict(model.named_parameters())[names[0]].shape)
