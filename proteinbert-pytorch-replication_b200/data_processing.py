@@ -122,7 +122,8 @@ def corrupt_pad(packed, device="cuda", out=None):
         want = (((B, L), torch.int64), ((B, L), torch.int64), ((B, L), torch.float64), ((B, A), torch.float32), ((B, A), torch.float32),
                 ((B, A), torch.float64))
         for t, (shp, dty) in zip((x_local, y_local, w_local, x_global, y_global, w_global), want):
-            if tuple(t.shape) != shp or t.dtype != dty or t.device != dev or not t.is_contiguous():
+            same_dev = t.device.type == "cuda" and (dev.index is None or t.device.index == dev.index)
+            if tuple(t.shape) != shp or t.dtype != dty or not same_dev or not t.is_contiguous():
                 raise ValueError("corrupt_pad(out=...): tensors of another shape, dtype or device")
     else:
         x_local = torch.empty((B, L), dtype=torch.int64, device=dev)
