@@ -198,3 +198,15 @@ def test_gradient_bucket_layout_follows_production_order():
     # views alias the flat buffer
     v = bk.view(names[0])
     assert v.data_ptr() == bk.flat.data_ptr() + 4 * bk.slices[names[0]][0] and tuple(v.shape) == tuple(dict(model.named_parameters())[names[0]].shape)
+
+
+def test_nvls_launch_shape_word():
+    """FlatGradBucket.nvls_shape packs (CTAs, threads, reductions in flight) as pb_multimem_allreduce reads them
+    (include/pb_b200.h: bits 0-15, 16-27, 28-30 with selector 0 -> 8, 1 -> 1, 2 -> 2, 3 -> 4)."""
+    from proteinbert_b200 import training
+    w = training.FlatGradBucket.nvls_shape(16, 128, 4)
+    assert w & 0xffff == 16 and (w >> 16) & 0xfff == 128 and (w >> 28) & 7 == 3
+    assert training.FlatGradBucket.nvls_shape(16) == 16 | (512 << 16)          # defaults: 512 threads, 8 in flight (selector 0)
+    assert (training.FlatGradBucket.nvls_shape(148, 32, 2) >> 28) & 7 == 2
+    with pytest.raises(KeyError):
+        training.FlatGradBucket.nvls_shape(8, 256, 3)
