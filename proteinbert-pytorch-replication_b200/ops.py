@@ -302,6 +302,7 @@ class ResLnRowsFn(torch.autograd.Function):
                                        B, G, _st())
         ctx.save_for_backward(gamma, xhat, rstd, c, w_param)
         ctx.has = (b is not None, c is not None)
+        ctx.keys = (gamma.data_ptr(), beta.data_ptr(), None if w_param is None else w_param.data_ptr())
         return y
 
     @staticmethod
@@ -313,9 +314,10 @@ class ResLnRowsFn(torch.autograd.Function):
         K = 0 if w_param is None else w_param.numel()
         dx = torch.empty_like(dy)
         dc = torch.empty_like(dy) if has_c else None
-        dgamma = torch.empty_like(gamma)
-        dbeta = torch.empty_like(gamma)
-        dwp = torch.empty_like(w_param) if has_c else None
+        # straight into the gradient bucket when a sink is active (the entry point clears these three outputs itself)
+        dgamma = _gout(ctx.keys[0], tuple(gamma.shape), dy.device)
+        dbeta = _gout(ctx.keys[1], tuple(gamma.shape), dy.device)
+        dwp = _gout(ctx.keys[2], tuple(w_param.shape), dy.device) if has_c else None
         _call("pb_res_ln_rows_bwd", _p(dy), _p(gamma), _p(xhat), _p(rstd), _p(c), _p(w_param), K, _p(dx), _p(dc),
                                        _p(dgamma), _p(dbeta), _p(dwp), B, G, _st())
         return dx, (dx if has_b else None), dc, dwp, dgamma, dbeta

@@ -154,7 +154,10 @@ class FlatGradBucket:
                 # queue behind them -- at 16 x 512 x 8 in flight concurrent LayerNorm / reduce kernels ran 3-6x slower and the
                 # overlap gained nothing.  8 x B200, step time: no overlap 1930 us, 16x512x8 1921, 8x256x4 1866, 148x32x2 1871,
                 # 32x128x2 1843, 16x128x4 1841 (scripts/ddp_sweep.py).
-                self._nvls_ctas_early = self.nvls_shape(int(os.environ.get("PB_B200_NVLS_EARLY_CTAS", "16")),
+                # ... for the default model's 64.7 MB bucket; a larger bucket has to move more bytes in the same backward, so the CTA
+                # count grows with it (BASELINE config 5, 297 MB: 16 CTAs left the exchange 850 us exposed on 2 GPUs, 64 CTAs 345)
+                early_ctas = 16 * min(4, max(1, -(-4 * self.numel // (80 << 20))))
+                self._nvls_ctas_early = self.nvls_shape(int(os.environ.get("PB_B200_NVLS_EARLY_CTAS", str(early_ctas))),
                                                         int(os.environ.get("PB_B200_NVLS_EARLY_THREADS", "128")),
                                                         int(os.environ.get("PB_B200_NVLS_EARLY_INFLIGHT", "4")))
             except Exception as e:
